@@ -1,0 +1,49 @@
+# Build libbibfs_b200.so (sm_100a only) and the native `bibfs` CLI, in-tree.
+#   make            -> bidirectional_bfs_b200/_native/libbibfs_b200.so + bin/bibfs
+#   make sass       -> docs/sass/*.sass listings (cuobjdump)
+#   make clean
+# Counterpart of the reference's per-variant Makefiles (v1..v4/Makefile); the reference's SMS list
+# (sm_50..sm_90, v3/Makefile:16-18) is replaced by the single Blackwell target.
+NVCC      ?= /usr/local/cuda/bin/nvcc
+CXX       ?= g++
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVCCFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O3,-Wall,-Wno-unknown-pragmas \
+             -Xptxas -v --expt-relaxed-constexpr -Iinclude
+CXXFLAGS  := -O3 -std=c++17 -fPIC -Wall -Wno-unknown-pragmas -ffp-contract=off -Iinclude -pthread
+BUILD     := build
+OUTDIR    := bidirectional_bfs_b200/_native
+LIB       := $(OUTDIR)/libbibfs_b200.so
+CLI       := bin/bibfs
+
+CU_SRCS   := csrc/gen_dev.cu csrc/csr_dev.cu csrc/bfs_dev.cu csrc/ctx.cu csrc/naive_dev.cu csrc/msbfs_dev.cu
+CPP_SRCS  := csrc/error.cpp csrc/host_io.cpp csrc/host_graph.cpp csrc/cpu_serial.cpp csrc/cpu_ranks.cpp
+CU_OBJS   := $(patsubst csrc/%.cu,$(BUILD)/%.o,$(CU_SRCS))
+CPP_OBJS  := $(patsubst csrc/%.cpp,$(BUILD)/%.o,$(CPP_SRCS))
+HDRS      := $(wildcard csrc/*.h csrc/*.cuh include/*.h)
+
+all: $(LIB) $(CLI)
+
+$(BUILD)/%.o: csrc/%.cu $(HDRS)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(NVCCFLAGS) -c $< -o $@ 2> $(BUILD)/$*.ptxas.log || (cat $(BUILD)/$*.ptxas.log; exit 1)
+
+$(BUILD)/%.o: csrc/%.cpp $(HDRS)
+	@mkdir -p $(BUILD)
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+
+$(LIB): $(CU_OBJS) $(CPP_OBJS)
+	@mkdir -p $(OUTDIR)
+	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart -lpthread
+
+$(CLI): csrc/cli_main.cpp $(LIB) $(HDRS)
+	@mkdir -p bin
+	$(CXX) $(CXXFLAGS) -I/usr/local/cuda/include csrc/cli_main.cpp -o $@ -L$(OUTDIR) -lbibfs_b200 -Wl,-rpath,'$$ORIGIN/../$(OUTDIR)' -L/usr/local/cuda/lib64 -Wl,-rpath,/usr/local/cuda/lib64 -lcudart
+
+sass: $(LIB)
+	@mkdir -p docs/sass
+	/usr/local/cuda/bin/cuobjdump -sass $(LIB) > docs/sass/libbibfs_b200.sass
+
+clean:
+	rm -rf $(BUILD) $(LIB) $(CLI)
+
+.PHONY: all clean sass

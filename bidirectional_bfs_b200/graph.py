@@ -1,0 +1,128 @@
+"""Graph: 1-D vertex-partitioned CSR shards held as torch tensors.
+
+``row_ptr`` is int64 (64-bit offsets: the reference's ``int`` offsets overflow at 2M >= 2^31,
+v4/comp.cu:49-55), ``col`` is int32 carrying uint32 bit patterns.  A Graph hosts one or more of
+the P shards: all of them on the CPU or for single-process multi-rank emulation, exactly one per
+process in the torchrun multi-GPU mode.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import io as _io
+from ._lib import GenSpec
+from .ops import csr as _csr
+from .ops import gen as _gen
+from .parallel.partition import Partition
+
+
+@dataclass
+class Shard:
+    rank: int
+    lo: int
+    hi: int
+    row_ptr: torch.Tensor
+    col: torch.Tensor
+
+    @property
+    def nnz(self) -> int:
+        return int(self.col.numel())
+
+
+@dataclass
+class Graph:
+    n: int
+    nranks: int
+    device: torch.device
+    shards: dict[int, Shard] = field(default_factory=dict)
+    m_records: int = 0            # edge records fed to the builder (each undirected edge once)
+    spec: GenSpec | None = None
+    name: str = ""
+
+    # ---- construction ------------------------------------------------------------------
+    @staticmethod
+    def _build(n, edges, spec, device, nranks, ranks, sort_rows, name) -> "Graph":
+        dev = torch.device(device)
+        part = Partition(n, nranks)
+        g = Graph(n=n, nranks=nranks, device=dev, spec=spec, name=name)
+        hosted = list(range(nranks)) if ranks is None else list(ranks)
+        if edges is not None:
+            if isinstance(edges, np.ndarray):
+                edges = torch.from_numpy(np.ascontiguousarray(edges.reshape(-1, 2)).view(np.int32))
+            edges = edges.reshape(-1, 2).to(torch.int32).to(dev).contiguous()
+            g.m_records = edges.shape[0]
+        for r in hosted:
+            lo, hi = part.range(r)
+            rp, col = _csr.build_csr(n, edges, spec if edges is None else None, lo, hi, dev, sort_rows)
+            g.shards[r] = Shard(r, lo, hi, rp, col)
+        return g
+
+    @staticmethod
+    def from_edges(n, edges, device="cpu", nranks=1, ranks=None, sort_rows=False, name="") -> "Graph":
+        return Graph._build(int(n), edges, None, device, nranks, ranks, sort_rows, name)
+
+    @staticmethod
+    def from_bin(path, device="cpu", nranks=1, ranks=None, sort_rows=False) -> "Graph":
+        n, edges = _io.read_bin(path)
+        return Graph._build(n, edges, None, device, nranks, ranks, sort_rows, str(path))
+
+    @staticmethod
+    def from_json(path, device="cpu", nranks=1, ranks=None, sort_rows=False) -> "Graph":
+        n, edges = _io.read_json_graph(path)
+        return Graph._build(n, edges, None, device, nranks, ranks, sort_rows, str(path))
+
+    @staticmethod
+    def from_file(path, **kw) -> "Graph":
+        return Graph.from_json(path, **kw) if str(path).endswith(".json") else Graph.from_bin(path, **kw)
+
+    @staticmethod
+    def generate(spec: GenSpec, device="cpu", nranks=1, ranks=None, sort_rows=False, name="") -> "Graph":
+        """Build straight from a generator spec: the edge list is never materialised; every hosted
+        shard regenerates the stream and keeps the rows it owns."""
+        return Graph._build(int(spec.n), None, spec, device, nranks, ranks, sort_rows, name)
+
+    # ---- views ---------------------------------------------------------------------------
+    @property
+    def partition(self) -> Partition:
+        return Partition(self.n, self.nranks)
+
+    @property
+    def nnz(self) -> int:
+        return sum(s.nnz for s in self.shards.values())
+
+    def single(self) -> Shard:
+        if self.nranks != 1:
+            raise ValueError("this operation needs an unpartitioned graph (nranks=1)")
+        return self.shards[0]
+
+    def degree(self, v: int) -> int:
+        s = self.shards[self.partition.owner(v)]
+        i = v - s.lo
+        return int(s.row_ptr[i + 1] - s.row_ptr[i])
+
+    def neighbors(self, v: int) -> np.ndarray:
+        s = self.shards[self.partition.owner(v)]
+        i = v - s.lo
+        a, b = int(s.row_ptr[i]), int(s.row_ptr[i + 1])
+        return s.col[a:b].cpu().numpy().view(np.uint32)
+
+    def to_scipy(self):
+        from scipy.sparse import csr_matrix
+        s = self.single()
+        rp = s.row_ptr.cpu().numpy()
+        col = s.col.cpu().numpy().view(np.uint32)
+        return csr_matrix((np.ones(col.shape[0], dtype=np.uint8), col, rp), shape=(self.n, self.n))
+
+    def to(self, device) -> "Graph":
+        dev = torch.device(device)
+        g = Graph(self.n, self.nranks, dev, {}, self.m_records, self.spec, self.name)
+        for r, s in self.shards.items():
+            g.shards[r] = Shard(r, s.lo, s.hi, s.row_ptr.to(dev), s.col.to(dev))
+        return g
+
+
+def edge_list(spec: GenSpec, device="cpu") -> np.ndarray:
+    return _gen.edges_to_numpy(_gen.generate_edges(spec, device))

@@ -1,0 +1,235 @@
+"""Solver classes behind ``bibfs(graph, src, dst, variant=...)``."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from .._lib import F_NO_PATH, Result, check, lib
+from ..graph import Graph
+from ..ops.search import PathResult, SearchContext, result_from_c
+
+VARIANTS = ("serial", "cpu-ranks", "gpu", "multi-gpu", "naive-gpu")
+
+
+class _CpuSolver:
+    variant = ""
+
+    def __init__(self, graph: Graph):
+        if graph.device.type != "cpu" or graph.nranks != 1:
+            graph = _as_single(graph, "cpu")
+        self.graph = graph
+        self._path = np.empty(graph.n + 1, dtype=np.uint32)
+
+    def close(self):
+        pass
+
+
+def _as_single(graph: Graph, device) -> Graph:
+    """Re-assemble / move a graph into a single shard on `device` (host-side convenience)."""
+    dev = torch.device(device)
+    if graph.nranks == 1:
+        return graph.to(dev)
+    if len(graph.shards) != graph.nranks:
+        raise ValueError("cannot re-assemble a graph whose shards live in other processes")
+    rps, cols, base = [], [], 0
+    for r in range(graph.nranks):
+        s = graph.shards[r]
+        rp = s.row_ptr.cpu()
+        rps.append(rp[:-1] + base)
+        base += int(rp[-1])
+        cols.append(s.col.cpu())
+    rps.append(torch.tensor([base], dtype=torch.int64))
+    g = Graph(graph.n, 1, dev, {}, graph.m_records, graph.spec, graph.name)
+    from ..graph import Shard
+    g.shards[0] = Shard(0, 0, graph.n, torch.cat(rps).to(dev), torch.cat(cols).to(dev))
+    return g
+
+
+class SerialSolver(_CpuSolver):
+    """v1 equivalent.  policy 0 replays v1's schedule (early break inside the level)."""
+    variant = "serial"
+
+    def __init__(self, graph: Graph, policy: int = 0):
+        super().__init__(graph)
+        self.policy = policy
+
+    def query(self, src, dst, want_path=True) -> PathResult:
+        s = self.graph.single()
+        r = Result()
+        check(lib().bibfs_serial(self.graph.n, s.row_ptr.data_ptr(), s.col.data_ptr(), int(src), int(dst), self.policy,
+                                 C.byref(r), self._path.ctypes.data if want_path else None, self._path.size if want_path else 0))
+        return result_from_c(src, dst, r, self._path, self.variant)
+
+
+class CpuRanksSolver(_CpuSolver):
+    """v2 equivalent with `ranks` worker threads standing in for MPI ranks."""
+    variant = "cpu-ranks"
+
+    def __init__(self, graph: Graph, ranks: int = 4):
+        super().__init__(graph)
+        self.ranks = ranks
+
+    def query(self, src, dst, want_path=True) -> PathResult:
+        s = self.graph.single()
+        r = Result()
+        check(lib().bibfs_cpu_ranks(self.graph.n, s.row_ptr.data_ptr(), s.col.data_ptr(), int(src), int(dst), self.ranks,
+                                    C.byref(r), self._path.ctypes.data if want_path else None, self._path.size if want_path else 0))
+        return result_from_c(src, dst, r, self._path, self.variant)
+
+
+class GpuSolver:
+    """Single-GPU persistent kernel (one launch per query)."""
+    variant = "gpu"
+
+    def __init__(self, graph: Graph, device=None, **ctx_kw):
+        if graph.device.type != "cuda" or graph.nranks != 1:
+            dev = device or (graph.device if graph.device.type == "cuda" else "cuda:0")
+            graph = _as_single(graph, dev)
+        self.graph = graph
+        self.ctx = SearchContext(graph, 0, 1, **ctx_kw)
+
+    def query(self, src, dst, want_path=True, flags=0, pinned_query=None) -> PathResult:
+        if not want_path:
+            flags |= F_NO_PATH
+        return self.ctx.query(src, dst, flags, want_path, pinned_query, self.variant)
+
+    def close(self):
+        self.ctx.close()
+
+
+class MultiGpuSolver:
+    """P ranks over 1-D partitioned shards.
+
+    Three deployments of the same fused kernel:
+      * ``MultiGpuSolver(graph)`` with all P shards on ONE device: P virtual ranks in one
+        cooperative launch (protocol test / fewer GPUs than ranks);
+      * ``MultiGpuSolver.across_devices(graphs)``: one process, one context per device, peers mapped
+        with cudaDeviceEnablePeerAccess;
+      * ``parallel.comm.DistributedSolver``: one process per GPU (torchrun), peers mapped through
+        CUDA IPC handles exchanged over torch.distributed.
+    """
+    variant = "multi-gpu"
+
+    def __init__(self, graph: Graph, **ctx_kw):
+        if graph.device.type != "cuda":
+            raise ValueError("MultiGpuSolver needs CUDA shards")
+        if len(graph.shards) != graph.nranks:
+            raise ValueError("virtual-rank mode hosts every shard on one device")
+        self.graph = graph
+        self.ctxs = [SearchContext(graph, 0, graph.nranks, **ctx_kw)]
+
+    @classmethod
+    def across_devices(cls, graphs: list[Graph], **ctx_kw) -> "MultiGpuSolver":
+        self = cls.__new__(cls)
+        self.graph = graphs[0]
+        self.ctxs = []
+        for g in graphs:
+            (rank,) = g.shards.keys()
+            with torch.cuda.device(g.device):
+                self.ctxs.append(SearchContext(g, rank, 1, **ctx_kw))
+        for a in self.ctxs:
+            for b in self.ctxs:
+                if a is not b:
+                    a.attach_local(b.rank_lo, b)
+        return self
+
+    def query(self, src, dst, want_path=True, flags=0) -> PathResult:
+        if not want_path:
+            flags |= F_NO_PATH
+        for c in self.ctxs:
+            with torch.cuda.device(c.device):
+                c.launch(src, dst, flags)
+        res = None
+        for i, c in enumerate(self.ctxs):
+            with torch.cuda.device(c.device):
+                r = c.fetch(src, dst, want_path and i == 0, self.variant)
+            if res is None:
+                res = r
+            else:   # device time = max over ranks
+                res.search_ms = max(res.search_ms, r.search_ms)
+                res.path_ms = max(res.path_ms, r.path_ms)
+        return res
+
+    def close(self):
+        for c in self.ctxs:
+            c.close()
+
+
+class NaiveGpuSolver:
+    """Reference-style level-synchronous GPU search (thread per vertex, host in the loop)."""
+    variant = "naive-gpu"
+
+    def __init__(self, graph: Graph, device=None):
+        if graph.device.type != "cuda" or graph.nranks != 1:
+            graph = _as_single(graph, device or "cuda:0")
+        self.graph = graph
+
+    def query(self, src, dst, want_path=False) -> PathResult:
+        s = self.graph.single()
+        length, ms = C.c_int32(-1), C.c_float(0)
+        with torch.cuda.device(self.graph.device):
+            check(lib().bibfs_naive_levelsync_device(self.graph.n, s.row_ptr.data_ptr(), s.col.data_ptr(), int(src), int(dst),
+                                                     C.byref(length), C.byref(ms),
+                                                     torch.cuda.current_stream(self.graph.device).cuda_stream))
+        return PathResult(src, dst, int(length.value) if length.value >= 0 else None, None,
+                          search_ms=float(ms.value), variant=self.variant)
+
+    def close(self):
+        pass
+
+
+class BatchSolver:
+    """Bit-parallel bidirectional MS-BFS: up to 64 queries per sweep (csrc/msbfs_dev.cu)."""
+    variant = "batch"
+
+    def __init__(self, graph: Graph, device=None):
+        if graph.device.type != "cuda" or graph.nranks != 1:
+            graph = _as_single(graph, device or "cuda:0")
+        self.graph = graph
+        with torch.cuda.device(graph.device):
+            self._ws = torch.empty(lib().bibfs_batch_workspace_bytes(graph.n), dtype=torch.uint8, device=graph.device)
+        self.last_ms = 0.0
+
+    def query_batch(self, srcs, dsts) -> list[int | None]:
+        srcs = np.ascontiguousarray(np.asarray(srcs, dtype=np.uint32))
+        dsts = np.ascontiguousarray(np.asarray(dsts, dtype=np.uint32))
+        assert srcs.shape == dsts.shape
+        s = self.graph.single()
+        out: list[int | None] = []
+        self.last_ms = 0.0
+        self.last_meet = []
+        with torch.cuda.device(self.graph.device):
+            st = torch.cuda.current_stream(self.graph.device).cuda_stream
+            for i in range(0, srcs.size, 64):
+                a, b = srcs[i:i + 64], dsts[i:i + 64]
+                lens = np.empty(a.size, dtype=np.int32)
+                meet = np.empty(a.size, dtype=np.uint32)
+                ms = C.c_float(0)
+                check(lib().bibfs_batch_query_device(self.graph.n, s.row_ptr.data_ptr(), s.col.data_ptr(), a.ctypes.data,
+                                                     b.ctypes.data, a.size, lens.ctypes.data, meet.ctypes.data,
+                                                     self._ws.data_ptr(), self._ws.numel(), C.byref(ms), st))
+                self.last_ms += float(ms.value)
+                out += [int(x) if x >= 0 else None for x in lens]
+                self.last_meet += [int(x) for x in meet]
+        return out
+
+    def close(self):
+        self._ws = None
+
+
+def make_solver(graph: Graph, variant: str = "gpu", **kw):
+    if variant == "serial":
+        return SerialSolver(graph, **kw)
+    if variant == "cpu-ranks":
+        return CpuRanksSolver(graph, **kw)
+    if variant == "gpu":
+        return GpuSolver(graph, **kw)
+    if variant == "multi-gpu":
+        return MultiGpuSolver(graph, **kw)
+    if variant == "naive-gpu":
+        return NaiveGpuSolver(graph, **kw)
+    if variant == "batch":
+        return BatchSolver(graph, **kw)
+    raise ValueError(f"unknown variant {variant!r}; choose from {VARIANTS + ('batch',)}")

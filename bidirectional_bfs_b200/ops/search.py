@@ -1,0 +1,135 @@
+"""SearchContext: Python handle on a device search context (csrc/ctx.cu, csrc/bfs_dev.cu).
+
+One context hosts the per-query state ("arena") of one or more consecutive ranks on the current
+device and launches ONE persistent cooperative kernel per query.  Counterpart of the reference's
+v4 C API (v4/comp.h:8-36), minus the per-level host calls.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from .._lib import CtxDesc, LevelTrace, Result, check, lib
+
+
+@dataclass
+class PathResult:
+    src: int
+    dst: int
+    length: int | None           # hops, None when no path
+    path: list[int] | None
+    meet: int | None = None
+    levels: int = 0
+    levels_bottom_up: int = 0
+    depth_s: int = 0
+    depth_t: int = 0
+    edges_scanned: int = 0
+    vertices_visited: int = 0
+    search_ms: float = 0.0       # device-timed for GPU variants, wall for CPU variants
+    path_ms: float = 0.0
+    variant: str = ""
+
+    @property
+    def found(self) -> bool:
+        return self.length is not None
+
+
+def result_from_c(src, dst, r: Result, path_buf, variant) -> PathResult:
+    found = r.length >= 0
+    path = None
+    if found and r.path_len:
+        path = [int(x) for x in np.asarray(path_buf[: r.path_len]).view(np.uint32)]
+    return PathResult(src, dst, int(r.length) if found else None, path,
+                      int(r.meet) if found else None, int(r.levels), int(r.levels_bottom_up),
+                      int(r.depth_s), int(r.depth_t), int(r.edges_scanned), int(r.vertices_visited),
+                      float(r.search_ms), float(r.path_ms), variant)
+
+
+class SearchContext:
+    def __init__(self, graph, rank_lo=0, vranks=None, max_path=0, solo_threshold=0, bottom_up_div=0,
+                 max_ctas=0, watchdog_ms=0):
+        if graph.device.type != "cuda":
+            raise ValueError("SearchContext needs a CUDA graph")
+        self.graph = graph
+        self.device = graph.device
+        self.nranks = graph.nranks
+        self.rank_lo = rank_lo
+        self.vranks = len(graph.shards) if vranks is None else vranks
+        d = CtxDesc()
+        d.n, d.nranks, d.rank_lo, d.vranks = graph.n, graph.nranks, rank_lo, self.vranks
+        for i in range(self.vranks):
+            s = graph.shards[rank_lo + i]
+            d.d_row_ptr[i] = s.row_ptr.data_ptr()
+            d.d_col[i] = s.col.data_ptr() if s.col.numel() else s.row_ptr.data_ptr()
+        d.max_path = max_path or min(graph.n + 1, 1 << 24)
+        d.solo_threshold, d.bottom_up_div, d.max_ctas, d.watchdog_ms = solo_threshold, bottom_up_div, max_ctas, watchdog_ms
+        self.max_path = d.max_path
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib().bibfs_ctx_create(C.byref(self._h), C.byref(d)))
+        self._path = np.empty(self.max_path, dtype=np.uint32)
+
+    # ---- peers ---------------------------------------------------------------------------
+    def ipc_handle(self, slot=0) -> bytes:
+        buf = C.create_string_buffer(64)
+        check(lib().bibfs_ctx_ipc_handle(self._h, slot, buf))
+        return buf.raw
+
+    def attach_ipc(self, rank: int, handle: bytes) -> None:
+        with torch.cuda.device(self.device):
+            check(lib().bibfs_ctx_attach_ipc(self._h, rank, C.create_string_buffer(handle, 64)))
+
+    def attach_local(self, rank: int, owner: "SearchContext") -> None:
+        check(lib().bibfs_ctx_attach_local(self._h, rank, owner._h))
+
+    @property
+    def arena_bytes(self) -> int:
+        return int(lib().bibfs_ctx_arena_bytes(self._h))
+
+    # ---- queries -------------------------------------------------------------------------
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def launch(self, src: int, dst: int, flags: int = 0, pinned_query: torch.Tensor | None = None) -> None:
+        q = pinned_query.data_ptr() if pinned_query is not None else None
+        check(lib().bibfs_ctx_query(self._h, int(src), int(dst), q, flags, self._stream()))
+
+    def fetch(self, src: int, dst: int, want_path=True, variant="gpu") -> PathResult:
+        r = Result()
+        check(lib().bibfs_ctx_result(self._h, C.byref(r), self._path.ctypes.data if want_path else None,
+                                     self.max_path if want_path else 0, self._stream()))
+        return result_from_c(src, dst, r, self._path, variant)
+
+    def query(self, src, dst, flags=0, want_path=True, pinned_query=None, variant="gpu") -> PathResult:
+        self.launch(src, dst, flags, pinned_query)
+        return self.fetch(src, dst, want_path, variant)
+
+    def timing(self) -> tuple[float, float]:
+        a, b = C.c_float(0), C.c_float(0)
+        check(lib().bibfs_ctx_timing(self._h, C.byref(a), C.byref(b)))
+        return float(a.value), float(b.value)
+
+    def trace(self, slot=0) -> list[dict]:
+        cnt = C.c_uint32(0)
+        check(lib().bibfs_ctx_trace(self._h, slot, None, 0, C.byref(cnt)))
+        arr = (LevelTrace * max(1, cnt.value))()
+        check(lib().bibfs_ctx_trace(self._h, slot, arr, cnt.value, C.byref(cnt)))
+        return [dict(side=int(t.side), mode=int(t.mode), frontier=int(t.frontier), discovered=int(t.discovered),
+                     t_ns=int(t.t_ns), edges=int(t.edges)) for t in arr[: cnt.value]]
+
+    def reset(self) -> None:
+        check(lib().bibfs_ctx_reset(self._h, self._stream()))
+
+    def close(self) -> None:
+        if self._h:
+            lib().bibfs_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,135 @@
+// bfs.h — device-resident data model of a search context (shared by bfs_dev.cu and ctx.cu).
+//
+// One ARENA per rank holds every piece of per-query state.  All arenas have the same layout, so
+// a rank reaches a peer's bitmap / parents / queues by adding the same offsets to the peer's
+// base pointer (mapped through CUDA IPC or cudaDeviceEnablePeerAccess).
+//
+//   Ctrl                      control block: query, barriers, exchange slots, level state, result
+//   vis   u64[NW]             word w = vertices 32w..32w+31: low 32 bits "reached from source",
+//                             high 32 bits "reached from target".  NW covers ALL vertices: the
+//                             slice of the owned vertices is authoritative, the rest is a local
+//                             "already forwarded to its owner" filter.
+//   fbm   u32[2][2][NW]       frontier bitmaps for bottom-up levels (side x double buffer), replicated
+//   parent u32[2][B]          BFS-tree parent of owned vertices per side (global ids)
+//   q     u32[2][B]           append-only queue of owned vertices discovered locally, per side
+//   rq    u32[2][P][B]        (P>1) per-sender segments: owned vertices discovered by rank p
+//   path  u32[max_path]       path output (rank 0 of the context group writes it)
+//   trace LevelTrace[TRACE_CAP]
+// The frontier of a side is a WINDOW [lo,hi) of its queue plus one window per sender segment;
+// nothing is copied or compacted between levels.
+#pragma once
+#include "common.h"
+
+namespace bibfs {
+
+constexpr u32 MAXR = BIBFS_MAX_RANKS;
+constexpr u32 NO_V = 0xFFFFFFFFu;
+constexpr u32 TRACE_CAP = 32768;
+constexpr int BFS_THREADS = 1024;
+
+enum Phase : u32 { PH_TD_SOLO = 0, PH_TD_GRID = 1, PH_BU = 2, PH_DONE = 3 };
+
+struct Slot {          // one 16-byte store per peer per level
+    u32 count;         // vertices this rank discovered in the level (local + remote)
+    u32 meet;          // smallest meeting vertex it saw, NO_V if none
+    u32 rq_tail;       // cumulative entries it has appended to the receiver's segment (this side)
+    u32 edges;         // adjacency entries it inspected (low 32 bits, trace only)
+};
+
+struct LevelState {
+    u32 phase;
+    u32 side;
+    u32 levels, levels_bu;
+    u32 depth[2];
+    u32 nf[2];                 // global frontier size per side
+    u32 q_lo[2], q_hi[2];      // local queue window per side
+    u32 rq_lo[2][MAXR], rq_hi[2][MAXR];
+    u32 fbm_cur[2], fbm_valid[2];
+    u32 local_front;           // vertices this rank expands in the coming level
+    i32 length;
+    u32 meet;
+    u32 status;
+    u32 wake;                  // number of local wake-ups issued so far (gen low word)
+    u32 pad;
+    u64 xepoch;                // cross-rank barrier epoch
+};
+
+struct alignas(16) Result {
+    i32 length;
+    u32 meet;
+    u32 depth_s, depth_t;
+    u32 levels, levels_bu;
+    u32 path_len;
+    i32 status;
+    u64 edges_scanned;
+    u64 vertices_visited;
+    u64 t_begin_ns, t_end_ns;
+};
+
+struct Ctrl {
+    // written by the host (H2D copy from pinned memory) before the launch
+    alignas(128) u32 q_src;
+    u32 q_dst;
+    // local grid barrier
+    alignas(128) u32 bar_count;
+    alignas(128) u64 bar_gen;            // (launch seq << 32) | wake-ups
+    // cross-rank barrier flags: arrive[p] is written by rank p
+    alignas(128) u64 arrive[MAXR];
+    alignas(128) Slot slot[2][MAXR];     // [epoch parity][sender]
+    // accumulators, reset by the leader each level / query
+    alignas(128) u32 q_tail[2];
+    u32 sent[2][MAXR];
+    u32 new_count;
+    u32 meet_local;
+    unsigned long long edges_acc;
+    unsigned long long edges_total;
+    // persisted across launches
+    alignas(128) u64 xepoch;
+    u32 abort_flag;
+    u32 trace_count;
+    alignas(128) LevelState st;
+    alignas(128) Result res;
+};
+
+struct Layout {
+    size_t off_vis, off_fbm, off_parent, off_q, off_rq, off_path, off_trace, total;
+    u32 nw;           // bitmap words covering P*B vertices
+};
+
+inline Layout make_layout(u32 B, u32 P, u32 max_path) {
+    auto al = [](size_t x) { return (x + 511) / 512 * 512; };
+    Layout L;
+    L.nw = (u32)(((u64)B * P) / 32);
+    size_t o = al(sizeof(Ctrl));
+    L.off_vis = o;    o += al((size_t)L.nw * 8);
+    L.off_fbm = o;    o += al((size_t)L.nw * 4 * 4);
+    L.off_parent = o; o += al((size_t)B * 4 * 2);
+    L.off_q = o;      o += al((size_t)B * 4 * 2);
+    L.off_rq = o;     o += (P > 1) ? al((size_t)B * 4 * 2 * P) : 0;
+    L.off_path = o;   o += al((size_t)max_path * 4);
+    L.off_trace = o;  o += al((size_t)TRACE_CAP * sizeof(bibfs_level_trace));
+    L.total = o;
+    return L;
+}
+
+struct KParams {
+    u32 n, B, P;
+    u32 rank_lo, vranks, cpr;      // ranks hosted by this launch, CTAs per rank
+    u32 solo_threshold, bu_div, flags, max_path;
+    u32 seq;                       // launch sequence number (local barrier generation prefix)
+    u32 watchdog_ms;
+    u32 src, dst, query_in_ctrl;   // query by value, or (query_in_ctrl) read from Ctrl::q_src/q_dst
+    Layout L;
+    char* arena[MAXR];             // base of every rank's arena as seen from this device
+    const u64* row_ptr[MAXR];      // CSR shards of the hosted ranks (index = rank)
+    const u32* col[MAXR];
+};
+
+// implemented in bfs_dev.cu
+int bfs_max_ctas_per_device(bool multi, int* out);
+#if defined(__CUDACC__) || defined(BIBFS_WITH_CUDA_RUNTIME)
+int bfs_launch(const KParams& K, bool multi, cudaStream_t st);
+int path_launch(const KParams& K, cudaStream_t st);
+#endif
+
+}  // namespace bibfs

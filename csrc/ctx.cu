@@ -1,0 +1,255 @@
+// ctx.cu — search-context management: arenas, peer mapping (CUDA IPC or in-process peer access),
+// query launch, result / timing / trace read-back.
+//
+// This is the counterpart of the reference's v4 C API (v4/comp.h:8-36, v4/comp.cu:49-133:
+// cudaInitGraph / cudaInitFrontiers / cudaExpandFrontier / cudaCheckIntersect / cudaFreeGraph)
+// with three differences: state lives in a handle instead of file-static device pointers
+// (comp.cu:13-17) so several graphs / ranks can coexist in one process; a device is selected
+// explicitly (v4 never calls cudaSetDevice); and the per-level host calls are gone —
+// bibfs_ctx_query enqueues the whole search.
+#include "bfs.h"
+#include <cstring>
+#include <vector>
+
+using namespace bibfs;
+
+struct bibfs_ctx {
+    bibfs_ctx_desc d;
+    int device = 0;
+    u32 B = 0;
+    Layout L;
+    char* arena_local[MAXR] = {};   // arenas allocated here (index = hosted slot)
+    char* arena_all[MAXR] = {};     // every rank's arena as seen from this device (index = rank)
+    bool ipc_opened[MAXR] = {};
+    u32 seq = 0;
+    u32 cpr = 0;
+    bool multi = false;
+    cudaEvent_t ev[3] = {};
+    char* h_stage = nullptr;        // pinned: Result + path
+    size_t h_stage_bytes = 0;
+    u32 last_flags = 0;
+};
+
+namespace {
+struct DeviceGuard {
+    int prev = -1;
+    bool active = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) { cudaSetDevice(dev); active = true; }
+    }
+    ~DeviceGuard() { if (active) cudaSetDevice(prev); }
+};
+size_t zero_prefix(const Layout& L) { return L.off_parent; }   // Ctrl + vis + fbm
+}  // namespace
+
+extern "C" size_t bibfs_ctx_arena_bytes(const bibfs_ctx* ctx) { return ctx ? ctx->L.total : 0; }
+
+extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
+    if (!out || !desc) return fail("NULL argument");
+    if (desc->n == 0 || desc->n > 0xFFFFFF00u) return fail("n out of range");
+    if (desc->nranks < 1 || desc->nranks > MAXR) return fail("nranks must be 1..%u", MAXR);
+    if (desc->vranks < 1 || desc->rank_lo + desc->vranks > desc->nranks) return fail("bad hosted rank range");
+    for (u32 i = 0; i < desc->vranks; ++i)
+        if (!desc->d_row_ptr[i]) return fail("hosted rank %u has no CSR", desc->rank_lo + i);
+    int coop = 0, dev = 0;
+    BIBFS_CUDA_TRY(cudaGetDevice(&dev));
+    BIBFS_CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    if (!coop) return fail("device %d does not support cooperative launches", dev);
+
+    bibfs_ctx* c = new bibfs_ctx();
+    c->d = *desc;
+    c->device = dev;
+    c->multi = desc->nranks > 1;
+    c->B = bibfs_block_size(desc->n, desc->nranks);
+    if (c->d.max_path == 0) c->d.max_path = 1u << 16;
+    if (c->d.solo_threshold == 0) c->d.solo_threshold = 1024;
+    if (c->d.bottom_up_div == 0) c->d.bottom_up_div = 24;
+    if (c->d.watchdog_ms == 0) c->d.watchdog_ms = 4000;
+    c->L = make_layout(c->B, desc->nranks, c->d.max_path);
+
+    int maxc = 0, sms = 0;
+    if (bfs_max_ctas_per_device(c->multi, &maxc)) { delete c; return 1; }
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    u32 per_rank = (u32)(sms < maxc ? sms : maxc) / desc->vranks;   // one CTA per SM keeps the barrier short
+    if (desc->max_ctas && desc->max_ctas < per_rank) per_rank = desc->max_ctas;
+    if (per_rank < 1) { delete c; return fail("not enough SMs for %u hosted ranks", desc->vranks); }
+    c->cpr = per_rank;
+
+    for (u32 i = 0; i < desc->vranks; ++i) {
+        cudaError_t e = cudaMalloc((void**)&c->arena_local[i], c->L.total);
+        if (e == cudaSuccess) e = cudaMemset(c->arena_local[i], 0, zero_prefix(c->L));
+        if (e != cudaSuccess) {
+            for (u32 j = 0; j <= i; ++j) if (c->arena_local[j]) cudaFree(c->arena_local[j]);
+            delete c;
+            return fail("arena allocation of %zu bytes failed: %s", c->L.total, cudaGetErrorString(e));
+        }
+        c->arena_all[desc->rank_lo + i] = c->arena_local[i];
+    }
+    for (int k = 0; k < 3; ++k) cudaEventCreate(&c->ev[k]);
+    c->h_stage_bytes = 256 + (size_t)c->d.max_path * 4;
+    if (cudaHostAlloc((void**)&c->h_stage, c->h_stage_bytes, cudaHostAllocDefault) != cudaSuccess) {
+        bibfs_ctx_destroy(c);
+        return fail("pinned staging allocation failed");
+    }
+    BIBFS_CUDA_TRY(cudaDeviceSynchronize());
+    *out = c;
+    return 0;
+}
+
+extern "C" int bibfs_ctx_destroy(bibfs_ctx* c) {
+    if (!c) return 0;
+    DeviceGuard g(c->device);
+    cudaDeviceSynchronize();
+    for (u32 r = 0; r < MAXR; ++r)
+        if (c->ipc_opened[r] && c->arena_all[r]) cudaIpcCloseMemHandle(c->arena_all[r]);
+    for (u32 i = 0; i < MAXR; ++i)
+        if (c->arena_local[i]) cudaFree(c->arena_local[i]);
+    for (int k = 0; k < 3; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    delete c;
+    return 0;
+}
+
+extern "C" int bibfs_ctx_ipc_handle(bibfs_ctx* c, uint32_t i, void* handle64) {
+    if (!c || i >= c->d.vranks) return fail("bad hosted slot");
+    DeviceGuard g(c->device);
+    cudaIpcMemHandle_t h;
+    BIBFS_CUDA_TRY(cudaIpcGetMemHandle(&h, c->arena_local[i]));
+    static_assert(sizeof(h) == 64, "IPC handle size");
+    memcpy(handle64, &h, 64);
+    return 0;
+}
+
+extern "C" int bibfs_ctx_attach_ipc(bibfs_ctx* c, uint32_t rank, const void* handle64) {
+    if (!c || rank >= c->d.nranks) return fail("bad rank");
+    if (c->arena_all[rank]) return fail("rank %u is already attached", rank);
+    DeviceGuard g(c->device);
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    void* p = nullptr;
+    BIBFS_CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->arena_all[rank] = (char*)p;
+    c->ipc_opened[rank] = true;
+    return 0;
+}
+
+extern "C" int bibfs_ctx_attach_local(bibfs_ctx* c, uint32_t rank, bibfs_ctx* owner) {
+    if (!c || !owner || rank >= c->d.nranks) return fail("bad argument");
+    if (rank < owner->d.rank_lo || rank >= owner->d.rank_lo + owner->d.vranks) return fail("owner does not host rank %u", rank);
+    if (owner->device != c->device) {
+        DeviceGuard g(c->device);
+        int can = 0;
+        BIBFS_CUDA_TRY(cudaDeviceCanAccessPeer(&can, c->device, owner->device));
+        if (!can) return fail("device %d cannot access device %d", c->device, owner->device);
+        cudaError_t e = cudaDeviceEnablePeerAccess(owner->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail("enable peer access: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+    }
+    c->arena_all[rank] = owner->arena_local[rank - owner->d.rank_lo];
+    return 0;
+}
+
+extern "C" int bibfs_ctx_reset(bibfs_ctx* c, void* stream) {
+    if (!c) return fail("NULL ctx");
+    DeviceGuard g(c->device);
+    for (u32 i = 0; i < c->d.vranks; ++i)
+        BIBFS_CUDA_TRY(cudaMemsetAsync(c->arena_local[i], 0, zero_prefix(c->L), (cudaStream_t)stream));
+    return 0;
+}
+
+static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl, u32 flags) {
+    memset(&K, 0, sizeof(K));
+    K.n = c->d.n; K.B = c->B; K.P = c->d.nranks;
+    K.rank_lo = c->d.rank_lo; K.vranks = c->d.vranks; K.cpr = c->cpr;
+    K.solo_threshold = c->d.solo_threshold;
+    K.bu_div = c->d.bottom_up_div;
+    K.flags = flags;
+    K.max_path = c->d.max_path;
+    K.seq = ++c->seq;
+    K.watchdog_ms = c->d.watchdog_ms;
+    K.src = src; K.dst = dst; K.query_in_ctrl = in_ctrl ? 1u : 0u;
+    K.L = c->L;
+    for (u32 r = 0; r < MAXR; ++r) K.arena[r] = c->arena_all[r];
+    for (u32 i = 0; i < c->d.vranks; ++i) {
+        K.row_ptr[c->d.rank_lo + i] = c->d.d_row_ptr[i];
+        K.col[c->d.rank_lo + i] = c->d.d_col[i];
+    }
+}
+
+extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const uint32_t* h_query_pinned,
+                               uint32_t flags, void* stream) {
+    if (!c) return fail("NULL ctx");
+    for (u32 r = 0; r < c->d.nranks; ++r)
+        if (!c->arena_all[r]) return fail("rank %u is not attached", r);
+    DeviceGuard g(c->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (h_query_pinned)
+        for (u32 i = 0; i < c->d.vranks; ++i)
+            BIBFS_CUDA_TRY(cudaMemcpyAsync(c->arena_local[i] + offsetof(Ctrl, q_src), h_query_pinned, 8, cudaMemcpyHostToDevice, st));
+    KParams K;
+    fill_params(c, K, src, dst, h_query_pinned != nullptr, flags);
+    c->last_flags = flags;
+    BIBFS_CUDA_TRY(cudaEventRecord(c->ev[0], st));
+    if (bfs_launch(K, c->multi, st)) return 1;
+    BIBFS_CUDA_TRY(cudaEventRecord(c->ev[1], st));
+    if (!(flags & BIBFS_F_NO_PATH))
+        if (path_launch(K, st)) return 1;
+    BIBFS_CUDA_TRY(cudaEventRecord(c->ev[2], st));
+    return 0;
+}
+
+extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path, uint32_t path_cap, void* stream) {
+    if (!c || !res) return fail("NULL argument");
+    DeviceGuard g(c->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    Result* hr = reinterpret_cast<Result*>(c->h_stage);
+    u32* hp = reinterpret_cast<u32*>(c->h_stage + 256);
+    BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, st));
+    BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
+    *res = bibfs_result();
+    res->length = hr->length;
+    res->meet = hr->meet;
+    res->depth_s = hr->depth_s;
+    res->depth_t = hr->depth_t;
+    res->levels = hr->levels;
+    res->levels_bottom_up = hr->levels_bu;
+    res->status = hr->status;
+    res->edges_scanned = hr->edges_scanned;
+    res->vertices_visited = hr->vertices_visited;
+    res->path_len = 0;
+    float a = 0, b = 0;
+    if (cudaEventElapsedTime(&a, c->ev[0], c->ev[1]) == cudaSuccess) res->search_ms = a;
+    if (cudaEventElapsedTime(&b, c->ev[1], c->ev[2]) == cudaSuccess) res->path_ms = b;
+    cudaGetLastError();
+    if (hr->status == 1) return fail("search aborted by the device watchdog (a rank did not arrive); reset the context");
+    if (hr->status == 2) return fail("src/dst out of range (n=%u)", c->d.n);
+    if (path && hr->path_len && hr->path_len <= path_cap) {
+        BIBFS_CUDA_TRY(cudaMemcpyAsync(hp, c->arena_local[0] + c->L.off_path, (size_t)hr->path_len * 4, cudaMemcpyDeviceToHost, st));
+        BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
+        memcpy(path, hp, (size_t)hr->path_len * 4);
+        res->path_len = hr->path_len;
+    }
+    return 0;
+}
+
+extern "C" int bibfs_ctx_timing(bibfs_ctx* c, float* search_ms, float* path_ms) {
+    if (!c) return fail("NULL ctx");
+    DeviceGuard g(c->device);
+    if (search_ms) BIBFS_CUDA_TRY(cudaEventElapsedTime(search_ms, c->ev[0], c->ev[1]));
+    if (path_ms) BIBFS_CUDA_TRY(cudaEventElapsedTime(path_ms, c->ev[1], c->ev[2]));
+    return 0;
+}
+
+extern "C" int bibfs_ctx_trace(bibfs_ctx* c, uint32_t i, bibfs_level_trace* out, uint32_t cap, uint32_t* count) {
+    if (!c || i >= c->d.vranks || !count) return fail("bad argument");
+    DeviceGuard g(c->device);
+    u32 k = 0;
+    BIBFS_CUDA_TRY(cudaMemcpy(&k, c->arena_local[i] + offsetof(Ctrl, trace_count), 4, cudaMemcpyDeviceToHost));
+    if (k > TRACE_CAP) k = TRACE_CAP;
+    *count = k;
+    if (out && cap) {
+        const u32 m = k < cap ? k : cap;
+        if (m) BIBFS_CUDA_TRY(cudaMemcpy(out, c->arena_local[i] + c->L.off_trace, (size_t)m * sizeof(bibfs_level_trace), cudaMemcpyDeviceToHost));
+    }
+    return 0;
+}
