@@ -7,7 +7,7 @@
 NVCC      ?= /usr/local/cuda/bin/nvcc
 CXX       ?= g++
 ARCH      := -gencode arch=compute_100a,code=sm_100a
-NVCCFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O3,-Wall,-Wno-unknown-pragmas \
+NVCCFLAGS := $(EXTRA) $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O3,-Wall,-Wno-unknown-pragmas \
              -Xptxas -v --expt-relaxed-constexpr -Iinclude
 CXXFLAGS  := -O3 -std=c++17 -fPIC -Wall -Wno-unknown-pragmas -ffp-contract=off -Iinclude -pthread
 BUILD     := build

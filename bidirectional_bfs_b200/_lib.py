@@ -55,7 +55,7 @@ class CtxDesc(C.Structure):
 class LevelTrace(C.Structure):
     _fields_ = [
         ("side", C.c_uint32), ("mode", C.c_uint32), ("frontier", C.c_uint32), ("discovered", C.c_uint32),
-        ("t_ns", C.c_uint64), ("edges", C.c_uint64),
+        ("t_ns", C.c_uint64), ("edges", C.c_uint64), ("t_expand_ns", C.c_uint64),
     ]
 
 

@@ -118,7 +118,7 @@ class SearchContext:
         arr = (LevelTrace * max(1, cnt.value))()
         check(lib().bibfs_ctx_trace(self._h, slot, arr, cnt.value, C.byref(cnt)))
         return [dict(side=int(t.side), mode=int(t.mode), frontier=int(t.frontier), discovered=int(t.discovered),
-                     t_ns=int(t.t_ns), edges=int(t.edges)) for t in arr[: cnt.value]]
+                     t_ns=int(t.t_ns), edges=int(t.edges), t_expand_ns=int(t.t_expand_ns)) for t in arr[: cnt.value]]
 
     def reset(self) -> None:
         check(lib().bibfs_ctx_reset(self._h, self._stream()))

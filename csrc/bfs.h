@@ -27,7 +27,7 @@ constexpr u32 NO_V = 0xFFFFFFFFu;
 constexpr u32 TRACE_CAP = 32768;
 constexpr int BFS_THREADS = 1024;
 
-enum Phase : u32 { PH_TD_SOLO = 0, PH_TD_GRID = 1, PH_BU = 2, PH_DONE = 3 };
+enum Phase : u32 { PH_TD_SOLO = 0, PH_TD_GRID = 1, PH_BU = 2, PH_DONE = 3, PH_TD_HUB = 4 };
 
 struct Slot {          // one 16-byte store per peer per level
     u32 count;         // vertices this rank discovered in the level (local + remote)
@@ -46,6 +46,8 @@ struct LevelState {
     u32 rq_lo[2][MAXR], rq_hi[2][MAXR];
     u32 fbm_cur[2], fbm_valid[2];
     u32 local_front;           // vertices this rank expands in the coming level
+    u32 hub_entries, hub_chunks; // hub phase work (PH_TD_HUB)
+    u32 prev_phase;            // phase that produced the hub list (solo or grid)
     i32 length;
     u32 meet;
     u32 status;
@@ -66,6 +68,24 @@ struct alignas(16) Result {
     u64 t_begin_ns, t_end_ns;
 };
 
+// level accumulators: one copy in Ctrl (grid mode), one in shared memory (solo mode)
+struct Acc {
+    u32 q_tail[2];     // append cursor of the local queue per side (persists through the query)
+    u32 new_count;     // vertices discovered in the current level
+    u32 meet_local;    // smallest meeting vertex seen in the current level
+    unsigned long long edges;   // adjacency entries inspected in the current level
+};
+
+struct HubEntry {      // a frontier vertex whose row is expanded by the whole grid
+    u32 u;
+    u32 nchunks;
+    u64 r0, r1;
+    u64 chunk_base;    // first global chunk id of this row
+};
+constexpr u32 HUB_ROW = 1024;     // rows at least this long are deferred to the hub phase
+constexpr u32 HUB_CHUNK = 512;    // adjacency entries per hub work item (2 KB: one bulk copy)
+constexpr u32 HUB_CAP = 16384;    // hub entries per level per rank (overflow: expanded in place)
+
 struct Ctrl {
     // written by the host (H2D copy from pinned memory) before the launch
     alignas(128) u32 q_src;
@@ -77,11 +97,9 @@ struct Ctrl {
     alignas(128) u64 arrive[MAXR];
     alignas(128) Slot slot[2][MAXR];     // [epoch parity][sender]
     // accumulators, reset by the leader each level / query
-    alignas(128) u32 q_tail[2];
+    alignas(128) Acc acc;
+    unsigned long long hub_packed;       // (entries << 40) | chunks, appended atomically
     u32 sent[2][MAXR];
-    u32 new_count;
-    u32 meet_local;
-    unsigned long long edges_acc;
     unsigned long long edges_total;
     // persisted across launches
     alignas(128) u64 xepoch;
@@ -92,7 +110,7 @@ struct Ctrl {
 };
 
 struct Layout {
-    size_t off_vis, off_fbm, off_parent, off_q, off_rq, off_path, off_trace, total;
+    size_t off_vis, off_fbm, off_parent, off_q, off_rq, off_path, off_trace, off_hub, total;
     u32 nw;           // bitmap words covering P*B vertices
 };
 
@@ -108,6 +126,7 @@ inline Layout make_layout(u32 B, u32 P, u32 max_path) {
     L.off_rq = o;     o += (P > 1) ? al((size_t)B * 4 * 2 * P) : 0;
     L.off_path = o;   o += al((size_t)max_path * 4);
     L.off_trace = o;  o += al((size_t)TRACE_CAP * sizeof(bibfs_level_trace));
+    L.off_hub = o;    o += al((size_t)HUB_CAP * sizeof(HubEntry));
     L.total = o;
     return L;
 }

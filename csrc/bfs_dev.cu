@@ -9,7 +9,9 @@
 // v4/mpi_bas.cpp:79-132).  What replaces what:
 //
 //   expand_frontier(_kernel)  (v3:13-43, comp.cu:20-38; one thread per vertex over all N)
-//        -> expand_td: frontier-proportional work, warp-cooperative neighbour gathering,
+//        -> expand_td: frontier-proportional work, warp-cooperative neighbour gathering with
+//           batched independent loads/atomics; rows >= HUB_ROW are deferred to a hub phase in
+//           which the whole grid splits them into 2 KB chunks;
 //           expand_bu: bottom-up sweep over unvisited owned vertices against a frontier bitmap
 //   check_intersect(_kernel) + host O(N) scan  (v3:45-62, comp.cu:40-47, mpi_bas.cpp:81-87)
 //        -> fused: the visited bitmap word carries both sides' bits, so the atomic OR that claims
@@ -25,9 +27,10 @@
 //           rank into an error instead of a hang.
 //
 // Scheduling: the side with the smaller (global) frontier is expanded, ties to the source side
-// (v1/main-v1.cpp:51, mpi_bas.cpp:90-92).  Small local frontiers are expanded by CTA 0 alone with
-// __syncthreads between levels ("solo"); the other CTAs sleep on the generation word.  Large
-// ones wake the whole grid; very large ones switch to bottom-up (Beamer et al., SC'12).
+// (v1/main-v1.cpp:51, mpi_bas.cpp:90-92).  Small local frontiers are expanded by CTA 0 alone
+// ("solo"): level state and accumulators live in shared memory and levels are separated by
+// __syncthreads only, while the other CTAs sleep on the generation word.  Large ones wake the
+// whole grid; very large ones switch to bottom-up (Beamer et al., SC'12).
 //
 // Exactness: levels are always completed; the first level in which any discovered vertex is
 // already marked by the other side ends the search and length = depth_s + depth_t (all hits of
@@ -40,15 +43,51 @@
 
 namespace bibfs {
 
+#ifdef BIBFS_FINE_TRACE
+__device__ u64 g_dbg[256][8];
+__device__ u64 g_dbg2[256][8];
+__device__ u32 g_dbg_level;
+#define DBG_STAMP(slot, dep)                                                                     \
+    do {                                                                                         \
+        if (blockIdx.x == 0 && threadIdx.x == 0 && g_dbg_level < 256) {                          \
+            u64 _t;                                                                              \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t) : "l"((u64)(dep)) : "memory"); \
+            g_dbg[g_dbg_level][slot] = _t;                                                       \
+        }                                                                                        \
+    } while (0)
+#define DBG_STAMP2(slot, dep)                                                                    \
+    do {                                                                                         \
+        if (blockIdx.x == 0 && threadIdx.x == 0 && g_dbg_level > 0 && g_dbg_level <= 256) {       \
+            u64 _t;                                                                              \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t) : "l"((u64)(dep)) : "memory"); \
+            g_dbg2[g_dbg_level - 1][slot] = _t;                                                  \
+        }                                                                                        \
+    } while (0)
+#else
+#define DBG_STAMP(slot, dep) do { } while (0)
+#define DBG_STAMP2(slot, dep) do { } while (0)
+#endif
+
 namespace {
 
 constexpr u32 FULL = 0xffffffffu;
 constexpr u32 BIG_ROW = 64;          // rows at least this long are strip-mined by the whole warp
+constexpr int UNR = 4;               // independent edges in flight per lane
+constexpr u32 WPC = BFS_THREADS / 32;
+constexpr u32 SOLO_CAP = 2048;       // entries of the shared-memory queue mirror per side
+constexpr u32 FILTER_MIN = 4096;     // frontiers at least this large pre-check the visited word
 
 struct Env {
     u32 me, lo, P, B, n, nw;
     u32 cta, cpr;
     Ctrl* C;
+    Acc* A;            // accumulators in use: &C->acc (grid) or the shared-memory copy (solo)
+    Acc* sA;           // the shared-memory copy
+    bool solo;
+    u32* sq;           // solo mode: shared-memory mirror of the entries appended in this level (else null)
+    u32 sq_base;       // queue index of sq[0]
+    u32* s_hub;        // solo mode: shared flag "a hub row was deferred" (else null)
+    bool filter;       // read the visited word before the atomic (pays off on large frontiers only)
     u64* vis;
     u32* parent[2];
     u32* q[2];
@@ -73,11 +112,31 @@ __device__ __forceinline__ u32* rq_of(const KParams& K, u32 r, u32 side, u32 sen
 __device__ __forceinline__ bibfs_level_trace* trace_of(const KParams& K, u32 r) {
     return reinterpret_cast<bibfs_level_trace*>(K.arena[r] + K.L.off_trace);
 }
+__device__ __forceinline__ HubEntry* hub_of(const KParams& K, u32 r) {
+    return reinterpret_cast<HubEntry*>(K.arena[r] + K.L.off_hub);
+}
 
 __device__ __forceinline__ u32 lanemask_lt() {
     u32 m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
     return m;
+}
+
+// accumulator updates: shared-window atomics in solo mode, global (L2) atomics in grid mode
+__device__ __forceinline__ u32 acc_take_slots(const Env& E, u32 side, u32 n) {
+    return E.solo ? ptx::atoms_add(&E.sA->q_tail[side], n) : atomicAdd(&E.A->q_tail[side], n);
+}
+__device__ __forceinline__ void acc_note_meet(const Env& E, u32 v) {
+    if (E.solo) ptx::reds_min(&E.sA->meet_local, v); else atomicMin(&E.A->meet_local, v);
+}
+__device__ __forceinline__ void acc_flush(const Env& E, u32 cnt, u64 edges) {
+    if (E.solo) {
+        if (cnt) ptx::reds_add(&E.sA->new_count, cnt);
+        if (edges) ptx::reds_add64(&E.sA->edges, edges);
+    } else {
+        if (cnt) atomicAdd(&E.A->new_count, cnt);
+        if (edges) atomicAdd(&E.A->edges, (unsigned long long)edges);
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -90,8 +149,8 @@ __device__ __forceinline__ bool expired(Ctrl* C, u64 deadline) {
 __device__ bool wait_gen(Ctrl* C, u64 want, u64 deadline) {
     u32 spins = 0;
     while (ptx::ld_acquire_gpu(&C->bar_gen) < want) {
-        if (++spins > 32) {
-            ptx::nanosleep(40);
+        if (++spins > 64) {
+            ptx::nanosleep(32);
             if ((spins & 255u) == 0 && expired(C, deadline)) return false;
         }
     }
@@ -114,10 +173,19 @@ __device__ bool wait_arrive(Ctrl* C, u32 p, u64 want, u64 deadline) {
     return true;
 }
 
+// accumulators are updated with atomics that live in L2: read them around the L1
+__device__ __forceinline__ void pull_acc(Acc& dst, const Acc* src) {
+    dst.q_tail[0] = ptx::ld_relaxed_gpu(&src->q_tail[0]);
+    dst.q_tail[1] = ptx::ld_relaxed_gpu(&src->q_tail[1]);
+    dst.new_count = ptx::ld_relaxed_gpu(&src->new_count);
+    dst.meet_local = ptx::ld_relaxed_gpu(&src->meet_local);
+    dst.edges = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&src->edges));
+}
+
 // ------------------------------------------------------------------------------------------
 // leader side: decisions
 // ------------------------------------------------------------------------------------------
-__device__ void decide_next(const KParams& K, LevelState& G) {
+__device__ __noinline__ void decide_next(const KParams& K, LevelState& G) {
     const u32 side = G.nf[0] <= G.nf[1] ? 0u : 1u;   // ties -> source side, like v1
     G.side = side;
     if (G.nf[side] == 0) {                            // the side to expand is exhausted: no path
@@ -136,7 +204,7 @@ __device__ void decide_next(const KParams& K, LevelState& G) {
     else G.phase = PH_TD_GRID;
 }
 
-__device__ void write_result(const KParams& K, Ctrl* C, const LevelState& G) {
+__device__ __noinline__ void write_result(const KParams& K, Ctrl* C, const LevelState& G) {
     Result& R = C->res;
     R.length = G.length;
     R.meet = G.meet;
@@ -151,18 +219,11 @@ __device__ void write_result(const KParams& K, Ctrl* C, const LevelState& G) {
     C->xepoch = G.xepoch;
 }
 
-// publish a new generation: everything the leader warp wrote becomes visible to the other CTAs
-__device__ __forceinline__ void bump_gen(const KParams& K, Ctrl* C, LevelState& G) {
-    G.wake += 1;
-    __threadfence();
-    ptx::st_release_gpu(&C->bar_gen, ((u64)K.seq << 32) | G.wake);
-}
-
 // Cross-rank handshake executed by the leader warp (lanes 0..P-1 each talk to one peer).
 // Writes `mine` into slot[parity][me] of every peer, raises arrive[me] there, waits until every
 // peer has done the same here and returns the peer's slot in `got`.  Returns false on timeout.
 template <bool MULTI>
-__device__ bool cross_exchange(const KParams& K, const Env& E, LevelState& G, const Slot mine_for_lane, Slot& got, u64 deadline) {
+__device__ __noinline__ bool cross_exchange(const KParams& K, const Env& E, LevelState& G, const Slot mine_for_lane, Slot& got, u64 deadline) {
     const u32 lane = threadIdx.x & 31;
     got = mine_for_lane;
     if (!MULTI) return true;
@@ -184,32 +245,46 @@ __device__ bool cross_exchange(const KParams& K, const Env& E, LevelState& G, co
         got.count = 0; got.meet = NO_V; got.rq_tail = 0; got.edges = 0;
     }
     ok = __all_sync(FULL, ok);
-    if (threadIdx.x == 0) G.xepoch = epoch;
+    if (lane == 0) G.xepoch = epoch;
     __syncwarp();
     return ok;
 }
 
 enum SyncKind : int { SYNC_LEVEL = 0, SYNC_LOCAL = 1, SYNC_CROSS = 2 };
 
-// Work of the leader warp (warp 0 of CTA 0 of the rank) at a synchronisation point, after every
-// participating local CTA has arrived.  G is the rank's LevelState in global memory.
+// Everything the leader warp (warp 0 of CTA 0 of the rank) does at a synchronisation point, after
+// all participating local CTAs have arrived.  G / A are the leader's shared-memory level state and
+// accumulators (pulled from global memory first when the level ran on the whole grid).
+// Returns false if the query was aborted.  On return G.phase says what happens next.
 template <bool MULTI>
-__device__ bool leader_sync(const KParams& K, const Env& E, int kind, bool solo, u32 level_mode, u64 deadline) {
+__device__ __noinline__ bool leader_sync(const KParams& K, const Env& E, LevelState& G, Acc& A, int kind, u32 level_mode, u64 deadline,
+                            bool maybe_hubs) {
     Ctrl* C = E.C;
-    LevelState& G = C->st;
     const u32 lane = threadIdx.x & 31;
-    if (lane == 0) ptx::st_relaxed_gpu(&C->bar_count, 0u);
-    if (kind == SYNC_LOCAL) {
-        if (lane == 0 && !solo) bump_gen(K, C, G);
-        __syncwarp();
-        return true;
-    }
+    if (kind == SYNC_LOCAL) return true;
     const u32 side = G.side;
+    const u64 t_sync0 = (K.flags & BIBFS_F_TRACE) ? ptx::globaltimer_ns() : 0ull;
+    DBG_STAMP2(0, side);
+    // hub rows found during the level?  Then the level is not over: the grid expands them first.
+    if (kind == SYNC_LEVEL && maybe_hubs && (level_mode == PH_TD_SOLO || level_mode == PH_TD_GRID)) {
+        const u64 hp = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&C->hub_packed));
+        if (hp) {
+            if (lane == 0) {
+                G.hub_entries = (u32)(hp >> 40);
+                G.hub_chunks = (u32)(hp & 0xFFFFFFFFFFull);
+                G.prev_phase = level_mode;
+                G.phase = PH_TD_HUB;
+                C->hub_packed = 0;
+            }
+            __syncwarp();
+            return true;
+        }
+    }
     Slot mine;
-    mine.count = ptx::ld_relaxed_gpu(&C->new_count);
-    mine.meet = ptx::ld_relaxed_gpu(&C->meet_local);
+    mine.count = A.new_count;
+    mine.meet = A.meet_local;
     mine.rq_tail = (MULTI && lane < K.P) ? ptx::ld_relaxed_gpu(&C->sent[side][lane]) : 0u;
-    const u64 my_edges = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&C->edges_acc));
+    const u64 my_edges = A.edges;
     mine.edges = (u32)my_edges;
     Slot got;
     const bool ok = cross_exchange<MULTI>(K, E, G, mine, got, deadline);
@@ -219,16 +294,11 @@ __device__ bool leader_sync(const KParams& K, const Env& E, int kind, bool solo,
             atomicExch(&C->abort_flag, 1u);
             G.status = 1; G.length = -1; G.phase = PH_DONE;
             write_result(K, C, G);
-            bump_gen(K, C, G);
         }
         __syncwarp();
         return false;
     }
-    if (kind == SYNC_CROSS) {
-        if (lane == 0 && !solo) bump_gen(K, C, G);
-        __syncwarp();
-        return true;
-    }
+    if (kind == SYNC_CROSS) return true;
     // ---- SYNC_LEVEL: reduce the slots, advance the level state, choose the next level
     u32 total = got.count, meetmin = got.meet;
     u64 etot = got.edges;
@@ -243,26 +313,28 @@ __device__ bool leader_sync(const KParams& K, const Env& E, int kind, bool solo,
         G.rq_hi[side][lane] = got.rq_tail;
     }
     __syncwarp();
+    DBG_STAMP2(1, total + meetmin);
     if (lane == 0) {
         const u32 expanded = G.nf[side];
+        const u32 mode = (level_mode == PH_TD_HUB) ? G.prev_phase : level_mode;
         G.nf[side] = total;
         G.depth[side] += 1;
         G.levels += 1;
-        if (level_mode == PH_BU) { G.levels_bu += 1; G.fbm_cur[side] ^= 1u; G.fbm_valid[side] = 1; }
+        if (mode == PH_BU) { G.levels_bu += 1; G.fbm_cur[side] ^= 1u; G.fbm_valid[side] = 1; }
         else G.fbm_valid[side] = 0;
         G.q_lo[side] = G.q_hi[side];
-        G.q_hi[side] = ptx::ld_relaxed_gpu(&C->q_tail[side]);
+        G.q_hi[side] = A.q_tail[side];
         C->edges_total += etot;   // all ranks' adjacency entries of this level
         C->res.vertices_visited += total;
         if ((K.flags & BIBFS_F_TRACE) && C->trace_count < TRACE_CAP) {
             bibfs_level_trace& T = trace_of(K, E.me)[C->trace_count++];
-            T.side = side; T.mode = level_mode; T.frontier = expanded; T.discovered = total;
-            T.t_ns = ptx::globaltimer_ns(); T.edges = my_edges;
+            T.side = side; T.mode = mode | (level_mode == PH_TD_HUB ? 8u : 0u); T.frontier = expanded; T.discovered = total;
+            T.t_ns = ptx::globaltimer_ns(); T.edges = my_edges; T.t_expand_ns = t_sync0;
         }
         // reset the per-level accumulators
-        C->new_count = 0;
-        C->meet_local = NO_V;
-        C->edges_acc = 0;
+        A.new_count = 0;
+        A.meet_local = NO_V;
+        A.edges = 0;
         if (meetmin != NO_V) {
             G.length = (i32)(G.depth[0] + G.depth[1]);
             G.meet = meetmin;
@@ -271,25 +343,25 @@ __device__ bool leader_sync(const KParams& K, const Env& E, int kind, bool solo,
             decide_next(K, G);
         }
         if (G.phase == PH_DONE) write_result(K, C, G);
-        if (!solo || G.phase != PH_TD_SOLO) bump_gen(K, C, G);
-        else __threadfence();
     }
+    DBG_STAMP2(2, G.phase);
     __syncwarp();
     return true;
 }
 
-// Query start, leader warp of each rank.
+// Query start, leader warp of each rank.  Works on the shared-memory state G / accumulators A.
 template <bool MULTI>
-__device__ bool leader_init(const KParams& K, const Env& E, u64 deadline) {
+__device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelState& G, Acc& A, u64 deadline) {
     Ctrl* C = E.C;
-    LevelState& G = C->st;
     const u32 lane = threadIdx.x & 31;
     const u32 src = K.query_in_ctrl ? C->q_src : K.src, dst = K.query_in_ctrl ? C->q_dst : K.dst;
     if (lane == 0) {
         C->bar_count = 0;
-        C->q_tail[0] = 0; C->q_tail[1] = 0;
+        A.q_tail[0] = 0; A.q_tail[1] = 0;
+        A.new_count = 0; A.meet_local = NO_V; A.edges = 0;
+        C->hub_packed = 0;
         for (u32 p = 0; p < MAXR; ++p) { C->sent[0][p] = 0; C->sent[1][p] = 0; }
-        C->new_count = 0; C->meet_local = NO_V; C->edges_acc = 0; C->edges_total = 0;
+        C->edges_total = 0;
         C->trace_count = 0;
         C->res.vertices_visited = 2;
         C->res.t_begin_ns = ptx::globaltimer_ns();
@@ -301,7 +373,8 @@ __device__ bool leader_init(const KParams& K, const Env& E, u64 deadline) {
             G.fbm_cur[s] = 0; G.fbm_valid[s] = 0;
             for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
         }
-        G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 0;
+        G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 0; G.pad = 0;
+        G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
         G.xepoch = C->xepoch;
         const bool bad = src >= K.n || dst >= K.n;
         if (bad) { G.status = 2; G.phase = PH_DONE; }
@@ -311,12 +384,12 @@ __device__ bool leader_init(const KParams& K, const Env& E, u64 deadline) {
             if (src >= E.lo && src < hi) {
                 atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[src >> 5]), 1ull << (src & 31));
                 E.q[0][0] = src; E.parent[0][src - E.lo] = NO_V;
-                C->q_tail[0] = 1; G.q_hi[0] = 1;
+                A.q_tail[0] = 1; G.q_hi[0] = 1;
             }
             if (dst >= E.lo && dst < hi) {
                 atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[dst >> 5]), 1ull << ((dst & 31) + 32));
                 E.q[1][0] = dst; E.parent[1][dst - E.lo] = NO_V;
-                C->q_tail[1] = 1; G.q_hi[1] = 1;
+                A.q_tail[1] = 1; G.q_hi[1] = 1;
             }
         }
     }
@@ -333,8 +406,6 @@ __device__ bool leader_init(const KParams& K, const Env& E, u64 deadline) {
         if (!ok) { atomicExch(&C->abort_flag, 1u); G.status = 1; G.phase = PH_DONE; }
         if (G.phase != PH_DONE) decide_next(K, G);
         if (G.phase == PH_DONE) write_result(K, C, G);
-        if (G.phase != PH_TD_SOLO) bump_gen(K, C, G);
-        else __threadfence();
     }
     __syncwarp();
     return ok;
@@ -344,9 +415,10 @@ __device__ bool leader_init(const KParams& K, const Env& E, u64 deadline) {
 // frontier access: flat index -> vertex, across the local window and the per-sender windows
 // ------------------------------------------------------------------------------------------
 template <bool MULTI>
-__device__ __forceinline__ u32 fetch_frontier(const KParams& K, const Env& E, const LevelState& st, u32 side, u32 i) {
+__device__ __forceinline__ u32 fetch_frontier(const KParams& K, const Env& E, const LevelState& st, u32 side, u32 i,
+                                              const u32* smem_front = nullptr) {
     const u32 nq = st.q_hi[side] - st.q_lo[side];
-    if (!MULTI || i < nq) return __ldcg(E.q[side] + st.q_lo[side] + i);
+    if (!MULTI || i < nq) return smem_front ? smem_front[i] : __ldcg(E.q[side] + st.q_lo[side] + i);
     i -= nq;
     u32 v = 0;
 #pragma unroll 1
@@ -359,109 +431,224 @@ __device__ __forceinline__ u32 fetch_frontier(const KParams& K, const Env& E, co
 }
 
 // ------------------------------------------------------------------------------------------
-// discovery: claim v for `side`, record its parent, enqueue it at its owner, test the meet
+// discovery, split in two so that several edges per lane can be in flight:
+//   claim    test-and-set the visited bit of v for `side` (the atomic also returns the other
+//            side's bit: the meet test costs nothing extra, even across NVLink)
+//   enqueue  record the parent and append v to its owner's queue, warp-aggregated
 // ------------------------------------------------------------------------------------------
+struct Claim {
+    u32 dest;
+    bool isnew, meet;
+};
+
 template <bool MULTI>
-__device__ __forceinline__ void visit(const KParams& K, const Env& E, u32 side, bool valid, u32 u, u32 v, u32& cnt) {
-    const u32 lane = threadIdx.x & 31;
-    bool isnew = false, meet = false;
-    u32 dest = E.me;
+__device__ __forceinline__ Claim claim(const KParams& K, const Env& E, u32 side, bool valid, u32 v, u64 seen_word) {
+    Claim c;
+    c.dest = E.me; c.isnew = false; c.meet = false;
     if (valid) {
         const u32 w = v >> 5;
         const u64 bit = 1ull << ((v & 31u) + 32u * side);
         const u64 obit = 1ull << ((v & 31u) + 32u * (1u - side));
-        const u64 cur = E.vis[w];                       // filter only; may be stale
-        if (!(cur & bit)) {
+        if (!(seen_word & bit)) {
             u64 old = ptx::atom_or_gpu(&E.vis[w], bit);
             if (!(old & bit)) {
-                isnew = true;
+                c.isnew = true;
                 if (MULTI) {
-                    dest = v / K.B;
-                    if (dest != E.me) {
+                    c.dest = v / K.B;
+                    if (c.dest != E.me) {
                         // first time THIS rank sees v: ask the owner.  One round trip returns both
                         // "new for this side" and "already reached by the other side".
-                        old = ptx::atom_or_sys(vis_of(K, dest) + w, bit);
-                        isnew = !(old & bit);
+                        old = ptx::atom_or_sys(vis_of(K, c.dest) + w, bit);
+                        c.isnew = !(old & bit);
                     }
                 }
-                meet = isnew && (old & obit);
+                c.meet = c.isnew && (old & obit);
             }
         }
     }
+    return c;
+}
+
+template <bool MULTI>
+__device__ __forceinline__ void enqueue(const KParams& K, const Env& E, u32 side, const Claim c, u32 u, u32 v, u32& cnt) {
+    const u32 lane = threadIdx.x & 31;
     if (!MULTI) {
-        const u32 m = __ballot_sync(FULL, isnew);
+        const u32 m = __ballot_sync(FULL, c.isnew);
         if (m) {
             const u32 leader = __ffs(m) - 1;
             u32 base = 0;
-            if (lane == leader) base = atomicAdd(&E.C->q_tail[side], (u32)__popc(m));
+            if (lane == leader) base = acc_take_slots(E, side, (u32)__popc(m));
             base = __shfl_sync(FULL, base, leader);
-            if (isnew) {
-                E.q[side][base + __popc(m & lanemask_lt())] = v;
+            if (c.isnew) {
+                const u32 slot = base + __popc(m & lanemask_lt());
+                E.q[side][slot] = v;
                 E.parent[side][v - E.lo] = u;
+                if (E.sq && slot - E.sq_base < SOLO_CAP) E.sq[slot - E.sq_base] = v;
+                ptx::prefetch_l2(E.row_ptr + (v - E.lo));
             }
         }
     } else {
-        const u32 key = isnew ? dest : 0xFFu;
+        const u32 key = c.isnew ? c.dest : 0xFFu;
         const u32 grp = __match_any_sync(FULL, key);
-        if (isnew) {
+        if (c.isnew) {
             const u32 leader = __ffs(grp) - 1;
             const u32 rank_in = __popc(grp & lanemask_lt());
             u32 base = 0;
-            if (dest == E.me) {
-                if (lane == leader) base = atomicAdd(&E.C->q_tail[side], (u32)__popc(grp));
+            if (c.dest == E.me) {
+                if (lane == leader) base = acc_take_slots(E, side, (u32)__popc(grp));
                 base = __shfl_sync(grp, base, leader);
-                E.q[side][base + rank_in] = v;
+                const u32 slot = base + rank_in;
+                E.q[side][slot] = v;
                 E.parent[side][v - E.lo] = u;
+                if (E.sq && slot - E.sq_base < SOLO_CAP) E.sq[slot - E.sq_base] = v;
+                ptx::prefetch_l2(E.row_ptr + (v - E.lo));
             } else {
-                if (lane == leader) base = atomicAdd(&E.C->sent[side][dest], (u32)__popc(grp));
+                if (lane == leader) base = atomicAdd(&E.C->sent[side][c.dest], (u32)__popc(grp));
                 base = __shfl_sync(grp, base, leader);
-                ptx::st_peer(rq_of(K, dest, side, E.me) + base + rank_in, v);
-                ptx::st_peer(parent_of(K, dest, side) + (v - dest * K.B), u);
+                ptx::st_peer(rq_of(K, c.dest, side, E.me) + base + rank_in, v);
+                ptx::st_peer(parent_of(K, c.dest, side) + (v - c.dest * K.B), u);
             }
         }
     }
-    cnt += isnew ? 1u : 0u;
-    if (meet) atomicMin(&E.C->meet_local, v);
+    cnt += c.isnew ? 1u : 0u;
+    if (c.meet) acc_note_meet(E, v);
+}
+
+// UNR edges per lane: all column loads first, then all filter loads, then all claims, then the
+// enqueues — three dependent memory round trips per UNR*32 edges instead of per 32.  Deliberately
+// NOT inlined: the level loop of a small search is executed once per level by a single warp, so
+// its cost is instruction fetch; one shared copy of this body keeps the hot path inside the
+// instruction cache (the fully inlined kernel was 124 KB of SASS and ran 2x slower).
+static_assert(UNR == 4, "visit_batch takes four edges per lane");
+template <bool MULTI>
+__device__ __noinline__ u32 visit_batch(const KParams& K, const Env& E, u32 side, u32 okmask, u32 u0, u32 u1, u32 u2, u32 u3,
+                                        const u32* p0, const u32* p1, const u32* p2, const u32* p3) {
+    const bool ok[UNR] = {(okmask & 1u) != 0, (okmask & 2u) != 0, (okmask & 4u) != 0, (okmask & 8u) != 0};
+    const u32 uu[UNR] = {u0, u1, u2, u3};
+    const u32* const vp[UNR] = {p0, p1, p2, p3};
+    u32 cnt = 0;
+    u32 v[UNR];
+    u64 seen[UNR];
+    Claim c[UNR];
+#pragma unroll
+    for (int k = 0; k < UNR; ++k) v[k] = ok[k] ? __ldg(vp[k]) : 0u;
+    DBG_STAMP(4, v[0] + v[1] + v[2] + v[3]);
+#pragma unroll
+    for (int k = 0; k < UNR; ++k) seen[k] = ok[k] ? (E.filter ? E.vis[v[k] >> 5] : 0ull) : ~0ull;   // filter only; may be stale
+#pragma unroll
+    for (int k = 0; k < UNR; ++k) c[k] = claim<MULTI>(K, E, side, ok[k], v[k], seen[k]);
+    DBG_STAMP(5, (u32)c[0].isnew + (u32)c[1].isnew + (u32)c[2].isnew + (u32)c[3].isnew);
+    if (MULTI) {
+#pragma unroll
+        for (int k = 0; k < UNR; ++k) enqueue<MULTI>(K, E, side, c[k], uu[k], v[k], cnt);
+    } else {
+        // one queue-cursor atomic for the whole batch
+        const u32 lane = threadIdx.x & 31;
+        u32 m[UNR];
+        u32 total = 0;
+#pragma unroll
+        for (int k = 0; k < UNR; ++k) { m[k] = __ballot_sync(FULL, c[k].isnew); total += __popc(m[k]); }
+        if (total) {
+            u32 base = 0;
+            if (lane == 0) base = acc_take_slots(E, side, total);
+            base = __shfl_sync(FULL, base, 0);
+#pragma unroll
+            for (int k = 0; k < UNR; ++k) {
+                if (c[k].isnew) {
+                    const u32 slot = base + __popc(m[k] & lanemask_lt());
+                    E.q[side][slot] = v[k];
+                    E.parent[side][v[k] - E.lo] = uu[k];
+                    if (E.sq && slot - E.sq_base < SOLO_CAP) E.sq[slot - E.sq_base] = v[k];
+                    ptx::prefetch_l2(E.row_ptr + (v[k] - E.lo));
+                    ++cnt;
+                    if (c[k].meet) acc_note_meet(E, v[k]);
+                }
+                base += __popc(m[k]);
+            }
+        }
+    }
+    return cnt;
+}
+
+// a contiguous range of one row, walked by the whole warp
+template <bool MULTI>
+__device__ __forceinline__ void expand_range(const KParams& K, const Env& E, u32 side, u32 uu, u64 b, u64 e, u32& cnt) {
+    const u32 lane = threadIdx.x & 31;
+    for (u64 p = b; p < e; p += 32 * UNR) {
+        const u64 i0 = p + lane;
+        u32 okmask = 0;
+#pragma unroll
+        for (int k = 0; k < UNR; ++k) okmask |= (i0 + (u64)k * 32 < e) ? (1u << k) : 0u;
+        const u32* c0 = E.col + i0;
+        cnt += visit_batch<MULTI>(K, E, side, okmask, uu, uu, uu, uu, c0, c0 + 32, c0 + 64, c0 + 96);
+    }
 }
 
 // ------------------------------------------------------------------------------------------
-// top-down level: warps take 32 frontier vertices at a time
+// top-down level.  Warps take `vpw` frontier vertices at a time (32 when the frontier is large,
+// fewer when it is small so that the work spreads over the machine).
 // ------------------------------------------------------------------------------------------
 template <bool MULTI>
-__device__ void expand_td(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps) {
+__device__ __noinline__ void expand_td(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps,
+                          const u32* smem_front = nullptr) {
     const u32 lane = threadIdx.x & 31;
     const u32 side = st.side;
     const u32 total = st.local_front;
+    u32 vpw = 32;
+    while (vpw > 1 && (u64)(vpw >> 1) * nwarps >= total) vpw >>= 1;
     u32 cnt = 0;
     u64 edges = 0;
-    for (u32 base = warp_gid * 32u; base < total; base += nwarps * 32u) {
-        const u32 i = base + lane;
+    const u32 nbatches = (total + vpw - 1) / vpw;
+    for (u32 b = warp_gid; b < nbatches; b += nwarps) {
+        const u32 i = b * vpw + lane;
         u32 u = 0;
         u64 r0 = 0, r1 = 0;
-        if (i < total) {
-            u = fetch_frontier<MULTI>(K, E, st, side, i);
+        DBG_STAMP(0, i);
+        if (lane < vpw && i < total) {
+            u = fetch_frontier<MULTI>(K, E, st, side, i, smem_front);
+            DBG_STAMP(1, u);
             const u32 ul = u - E.lo;
             r0 = __ldg(E.row_ptr + ul);
             r1 = __ldg(E.row_ptr + ul + 1);
         }
-        const u64 deg = r1 - r0;
+        u64 deg = r1 - r0;
+        DBG_STAMP(2, deg);
         edges += deg;
+        // hub rows: hand them to the whole grid (hub phase) unless the list is full
+        if (deg >= HUB_ROW) {
+            const u32 nch = (u32)((deg + HUB_CHUNK - 1) / HUB_CHUNK);
+            const unsigned long long inc = (1ull << 40) | (unsigned long long)nch;
+            const unsigned long long old = atomicAdd(&E.C->hub_packed, inc);
+            const u32 slot = (u32)(old >> 40);
+            if (slot < HUB_CAP) {
+                HubEntry h;
+                h.u = u; h.nchunks = nch; h.r0 = r0; h.r1 = r1; h.chunk_base = old & 0xFFFFFFFFFFull;
+                hub_of(K, E.me)[slot] = h;
+                if (E.s_hub) *E.s_hub = 1u;
+                deg = 0; r1 = r0;
+            } else {
+                atomicAdd(&E.C->hub_packed, 0ull - inc);
+            }
+        }
         // long rows: the whole warp walks one row, coalesced
         u32 big = __ballot_sync(FULL, deg >= BIG_ROW);
         while (big) {
             const u32 srcl = __ffs(big) - 1;
             big &= big - 1;
             const u32 uu = __shfl_sync(FULL, u, srcl);
-            const u64 b = __shfl_sync(FULL, r0, srcl), e = __shfl_sync(FULL, r1, srcl);
-            for (u64 p = b; p < e; p += 32) {
-                const u64 idx = p + lane;
-                const bool ok = idx < e;
-                const u32 v = ok ? __ldg(E.col + idx) : 0u;
-                visit<MULTI>(K, E, side, ok, uu, v, cnt);
-            }
+            const u64 rb = __shfl_sync(FULL, r0, srcl), re = __shfl_sync(FULL, r1, srcl);
+            expand_range<MULTI>(K, E, side, uu, rb, re, cnt);
         }
-        // short rows: flatten the 32 rows into one edge index space (scan + search by shuffles)
-        const u32 sdeg = deg >= BIG_ROW ? 0u : (u32)deg;
+        // tiny rows (<= UNR entries): every lane walks its own row, no cross-lane bookkeeping
+        if (__any_sync(FULL, deg != 0 && deg <= (u64)UNR)) {
+            const u32 okmask = deg <= (u64)UNR ? ((1u << (u32)deg) - 1u) : 0u;
+            const u32* c0 = E.col + r0;
+            DBG_STAMP(3, c0);
+            cnt += visit_batch<MULTI>(K, E, side, okmask, u, u, u, u, c0, c0 + 1, c0 + 2, c0 + 3);
+            DBG_STAMP(6, cnt);
+        }
+        // short rows: flatten the rows of the batch into one edge index space (scan + search by shuffles)
+        const u32 sdeg = (deg >= BIG_ROW || deg <= (u64)UNR) ? 0u : (u32)deg;
         u32 incl = sdeg;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -470,21 +657,27 @@ __device__ void expand_td(const KParams& K, const Env& E, const LevelState& st, 
         }
         const u32 excl = incl - sdeg;
         const u32 tot = __shfl_sync(FULL, incl, 31);
-        for (u32 t = 0; t < tot; t += 32) {
-            const u32 idx = t + lane;
-            const bool ok = idx < tot;
-            u32 j = 0;
+        for (u32 t = 0; t < tot; t += 32 * UNR) {
+            u32 okmask = 0;
+            u32 us[UNR];
+            const u32* vp[UNR];
 #pragma unroll
-            for (int step = 16; step > 0; step >>= 1) {
-                const u32 cand = j + step;
-                const u32 ec = __shfl_sync(FULL, excl, cand & 31u);
-                if (cand < 32u && ec <= idx) j = cand;
+            for (int k = 0; k < UNR; ++k) {
+                const u32 idx = t + k * 32 + lane;
+                okmask |= (idx < tot) ? (1u << k) : 0u;
+                u32 j = 0;
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const u32 cand = j + step;
+                    const u32 ec = __shfl_sync(FULL, excl, cand & 31u);
+                    if (cand < 32u && ec <= idx) j = cand;
+                }
+                us[k] = __shfl_sync(FULL, u, j);
+                const u64 rb = __shfl_sync(FULL, r0, j);
+                const u32 eb = __shfl_sync(FULL, excl, j);
+                vp[k] = E.col + rb + (idx - eb);
             }
-            const u32 uu = __shfl_sync(FULL, u, j);
-            const u64 rb = __shfl_sync(FULL, r0, j);
-            const u32 eb = __shfl_sync(FULL, excl, j);
-            const u32 v = ok ? __ldg(E.col + rb + (idx - eb)) : 0u;
-            visit<MULTI>(K, E, side, ok, uu, v, cnt);
+            cnt += visit_batch<MULTI>(K, E, side, okmask, us[0], us[1], us[2], us[3], vp[0], vp[1], vp[2], vp[3]);
         }
     }
     // flush this warp's counters
@@ -493,17 +686,48 @@ __device__ void expand_td(const KParams& K, const Env& E, const LevelState& st, 
         cnt += __shfl_xor_sync(FULL, cnt, d);
         edges += __shfl_xor_sync(FULL, edges, d);
     }
-    if (lane == 0) {
-        if (cnt) atomicAdd(&E.C->new_count, cnt);
-        if (edges) atomicAdd(&E.C->edges_acc, (unsigned long long)edges);
+    if (lane == 0) acc_flush(E, cnt, edges);
+    DBG_STAMP(7, cnt);
+#ifdef BIBFS_FINE_TRACE
+    if (blockIdx.x == 0 && threadIdx.x == 0) g_dbg_level++;
+#endif
+}
+
+// hub phase: every warp of the rank takes 2 KB chunks of the deferred rows
+template <bool MULTI>
+__device__ __noinline__ void expand_hubs(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 side = st.side;
+    const HubEntry* H = hub_of(K, E.me);
+    const u32 ne = min(st.hub_entries, HUB_CAP);
+    u32 cnt = 0;
+    for (u32 c = warp_gid; c < st.hub_chunks; c += nwarps) {
+        // entries are ordered by chunk_base (slot and base come from one atomic): binary search
+        u32 lo = 0, hi = ne;
+        while (hi - lo > 1) {
+            const u32 mid = (lo + hi) >> 1;
+            if (__ldcg(&H[mid].chunk_base) <= c) lo = mid; else hi = mid;
+        }
+        const u64 base = __ldcg(&H[lo].chunk_base);
+        const u32 nch = __ldcg(&H[lo].nchunks);
+        if (c - base >= nch) continue;        // chunk of an entry that did not fit in the list
+        const u64 r0 = __ldcg(&H[lo].r0), r1 = __ldcg(&H[lo].r1);
+        const u32 uu = __ldcg(&H[lo].u);
+        const u64 b = r0 + (c - base) * HUB_CHUNK;
+        const u64 e = min(r1, b + HUB_CHUNK);
+        expand_range<MULTI>(K, E, side, uu, b, e, cnt);
     }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(FULL, cnt, d);
+    if (lane == 0) acc_flush(E, cnt, 0);
 }
 
 // ------------------------------------------------------------------------------------------
-// bottom-up level: every unvisited owned vertex looks for a parent in the frontier bitmap
+// bottom-up level: every unvisited owned vertex looks for a parent in the frontier bitmap.
+// Short rows are scanned by their lane, long rows by the whole warp (ballot = early exit).
 // ------------------------------------------------------------------------------------------
 template <bool MULTI>
-__device__ void expand_bu(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps) {
+__device__ __noinline__ void expand_bu(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps) {
     const u32 lane = threadIdx.x & 31;
     const u32 side = st.side;
     const u32* fcur = fbm_of(K, E.me, side, st.fbm_cur[side]);
@@ -519,13 +743,31 @@ __device__ void expand_bu(const KParams& K, const Env& E, const LevelState& st, 
         const bool unvis = v < K.n && !((word >> (32u * side + lane)) & 1ull);
         bool found = false;
         u32 par = NO_V;
-        if (unvis) {
-            const u64 r0 = __ldg(E.row_ptr + (v - E.lo)), r1 = __ldg(E.row_ptr + (v - E.lo) + 1);
+        u64 r0 = 0, r1 = 0;
+        if (unvis) { r0 = __ldg(E.row_ptr + (v - E.lo)); r1 = __ldg(E.row_ptr + (v - E.lo) + 1); }
+        const u64 deg = r1 - r0;
+        if (unvis && deg < BIG_ROW) {
             for (u64 e = r0; e < r1; ++e) {
                 const u32 u = __ldg(E.col + e);
                 ++edges;
                 if ((fcur[u >> 5] >> (u & 31u)) & 1u) { found = true; par = u; break; }
             }
+        }
+        u32 big = __ballot_sync(FULL, unvis && deg >= BIG_ROW);
+        while (big) {
+            const u32 sl = __ffs(big) - 1;
+            big &= big - 1;
+            const u64 b = __shfl_sync(FULL, r0, sl), e = __shfl_sync(FULL, r1, sl);
+            u32 hitpar = NO_V;
+            for (u64 p = b; p < e; p += 32) {
+                const u64 idx = p + lane;
+                u32 u = 0;
+                bool hit = false;
+                if (idx < e) { u = __ldg(E.col + idx); ++edges; hit = (fcur[u >> 5] >> (u & 31u)) & 1u; }
+                const u32 hm = __ballot_sync(FULL, hit);
+                if (hm) { hitpar = __shfl_sync(FULL, u, __ffs(hm) - 1); break; }
+            }
+            if (lane == sl && hitpar != NO_V) { found = true; par = hitpar; }
         }
         const u32 newmask = __ballot_sync(FULL, found);
         if (newmask) {
@@ -533,8 +775,8 @@ __device__ void expand_bu(const KParams& K, const Env& E, const LevelState& st, 
             if (lane == 0) {
                 E.vis[wg] = word | ((u64)newmask << (32u * side));
                 const u32 meetmask = newmask & (u32)(word >> (32u * (1u - side)));
-                if (meetmask) atomicMin(&E.C->meet_local, E.lo + wl * 32u + (u32)(__ffs(meetmask) - 1));
-                base = atomicAdd(&E.C->q_tail[side], (u32)__popc(newmask));
+                if (meetmask) atomicMin(&E.A->meet_local, E.lo + wl * 32u + (u32)(__ffs(meetmask) - 1));
+                base = atomicAdd(&E.A->q_tail[side], (u32)__popc(newmask));
             }
             base = __shfl_sync(FULL, base, 0);
             if (found) {
@@ -551,13 +793,13 @@ __device__ void expand_bu(const KParams& K, const Env& E, const LevelState& st, 
         edges += __shfl_xor_sync(FULL, edges, d);
     }
     if (lane == 0) {
-        if (cnt) atomicAdd(&E.C->new_count, cnt);
-        if (edges) atomicAdd(&E.C->edges_acc, (unsigned long long)edges);
+        if (cnt) atomicAdd(&E.A->new_count, cnt);
+        if (edges) atomicAdd(&E.A->edges, (unsigned long long)edges);
     }
 }
 
 // copy this rank's slice of a frontier bitmap into every peer's replica (8-byte stores over NVLink)
-__device__ void push_fbm_slice(const KParams& K, const Env& E, u32 side, u32 buf, u32 gtid, u32 gthreads) {
+__device__ __noinline__ void push_fbm_slice(const KParams& K, const Env& E, u32 side, u32 buf, u32 gtid, u32 gthreads) {
     const u32 words2 = K.B / 64;                 // 8-byte units in the slice
     const u32 w0 = E.lo / 32;
     const uint2* src = reinterpret_cast<const uint2*>(fbm_of(K, E.me, side, buf) + w0);
@@ -571,6 +813,183 @@ __device__ void push_fbm_slice(const KParams& K, const Env& E, u32 side, u32 buf
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// shared memory of the search kernel
+// ------------------------------------------------------------------------------------------
+struct Smem {
+    LevelState st;
+    Acc acc;
+    u32 fail, hub;
+    u32 qcur[2], qvalid[2];
+    unsigned long long pend_edges, pend_visited;   // solo levels: totals not yet added to Ctrl
+    u32 q[2][2][SOLO_CAP];
+};
+
+__device__ __noinline__ void trace_level(const KParams& K, const Env& E, u32 side, u32 mode, u32 expanded, u32 discovered, u64 edges,
+                                         u64 t_expand) {
+    Ctrl* C = E.C;
+    if (C->trace_count >= TRACE_CAP) return;
+    bibfs_level_trace& T = trace_of(K, E.me)[C->trace_count++];
+    T.side = side; T.mode = mode; T.frontier = expanded; T.discovered = discovered;
+    T.t_ns = ptx::globaltimer_ns(); T.edges = edges; T.t_expand_ns = t_expand;
+}
+
+__device__ __noinline__ void solo_push_hub(const KParams& K, const Env& E, Smem& sm, u32 u, u64 r0, u64 r1) {
+    const u64 deg = r1 - r0;
+    const u32 nch = (u32)((deg + HUB_CHUNK - 1) / HUB_CHUNK);
+    const unsigned long long inc = (1ull << 40) | (unsigned long long)nch;
+    const unsigned long long old = atomicAdd(&E.C->hub_packed, inc);
+    const u32 slot = (u32)(old >> 40);
+    HubEntry h;
+    h.u = u; h.nchunks = nch; h.r0 = r0; h.r1 = r1; h.chunk_base = old & 0xFFFFFFFFFFull;
+    if (slot < HUB_CAP) hub_of(K, E.me)[slot] = h;   // solo frontiers hold <= 1024 vertices: never overflows
+    sm.hub = 1u;
+}
+
+// Consecutive solo levels of a single-rank search, one frontier vertex per thread.  This is the
+// latency path (reference-sized graphs finish here; a 4-digit-path grid spends thousands of levels
+// here), so it is written for a short instruction stream and a short dependent-memory chain:
+//   frontier vertex (shared mirror) -> row offsets (L2, prefetched at discovery) -> up to 4 column
+//   loads in flight -> up to 4 claims in flight -> one shared-memory cursor atomic per warp.
+// State and accumulators stay in shared memory; nothing is published until the grid is needed.
+__device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
+    const u32 tid = threadIdx.x, lane = tid & 31;
+    LevelState& st = sm.st;
+    E.solo = true; E.A = &sm.acc; E.sA = &sm.acc; E.filter = false; E.s_hub = &sm.hub;
+    while (true) {
+        const u32 side = st.side;
+        const u32 total = st.local_front;
+        const u32 cur = sm.qcur[side];
+        const bool from_mirror = sm.qvalid[side] != 0;
+        u32* const out = sm.q[side][cur ^ 1u];
+        const u32 base_tail = st.q_hi[side];
+        const u32 qlo = st.q_lo[side];
+        const u32 sh = 32u * side, osh = 32u - sh;
+        E.sq = out; E.sq_base = base_tail;
+        u32 u = 0;
+        u64 r0 = 0, r1 = 0;
+        if (tid < total) {
+            u = from_mirror ? sm.q[side][cur][tid] : __ldcg(E.q[side] + qlo + tid);
+            r0 = __ldg(E.row_ptr + (u - E.lo));
+            r1 = __ldg(E.row_ptr + (u - E.lo) + 1);
+        }
+        u64 deg = r1 - r0;
+        const u64 t_begin = (K.flags & BIBFS_F_TRACE) ? ptx::globaltimer_ns() : 0ull;
+        (void)t_begin;
+        // per-warp edge count
+        {
+            u32 d32 = (u32)(deg > 0xFFFFFFFFull ? 0xFFFFFFFFull : deg);
+            const u32 wsum = __reduce_add_sync(FULL, d32);
+            if (lane == 0 && wsum) ptx::reds_add64(&sm.acc.edges, wsum);
+        }
+        if (deg >= HUB_ROW) { solo_push_hub(K, E, sm, u, r0, r1); deg = 0; }
+        // rows shorter than a warp: each lane walks its own row, 4 entries at a time
+        const u32 sdeg = deg < 32 ? (u32)deg : 0u;
+        const u32 wmax = __reduce_max_sync(FULL, sdeg);
+        for (u32 e0 = 0; e0 < wmax; e0 += 4) {
+            u32 v[4];
+            u64 old[4];
+            bool isnew[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] = (e0 + k < sdeg) ? __ldg(E.col + r0 + e0 + k) : 0xFFFFFFFFu;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                old[k] = (e0 + k < sdeg) ? ptx::atom_or_gpu(&E.vis[v[k] >> 5], 1ull << ((v[k] & 31u) + sh)) : ~0ull;
+            u32 m[4], tot = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                isnew[k] = !((old[k] >> ((v[k] & 31u) + sh)) & 1ull);
+                m[k] = __ballot_sync(FULL, isnew[k]);
+                tot += __popc(m[k]);
+            }
+            if (tot) {
+                u32 base = 0;
+                if (lane == 0) base = ptx::atoms_add(&sm.acc.q_tail[side], tot);
+                base = __shfl_sync(FULL, base, 0);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (isnew[k]) {
+                        const u32 slot = base + __popc(m[k] & lanemask_lt());
+                        E.q[side][slot] = v[k];
+                        E.parent[side][v[k] - E.lo] = u;
+                        if (slot - base_tail < SOLO_CAP) out[slot - base_tail] = v[k];
+                        ptx::prefetch_l2(E.row_ptr + (v[k] - E.lo));
+                        if ((old[k] >> ((v[k] & 31u) + osh)) & 1ull) ptx::reds_min(&sm.acc.meet_local, v[k]);
+                    }
+                    base += __popc(m[k]);
+                }
+            }
+        }
+        // rows of a warp's length or more (below the hub threshold): the warp walks them together
+        u32 big = __ballot_sync(FULL, deg >= 32);
+        if (big) {
+            u32 cnt = 0;
+            while (big) {
+                const u32 sl = __ffs(big) - 1;
+                big &= big - 1;
+                const u32 uu = __shfl_sync(FULL, u, sl);
+                const u64 rb = __shfl_sync(FULL, r0, sl), re = __shfl_sync(FULL, r1, sl);
+                expand_range<false>(K, E, side, uu, rb, re, cnt);
+            }
+        }
+        __syncthreads();
+        // ---- level end: one thread, shared memory only
+        if (tid == 0) {
+            Ctrl* C = E.C;
+            if (sm.hub) {
+                // the level is not over: publish and let the grid expand the deferred rows
+                const u64 hp = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&C->hub_packed));
+                st.hub_entries = (u32)(hp >> 40);
+                st.hub_chunks = (u32)(hp & 0xFFFFFFFFFFull);
+                st.prev_phase = PH_TD_SOLO;
+                st.phase = PH_TD_HUB;
+                C->hub_packed = 0;
+                sm.acc.new_count = sm.acc.q_tail[side] - base_tail;
+                sm.qcur[side] ^= 1u; sm.qvalid[side] = 0; sm.hub = 0;
+            } else {
+                const u32 tail = sm.acc.q_tail[side];
+                const u32 found = tail - base_tail;
+                const u32 meet = sm.acc.meet_local;
+                const u32 expanded = st.nf[side];
+                const u64 ed = sm.acc.edges;
+                st.nf[side] = found;
+                st.depth[side] += 1;
+                st.levels += 1;
+                st.fbm_valid[side] = 0;
+                st.q_lo[side] = base_tail;
+                st.q_hi[side] = tail;
+                sm.pend_edges += ed;
+                sm.pend_visited += found;
+                sm.acc.edges = 0; sm.acc.new_count = 0; sm.acc.meet_local = NO_V;
+                sm.qcur[side] ^= 1u;
+                sm.qvalid[side] = found <= SOLO_CAP ? 1u : 0u;
+                if (K.flags & BIBFS_F_TRACE) trace_level(K, E, side, PH_TD_SOLO, expanded, found, ed, ptx::globaltimer_ns());
+                if (meet != NO_V) {
+                    st.length = (i32)(st.depth[0] + st.depth[1]);
+                    st.meet = meet;
+                    st.phase = PH_DONE;
+                } else {
+                    const u32 ns = st.nf[0] <= st.nf[1] ? 0u : 1u;
+                    st.side = ns;
+                    const u32 lf = st.q_hi[ns] - st.q_lo[ns];
+                    st.local_front = lf;
+                    if (st.nf[ns] == 0) { st.length = -1; st.phase = PH_DONE; }
+                    else if (lf > K.solo_threshold || (K.flags & (BIBFS_F_FORCE_BU | BIBFS_F_FORCE_GRID))) decide_next(K, st);
+                    else if (!(K.flags & BIBFS_F_FORCE_TD) && K.bu_div != 0xFFFFFFFFu && st.nf[ns] > K.n / K.bu_div) decide_next(K, st);
+                }
+            }
+            if (st.phase != PH_TD_SOLO) {
+                C->edges_total += sm.pend_edges;
+                C->res.vertices_visited += sm.pend_visited;
+                sm.pend_edges = 0; sm.pend_visited = 0;
+                if (st.phase == PH_DONE) write_result(K, C, st);
+            }
+        }
+        __syncthreads();
+        if (st.phase != PH_TD_SOLO) return;
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------
@@ -578,10 +997,15 @@ __device__ void push_fbm_slice(const KParams& K, const Env& E, u32 side, u32 buf
 // ------------------------------------------------------------------------------------------
 template <bool MULTI>
 __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant__ KParams K) {
-    __shared__ LevelState st;
-    __shared__ u32 s_fail;
+    __shared__ Smem sm;
+    LevelState& st = sm.st;        // this CTA's copy of the level state (the leader CTA's is authoritative)
+    Acc& s_acc = sm.acc;           // leader CTA: accumulators of solo levels / staging at sync points
+    u32& s_fail = sm.fail;
+    u32& s_hub = sm.hub;           // solo level deferred at least one hub row
+    auto& s_q = sm.q;              // solo mode: entries each side appended in its last level (double buffered)
+    u32 (&s_qcur)[2] = sm.qcur;    // which buffer holds the side's current frontier
+    u32 (&s_qvalid)[2] = sm.qvalid;  // ... and whether that mirror is complete
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr u32 WPC = BFS_THREADS / 32;
     const u32 vr = MULTI ? blockIdx.x / K.cpr : 0u;
     Env E;
     E.cta = blockIdx.x - vr * K.cpr;
@@ -590,6 +1014,9 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     E.lo = E.me * K.B;
     E.P = K.P; E.B = K.B; E.n = K.n; E.nw = K.L.nw;
     E.C = ctrl_of(K, E.me);
+    E.A = &E.C->acc;
+    E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = true;
+    E.sA = &s_acc; E.solo = false;
     E.vis = vis_of(K, E.me);
     E.parent[0] = parent_of(K, E.me, 0); E.parent[1] = parent_of(K, E.me, 1);
     E.q[0] = q_of(K, E.me, 0); E.q[1] = q_of(K, E.me, 1);
@@ -598,73 +1025,148 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     Ctrl* C = E.C;
     const u64 deadline = ptx::globaltimer_ns() + (u64)K.watchdog_ms * 1000000ull;
     const u64 genbase = (u64)K.seq << 32;
-    if (tid == 0) s_fail = 0;
+    const bool is_leader_cta = (E.cta == 0);
+    if (tid == 0) { s_fail = 0; s_hub = 0; s_qvalid[0] = 0; s_qvalid[1] = 0; s_qcur[0] = 0; s_qcur[1] = 0; sm.pend_edges = 0; sm.pend_visited = 0; }
     __syncthreads();
 
-    // ---- query start
-    if (E.cta == 0) {
-        if (warp == 0) {
-            const bool ok = leader_init<MULTI>(K, E, deadline);
-            if (!ok && lane == 0) s_fail = 1;
-        }
-    } else if (tid == 0) {
-        if (!wait_gen(C, genbase | 1u, deadline)) s_fail = 1;
-    }
-    __syncthreads();
-
-    // every CTA keeps a shared-memory copy of the level state
+    // non-leader CTAs: copy the published level state global -> shared after a wake-up
     auto load_state = [&]() {
         const u32* g = reinterpret_cast<const u32*>(&C->st);
         u32* s = reinterpret_cast<u32*>(&st);
         for (u32 i = tid; i < sizeof(LevelState) / 4; i += BFS_THREADS) s[i] = __ldcg(g + i);
         __syncthreads();
     };
+    // leader warp: publish the shared state + accumulators and wake the other CTAs
+    auto publish_and_wake = [&]() {
+        if (lane == 0) st.wake += 1;
+        __syncwarp();
+        u32* g = reinterpret_cast<u32*>(&C->st);
+        const u32* s = reinterpret_cast<const u32*>(&st);
+        for (u32 i = lane; i < sizeof(LevelState) / 4; i += 32) g[i] = s[i];
+        __syncwarp();
+        if (lane == 0) {
+            C->acc = s_acc;
+            ptx::fence_gpu();
+            ptx::st_release_gpu(&C->bar_gen, genbase | (u64)st.wake);
+        }
+        __syncwarp();
+    };
 
-    // synchronisation point shared by all phases.  Returns false if the query was aborted.
-    auto sync_point = [&](int kind, bool solo, u32 mode) -> bool {
+    // ---- query start.  The leader CTA always works on the shared-memory state; it publishes it
+    // whenever the next phase needs the other CTAs.
+    if (is_leader_cta) {
+        if (warp == 0) {
+            const bool ok = leader_init<MULTI>(K, E, st, s_acc, deadline);
+            if (!ok && lane == 0) s_fail = 1;
+            if (lane == 0) {   // the seeds are the first mirrored entries
+                const u32 src = K.query_in_ctrl ? C->q_src : K.src, dst = K.query_in_ctrl ? C->q_dst : K.dst;
+                if (s_acc.q_tail[0] == 1) { s_q[0][0][0] = src; s_qvalid[0] = 1; }
+                if (s_acc.q_tail[1] == 1) { s_q[1][0][0] = dst; s_qvalid[1] = 1; }
+            }
+            __syncwarp();
+            if (st.phase != PH_TD_SOLO) publish_and_wake();
+        }
         __syncthreads();
-        if (solo) {
-            if (warp == 0 && !leader_sync<MULTI>(K, E, kind, true, mode, deadline) && lane == 0) s_fail = 1;
-        } else if (E.cta != 0) {
+    } else {
+        if (tid == 0 && !wait_gen(C, genbase | 1u, deadline)) s_fail = 1;
+        __syncthreads();
+        if (!s_fail) load_state();
+    }
+    bool alive = (s_fail == 0);
+
+    // Synchronisation point of grid-mode phases.  Returns false if the query was aborted.
+    auto sync_grid = [&](int kind, u32 mode) -> bool {
+        __syncthreads();
+        if (!is_leader_cta) {
             if (tid == 0) {
                 if (MULTI) ptx::fence_sys();
                 ptx::red_release_gpu_add(&C->bar_count, 1u);
                 if (!wait_gen(C, genbase | (u64)(st.wake + 1u), deadline)) s_fail = 1;
             }
-        } else if (warp == 0) {
+            __syncthreads();
+            if (s_fail) return false;
+            load_state();
+            return true;
+        }
+        if (warp == 0) {
             bool ok = true;
-            if (lane == 0) ok = wait_count(C, E.cpr - 1u, deadline);
+            if (lane == 0) {
+                ok = wait_count(C, E.cpr - 1u, deadline);
+                ptx::st_relaxed_gpu(&C->bar_count, 0u);
+                pull_acc(s_acc, &C->acc);               // the grid's accumulators -> shared memory
+            }
             ok = __shfl_sync(FULL, ok, 0);
-            if (ok) ok = leader_sync<MULTI>(K, E, kind, false, mode, deadline);
-            else if (lane == 0) { atomicExch(&C->abort_flag, 1u); C->st.status = 1; C->st.phase = PH_DONE; write_result(K, C, C->st); }
+            if (lane == 0 && kind == SYNC_LEVEL) s_qvalid[st.side] = 0;   // grid levels do not feed the solo mirror
+            __syncwarp();
+            if (ok) ok = leader_sync<MULTI>(K, E, st, s_acc, kind, mode, deadline, true);
+            else if (lane == 0) { atomicExch(&C->abort_flag, 1u); st.status = 1; st.phase = PH_DONE; write_result(K, C, st); }
             if (!ok && lane == 0) s_fail = 1;
+            __syncwarp();
+            publish_and_wake();     // grid mode: every sync point releases the other CTAs
         }
         __syncthreads();
-        if (s_fail) return false;
-        load_state();
-        return true;
+        return s_fail == 0;
     };
-
-    bool alive = (s_fail == 0);
-    if (alive) load_state();
 
     while (alive) {
         const u32 phase = st.phase;
         if (phase == PH_DONE) break;
         if (phase == PH_TD_SOLO) {
-            if (E.cta != 0) {   // parked until the leader wakes the grid
+            if (!is_leader_cta) {   // parked until the leader wakes the grid
                 if (tid == 0 && !wait_gen(C, genbase | (u64)(st.wake + 1u), deadline)) s_fail = 1;
                 __syncthreads();
                 if (s_fail) { alive = false; break; }
                 load_state();
                 continue;
             }
-            expand_td<MULTI>(K, E, st, warp, WPC);
-            alive = sync_point(SYNC_LEVEL, true, PH_TD_SOLO);
+            if (!MULTI) {
+                solo_run(K, E, sm);
+                if (warp == 0) publish_and_wake();      // left solo mode: the grid is needed (or the query is done)
+                __syncthreads();
+                continue;
+            }
+            {
+                const u32 side = st.side;
+                const u32 nq = st.q_hi[side] - st.q_lo[side];
+                // read the frontier from the shared mirror when the previous level of this side left
+                // one; this level's discoveries go to the side's other buffer
+                const u32 cur = s_qcur[side];
+                const u32* front = (s_qvalid[side] && nq <= SOLO_CAP) ? s_q[side][cur] : nullptr;
+                E.A = &s_acc; E.solo = true;
+                E.sq = s_q[side][cur ^ 1u];
+                E.sq_base = st.q_hi[side];           // == current tail of this side's queue
+                E.s_hub = &s_hub;
+                E.filter = st.local_front >= FILTER_MIN;
+                expand_td<MULTI>(K, E, st, warp, WPC, front);
+            }
+            __syncthreads();
+            if (warp == 0) {
+                const bool hubs = s_hub != 0;
+                const u32 side_done = st.side;
+                if (!leader_sync<MULTI>(K, E, st, s_acc, SYNC_LEVEL, PH_TD_SOLO, deadline, hubs) && lane == 0) s_fail = 1;
+                if (lane == 0) {
+                    // (a hub phase appends to the global queue only: the mirror is then incomplete)
+                    s_qcur[side_done] ^= 1u;
+                    s_qvalid[side_done] = (!hubs && s_acc.q_tail[side_done] - E.sq_base <= SOLO_CAP) ? 1u : 0u;
+                    s_hub = 0;
+                }
+                __syncwarp();
+                if (st.phase != PH_TD_SOLO) publish_and_wake();
+            }
+            __syncthreads();
+            DBG_STAMP2(3, st.phase);
+            E.sq = nullptr; E.s_hub = nullptr; E.filter = true; E.solo = false; E.A = &C->acc;
+            if (s_fail) { alive = false; break; }
         } else if (phase == PH_TD_GRID) {
+            E.A = &C->acc;
             expand_td<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
-            alive = sync_point(SYNC_LEVEL, false, PH_TD_GRID);
+            alive = sync_grid(SYNC_LEVEL, PH_TD_GRID);
+        } else if (phase == PH_TD_HUB) {
+            E.A = &C->acc;
+            expand_hubs<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
+            alive = sync_grid(SYNC_LEVEL, PH_TD_HUB);
         } else {  // PH_BU
+            E.A = &C->acc;
             const u32 side = st.side;
             const u32 gtid = E.cta * BFS_THREADS + tid, gthreads = E.cpr * BFS_THREADS;
             if (!st.fbm_valid[side]) {
@@ -672,29 +1174,29 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 u32* f = fbm_of(K, E.me, side, st.fbm_cur[side]);
                 const u32 w0 = E.lo / 32, words = K.B / 32;
                 for (u32 i = gtid; i < words; i += gthreads) f[w0 + i] = 0;
-                alive = sync_point(SYNC_LOCAL, false, PH_BU);
+                alive = sync_grid(SYNC_LOCAL, PH_BU);
                 if (!alive) break;
                 for (u32 i = gtid; i < st.local_front; i += gthreads) {
                     const u32 u = fetch_frontier<MULTI>(K, E, st, side, i);
                     atomicOr(&f[u >> 5], 1u << (u & 31u));
                 }
                 if (MULTI) {
-                    alive = sync_point(SYNC_LOCAL, false, PH_BU);
+                    alive = sync_grid(SYNC_LOCAL, PH_BU);
                     if (!alive) break;
                     push_fbm_slice(K, E, side, st.fbm_cur[side], gtid, gthreads);
-                    alive = sync_point(SYNC_CROSS, false, PH_BU);
+                    alive = sync_grid(SYNC_CROSS, PH_BU);
                 } else {
-                    alive = sync_point(SYNC_LOCAL, false, PH_BU);
+                    alive = sync_grid(SYNC_LOCAL, PH_BU);
                 }
                 if (!alive) break;
             }
             expand_bu<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
             if (MULTI) {
-                alive = sync_point(SYNC_LOCAL, false, PH_BU);
+                alive = sync_grid(SYNC_LOCAL, PH_BU);
                 if (!alive) break;
                 push_fbm_slice(K, E, side, st.fbm_cur[side] ^ 1u, gtid, gthreads);
             }
-            alive = sync_point(SYNC_LEVEL, false, PH_BU);
+            alive = sync_grid(SYNC_LEVEL, PH_BU);
         }
     }
     if (!alive) return;   // aborted: the host must reset the context
@@ -704,7 +1206,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     // otherwise (and always with several ranks, whose filter bits are not logged) sweep the bitmap.
     {
         const u32 gtid = E.cta * BFS_THREADS + tid, gthreads = E.cpr * BFS_THREADS;
-        const u32 t0 = __ldcg(&C->q_tail[0]), t1 = __ldcg(&C->q_tail[1]);
+        const u32 t0 = __ldcg(&C->acc.q_tail[0]), t1 = __ldcg(&C->acc.q_tail[1]);
         if (!MULTI && (u64)(t0 + t1) * 8ull < (u64)E.nw) {
             for (u32 i = gtid; i < t0; i += gthreads) E.vis[__ldcg(E.q[0] + i) >> 5] = 0ull;
             for (u32 i = gtid; i < t1; i += gthreads) E.vis[__ldcg(E.q[1] + i) >> 5] = 0ull;
@@ -771,6 +1273,17 @@ int bfs_launch(const KParams& K, bool multi, cudaStream_t st) {
     count_launch();
     return 0;
 }
+
+#ifdef BIBFS_FINE_TRACE
+extern "C" int bibfs_debug_read(uint64_t* out, uint32_t* levels) {
+    cudaMemcpyFromSymbol(out, g_dbg, sizeof(u64) * 256 * 8);
+    cudaMemcpyFromSymbol(out + 256 * 8, g_dbg2, sizeof(u64) * 256 * 8);
+    cudaMemcpyFromSymbol(levels, g_dbg_level, 4);
+    u32 z = 0;
+    cudaMemcpyToSymbol(g_dbg_level, &z, 4);
+    return 0;
+}
+#endif
 
 int path_launch(const KParams& K, cudaStream_t st) {
     k_path<<<1, 64, 0, st>>>(K);

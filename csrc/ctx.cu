@@ -62,7 +62,7 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     c->multi = desc->nranks > 1;
     c->B = bibfs_block_size(desc->n, desc->nranks);
     if (c->d.max_path == 0) c->d.max_path = 1u << 16;
-    if (c->d.solo_threshold == 0) c->d.solo_threshold = 1024;
+    if (c->d.solo_threshold == 0 || c->d.solo_threshold > (u32)BFS_THREADS) c->d.solo_threshold = BFS_THREADS;   // one frontier vertex per thread
     if (c->d.bottom_up_div == 0) c->d.bottom_up_div = 24;
     if (c->d.watchdog_ms == 0) c->d.watchdog_ms = 4000;
     c->L = make_layout(c->B, desc->nranks, c->d.max_path);

@@ -82,6 +82,7 @@ __device__ __forceinline__ void st_peer_v4(u32* p, u32 a, u32 b, u32 c, u32 d) {
     asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void nanosleep(u32 ns) { asm volatile("nanosleep.u32 %0;" ::"r"(ns)); }
 
 // ---- mbarrier + 1-D bulk async copy (TMA engine, SASS UBLKCP) -----------------------------
@@ -121,6 +122,23 @@ __device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, u32 b
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// shared-memory atomics through the shared window (a generic-address atomic on a shared location
+// takes the slow generic path)
+__device__ __forceinline__ u32 atoms_add(u32* p, u32 v) {
+    u32 old;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(smem_addr(p)), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void reds_add(u32* p, u32 v) {
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(smem_addr(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ void reds_add64(unsigned long long* p, u64 v) {
+    asm volatile("red.shared.add.u64 [%0], %1;" ::"r"(smem_addr(p)), "l"(v) : "memory");
+}
+__device__ __forceinline__ void reds_min(u32* p, u32 v) {
+    asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(smem_addr(p)), "r"(v) : "memory");
+}
 
 // ---- clusters / DSMEM ---------------------------------------------------------------------
 __device__ __forceinline__ u32 cluster_ctarank() {

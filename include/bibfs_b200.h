@@ -205,6 +205,7 @@ typedef struct {
     uint32_t discovered; /* global vertices discovered                                      */
     uint64_t t_ns;       /* %globaltimer at the end of the level (rank-local)               */
     uint64_t edges;      /* adjacency entries inspected by this rank in this level          */
+    uint64_t t_expand_ns;/* %globaltimer when this rank finished expanding (sync starts)    */
 } bibfs_level_trace;
 int bibfs_ctx_trace(bibfs_ctx* ctx, uint32_t i, bibfs_level_trace* out, uint32_t cap, uint32_t* count);
 
