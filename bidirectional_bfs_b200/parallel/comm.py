@@ -1,0 +1,75 @@
+"""One-process-per-GPU deployment of the fused multi-GPU search (torchrun / torch.distributed).
+
+torch.distributed (NCCL or gloo) is used for PLUMBING only: exchanging the 64-byte CUDA IPC
+handles of the per-rank state arenas at start-up and an occasional barrier.  The per-level
+frontier exchange, meet test and termination run inside the persistent kernels over the mapped
+peer memory (csrc/bfs_dev.cu) — no NCCL / MPI call per level, unlike the reference's
+MPI_Allreduce(BOR) + two scalar allreduces per level (v4/mpi_bas.cpp:85,107,124).
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+
+from .._lib import F_NO_PATH
+from ..graph import Graph
+from ..ops.search import PathResult, SearchContext
+
+
+def init_distributed(backend: str | None = None) -> tuple[int, int, int]:
+    """Initialise torch.distributed from the torchrun environment; returns (rank, world, local_rank)."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if torch.cuda.is_available():
+            torch.cuda.set_device(local)
+        kw = {}
+        if backend == "nccl":
+            kw["device_id"] = torch.device("cuda", local)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world, **kw)
+    return rank, world, local
+
+
+class DistributedSolver:
+    """Rank-local handle of a P-GPU search; every rank must make the same calls in the same order."""
+    variant = "multi-gpu"
+
+    def __init__(self, graph: Graph, **ctx_kw):
+        if not dist.is_initialized():
+            raise RuntimeError("torch.distributed is not initialised (use init_distributed())")
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        if graph.nranks != self.world or list(graph.shards) != [self.rank]:
+            raise ValueError("graph must hold exactly this rank's shard of a world-sized partition")
+        self.graph = graph
+        with torch.cuda.device(graph.device):
+            self.ctx = SearchContext(graph, self.rank, 1, **ctx_kw)
+            handles = [None] * self.world
+            dist.all_gather_object(handles, self.ctx.ipc_handle(0))
+            for r, h in enumerate(handles):
+                if r != self.rank:
+                    self.ctx.attach_ipc(r, h)
+        dist.barrier()
+
+    def launch(self, src, dst, flags=0, pinned_query=None):
+        self.ctx.launch(src, dst, flags, pinned_query)
+
+    def fetch(self, src, dst, want_path=True) -> PathResult:
+        return self.ctx.fetch(src, dst, want_path, self.variant)
+
+    def query(self, src, dst, want_path=True, flags=0, pinned_query=None) -> PathResult:
+        if not want_path:
+            flags |= F_NO_PATH
+        self.ctx.launch(src, dst, flags, pinned_query)
+        return self.ctx.fetch(src, dst, want_path, self.variant)
+
+    def close(self):
+        torch.cuda.synchronize(self.graph.device)
+        dist.barrier()
+        self.ctx.close()
