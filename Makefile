@@ -15,7 +15,7 @@ OUTDIR    := bidirectional_bfs_b200/_native
 LIB       := $(OUTDIR)/libbibfs_b200.so
 CLI       := bin/bibfs
 
-CU_SRCS   := csrc/gen_dev.cu csrc/csr_dev.cu csrc/bfs_dev.cu csrc/ctx.cu csrc/naive_dev.cu csrc/msbfs_dev.cu
+CU_SRCS   := csrc/gen_dev.cu csrc/csr_dev.cu csrc/bfs_dev.cu csrc/ctx.cu csrc/naive_dev.cu csrc/msbfs_dev.cu csrc/scan_noalloc.cu
 CPP_SRCS  := csrc/error.cpp csrc/host_io.cpp csrc/host_graph.cpp csrc/cpu_serial.cpp csrc/cpu_ranks.cpp
 CU_OBJS   := $(patsubst csrc/%.cu,$(BUILD)/%.o,$(CU_SRCS))
 CPP_OBJS  := $(patsubst csrc/%.cpp,$(BUILD)/%.o,$(CPP_SRCS))

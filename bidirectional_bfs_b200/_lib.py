@@ -95,6 +95,8 @@ def _declare(lib):
         "bibfs_csr_fill_device": (C.c_int, [u32, u64, vp, P(GenSpec), u32, u32, vp, vp, vp, C.c_size_t, C.c_int, vp]),
         "bibfs_scan_workspace_bytes": (C.c_size_t, [u64]),
         "bibfs_scan_u32_device": (C.c_int, [vp, vp, u64, vp, C.c_size_t, vp]),
+        "bibfs_scan_noalloc_max_count": (u64, []),
+        "bibfs_scan_u32_device_noalloc": (C.c_int, [vp, vp, u64, vp]),
         "bibfs_serial": (C.c_int, [u32, vp, vp, u32, u32, C.c_int, P(Result), vp, u32]),
         "bibfs_cpu_ranks": (C.c_int, [u32, vp, vp, u32, u32, C.c_int, P(Result), vp, u32]),
         "bibfs_validate_path": (C.c_int, [u32, vp, vp, u32, u32, vp, u32]),

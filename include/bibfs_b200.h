@@ -103,6 +103,25 @@ int bibfs_csr_fill_device(uint32_t n, uint64_t m, const uint32_t* d_edges, const
 size_t bibfs_scan_workspace_bytes(uint64_t count);
 int bibfs_scan_u32_device(const uint32_t* d_in, uint64_t* d_out, uint64_t count,
                           void* d_ws, size_t ws_bytes, void* stream);
+/* The same scan for callers that cannot allocate (no counterpart in the reference, which
+ * allocates everything with cudaMalloc up front, v4/comp.cu:49-73).  Meant for code that is
+ * handed only its inputs and outputs — a custom operator inside an inference server or another
+ * framework's stream pipeline — and must neither exceed a memory budget fixed at start-up nor
+ * call cudaMalloc/cudaFree, which can synchronise the device under the host application.
+ * The scratch is a fixed array inside this library's device image instead:
+ *   - every GPU that loads the library holds it (128 KB) from load until the process exits;
+ *   - count must be <= bibfs_scan_noalloc_max_count() (2^26); larger inputs are rejected with an
+ *     error, use bibfs_scan_u32_device with your own scratch for those;
+ *   - the call performs no cudaMalloc / cudaFree and calls no allocating routine;
+ *   - the FIRST call on each device looks up the array's device address (a one-off runtime
+ *     query, with that device current); make that first call before starting any stream capture;
+ *   - all calls on a device share the array and it keeps the previous call's contents (nothing
+ *     in it needs to start at zero, each call overwrites what it reads); two calls that overlap
+ *     on the GPU — different streams, or different host threads — race on it and give wrong
+ *     results: serialise them on one stream.
+ * d_in / d_out are the caller's, exactly as for bibfs_scan_u32_device (d_out has count+1 entries). */
+uint64_t bibfs_scan_noalloc_max_count(void);
+int bibfs_scan_u32_device_noalloc(const uint32_t* d_in, uint64_t* d_out, uint64_t count, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * results
