@@ -30,9 +30,14 @@ struct SpinBarrier {
             count.store(0, std::memory_order_relaxed);
             gen.store(g + 1, std::memory_order_release);
         } else {
+            // levels last microseconds: spin (with a pause hint) before giving the core away
             u32 spins = 0;
-            while (gen.load(std::memory_order_acquire) == g)
-                if (++spins > 256) std::this_thread::yield();
+            while (gen.load(std::memory_order_acquire) == g) {
+#if defined(__x86_64__) || defined(__i386__)
+                __builtin_ia32_pause();
+#endif
+                if (++spins > 4000) std::this_thread::yield();   // oversubscribed box: let the other ranks run
+            }
         }
     }
 };
@@ -66,7 +71,11 @@ struct Shared {
     }
 };
 
-void worker(Shared& S, SpinBarrier& bar, u32 rank) {
+void worker(Shared& S, SpinBarrier& bar, u32 rank, std::chrono::steady_clock::time_point* t_start) {
+    // start line: the timed region begins when every rank is up (v2 starts MPI_Wtime after MPI_Init
+    // and the graph broadcast, second_try.cpp:66)
+    bar.wait();
+    if (t_start) *t_start = std::chrono::steady_clock::now();
     while (true) {
         const int s = S.side, o = 1 - s;
         if (S.done) return;
@@ -149,12 +158,12 @@ extern "C" int bibfs_cpu_ranks(uint32_t n, const uint64_t* row_ptr, const uint32
     S.vis[1][dst >> 6].fetch_or(1ull << (dst & 63));
     SpinBarrier bar((u32)ranks);
 
-    auto t0 = std::chrono::steady_clock::now();
+    std::chrono::steady_clock::time_point t0;
     std::vector<std::thread> th;
-    for (int r = 1; r < ranks; ++r) th.emplace_back(worker, std::ref(S), std::ref(bar), (u32)r);
-    worker(S, bar, 0);
-    for (auto& t : th) t.join();
+    for (int r = 1; r < ranks; ++r) th.emplace_back(worker, std::ref(S), std::ref(bar), (u32)r, nullptr);
+    worker(S, bar, 0, &t0);
     auto t1 = std::chrono::steady_clock::now();
+    for (auto& t : th) t.join();
 
     res->search_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
     res->levels = S.levels;

@@ -1,0 +1,39 @@
+"""torchrun correctness check of the one-process-per-GPU path against the serial oracle.
+   python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 scripts/dist_check.py"""
+import sys, time
+import numpy as np, torch
+sys.path.insert(0, ".")
+import bidirectional_bfs_b200 as bb
+from bidirectional_bfs_b200.parallel import comm
+import torch.distributed as dist
+
+rank, world, local = comm.init_distributed()
+dev = torch.device("cuda", local)
+torch.cuda.set_device(dev)
+ok = True
+for name, spec in (("er", bb.er_spec(30000, 2.2 / 30000, seed=1)), ("rmat", bb.rmat_spec(15, edgefactor=16, seed=3)),
+                   ("grid", bb.grid_spec(150, 100)), ("er_dense", bb.er_spec(5000, 10.0 / 5000, seed=2))):
+    g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
+    solver = comm.DistributedSolver(g)
+    oracle = bb.SerialSolver(bb.Graph.generate(spec), policy=1)
+    rng = np.random.default_rng(5)
+    pairs = [(0, spec.n - 1), (3, 3)] + [(int(rng.integers(spec.n)), int(rng.integers(spec.n))) for _ in range(25)]
+    for flags in (0, 2, 2 | 8):
+        t0 = time.time()
+        for s, t in pairs:
+            want = oracle.query(s, t, want_path=False).length
+            r = solver.query(s, t, flags=flags)
+            if r.length != want:
+                ok = False
+                print(f"[rank {rank}] MISMATCH {name} flags={flags} {s}->{t}: got {r.length} want {want}", flush=True)
+            elif want is not None and rank == 0:
+                bb.validate_path(oracle.graph, s, t, r.path, want)
+        if rank == 0:
+            print(f"{name} flags={flags}: {len(pairs)} queries ok={ok} {time.time()-t0:.2f}s last search_ms={r.search_ms:.4f}", flush=True)
+    solver.close()
+t = torch.tensor([0 if ok else 1], device=dev)
+dist.all_reduce(t)
+if rank == 0:
+    print("DIST_CHECK", "PASS" if t.item() == 0 else "FAIL", "world", world, flush=True)
+dist.destroy_process_group()
+sys.exit(0 if t.item() == 0 else 1)
