@@ -848,81 +848,108 @@ __device__ __noinline__ void solo_push_hub(const KParams& K, const Env& E, Smem&
 
 // Consecutive solo levels of a single-rank search, one frontier vertex per thread.  This is the
 // latency path (reference-sized graphs finish here; a 4-digit-path grid spends thousands of levels
-// here), so it is written for a short instruction stream and a short dependent-memory chain:
-//   frontier vertex (shared mirror) -> row offsets (L2, prefetched at discovery) -> up to 4 column
-//   loads in flight -> up to 4 claims in flight -> one shared-memory cursor atomic per warp.
-// State and accumulators stay in shared memory; nothing is published until the grid is needed.
+// here).  A single level is a chain of dependent memory operations executed by a handful of
+// warps, so what counts is the length of that chain and the number of instructions on it:
+//   one 16-byte shared load (level descriptor) -> frontier vertex (shared mirror) -> row offsets
+//   (L2, prefetched at discovery) -> up to 8 column loads in flight -> up to 8 claims in flight
+//   -> one shared-memory cursor atomic per discovering lane -> stores.
+// The level bookkeeping runs in registers of thread 0; the other threads only ever read the
+// 16-byte descriptor.  Nothing is published to the grid until it is needed.
+struct SoloLevel {          // written by thread 0 at the end of a level, read by everybody
+    u32 side_flags;         // bit 0 side, bit 1 frontier is in the shared mirror, bit 2 which mirror buffer, bit 3 stop
+    u32 total;              // frontier vertices
+    u32 q_lo;               // window start in the global queue (used when not mirrored)
+    u32 base_tail;          // queue cursor at the start of the level (== window end)
+};
+static_assert(sizeof(SoloLevel) == 16, "one LDS.128");
+
+constexpr int SW = 8;       // adjacency entries per lane per round
+
 __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
     const u32 tid = threadIdx.x, lane = tid & 31;
     LevelState& st = sm.st;
     E.solo = true; E.A = &sm.acc; E.sA = &sm.acc; E.filter = false; E.s_hub = &sm.hub;
+    __shared__ __align__(16) SoloLevel s_lv;
+    // thread 0 keeps the level state in registers across levels
+    u32 nf0 = st.nf[0], nf1 = st.nf[1], d0 = st.depth[0], d1 = st.depth[1], levels = st.levels;
+    u32 qlo0 = st.q_lo[0], qlo1 = st.q_lo[1], qhi0 = st.q_hi[0], qhi1 = st.q_hi[1];
+    u32 cur0 = sm.qcur[0], cur1 = sm.qcur[1], val0 = sm.qvalid[0], val1 = sm.qvalid[1];
+    u64 pend_edges = 0, pend_vis = 0;
+    if (tid == 0) {
+        const u32 sd = st.side;
+        SoloLevel lv;
+        lv.side_flags = sd | ((sd ? val1 : val0) ? 2u : 0u) | ((sd ? cur1 : cur0) ? 4u : 0u);
+        lv.total = st.local_front;
+        lv.q_lo = sd ? qlo1 : qlo0;
+        lv.base_tail = sd ? qhi1 : qhi0;
+        s_lv = lv;
+    }
+    __syncthreads();
     while (true) {
-        const u32 side = st.side;
-        const u32 total = st.local_front;
-        const u32 cur = sm.qcur[side];
-        const bool from_mirror = sm.qvalid[side] != 0;
+        DBG_STAMP(0, tid);
+        const uint4 raw = *reinterpret_cast<const uint4*>(&s_lv);
+        const u32 side = raw.x & 1u, total = raw.y, base_tail = raw.w;
+        if (raw.x & 8u) break;
+        const u32 cur = (raw.x >> 2) & 1u;
         u32* const out = sm.q[side][cur ^ 1u];
-        const u32 base_tail = st.q_hi[side];
-        const u32 qlo = st.q_lo[side];
         const u32 sh = 32u * side, osh = 32u - sh;
-        E.sq = out; E.sq_base = base_tail;
         u32 u = 0;
         u64 r0 = 0, r1 = 0;
         if (tid < total) {
-            u = from_mirror ? sm.q[side][cur][tid] : __ldcg(E.q[side] + qlo + tid);
+            u = (raw.x & 2u) ? sm.q[side][cur][tid] : __ldcg(E.q[side] + raw.z + tid);
             r0 = __ldg(E.row_ptr + (u - E.lo));
             r1 = __ldg(E.row_ptr + (u - E.lo) + 1);
         }
-        u64 deg = r1 - r0;
-        const u64 t_begin = (K.flags & BIBFS_F_TRACE) ? ptx::globaltimer_ns() : 0ull;
-        (void)t_begin;
-        // per-warp edge count
-        {
-            u32 d32 = (u32)(deg > 0xFFFFFFFFull ? 0xFFFFFFFFull : deg);
-            const u32 wsum = __reduce_add_sync(FULL, d32);
-            if (lane == 0 && wsum) ptx::reds_add64(&sm.acc.edges, wsum);
-        }
+        u32 deg = (u32)min(r1 - r0, (u64)0xFFFFFFFFu);
+        DBG_STAMP(1, deg);
         if (deg >= HUB_ROW) { solo_push_hub(K, E, sm, u, r0, r1); deg = 0; }
-        // rows shorter than a warp: each lane walks its own row, 4 entries at a time
-        const u32 sdeg = deg < 32 ? (u32)deg : 0u;
-        const u32 wmax = __reduce_max_sync(FULL, sdeg);
-        for (u32 e0 = 0; e0 < wmax; e0 += 4) {
-            u32 v[4];
-            u64 old[4];
-            bool isnew[4];
+        u32 sdeg = deg < 32u ? deg : 0u;
+        u32 nedges = deg;
+        DBG_STAMP(2, sdeg);
+        // rows shorter than a warp: each lane walks its own row, SW entries per round
+        for (u32 e0 = 0; __any_sync(FULL, e0 < sdeg); e0 += SW) {
+            u32 v[SW];
+            u64 old[SW];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) v[k] = (e0 + k < sdeg) ? __ldg(E.col + r0 + e0 + k) : 0xFFFFFFFFu;
+            for (int k = 0; k < SW; ++k) v[k] = (e0 + k < sdeg) ? __ldg(E.col + r0 + e0 + k) : 0u;
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < SW; ++k)
                 old[k] = (e0 + k < sdeg) ? ptx::atom_or_gpu(&E.vis[v[k] >> 5], 1ull << ((v[k] & 31u) + sh)) : ~0ull;
-            u32 m[4], tot = 0;
+            DBG_STAMP(3, v[0] + v[SW - 1]);
+            u32 newmask = 0, meetmask = 0;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                isnew[k] = !((old[k] >> ((v[k] & 31u) + sh)) & 1ull);
-                m[k] = __ballot_sync(FULL, isnew[k]);
-                tot += __popc(m[k]);
+            for (int k = 0; k < SW; ++k) {
+                const u64 w = old[k] >> (v[k] & 31u);
+                const u32 isnew = ((u32)(w >> sh) & 1u) ^ 1u;
+                newmask |= isnew << k;
+                meetmask |= (isnew & (u32)(w >> osh)) << k;
             }
-            if (tot) {
-                u32 base = 0;
-                if (lane == 0) base = ptx::atoms_add(&sm.acc.q_tail[side], tot);
-                base = __shfl_sync(FULL, base, 0);
+            DBG_STAMP(4, newmask);
+            if (newmask) {
+                const u32 cntnew = __popc(newmask);
+                u32 slot = ptx::atoms_add(&sm.acc.q_tail[side], cntnew);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    if (isnew[k]) {
-                        const u32 slot = base + __popc(m[k] & lanemask_lt());
+                for (int k = 0; k < SW; ++k) {
+                    if ((newmask >> k) & 1u) {
                         E.q[side][slot] = v[k];
                         E.parent[side][v[k] - E.lo] = u;
                         if (slot - base_tail < SOLO_CAP) out[slot - base_tail] = v[k];
                         ptx::prefetch_l2(E.row_ptr + (v[k] - E.lo));
-                        if ((old[k] >> ((v[k] & 31u) + osh)) & 1ull) ptx::reds_min(&sm.acc.meet_local, v[k]);
+                        ++slot;
                     }
-                    base += __popc(m[k]);
+                }
+                if (meetmask) {
+#pragma unroll
+                    for (int k = 0; k < SW; ++k)
+                        if ((meetmask >> k) & 1u) ptx::reds_min(&sm.acc.meet_local, v[k]);
                 }
             }
         }
+        DBG_STAMP(5, sdeg);
         // rows of a warp's length or more (below the hub threshold): the warp walks them together
-        u32 big = __ballot_sync(FULL, deg >= 32);
+        u32 big = __ballot_sync(FULL, deg >= 32u);
         if (big) {
+            E.sq = out; E.sq_base = base_tail;
             u32 cnt = 0;
             while (big) {
                 const u32 sl = __ffs(big) - 1;
@@ -932,10 +959,19 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
                 expand_range<false>(K, E, side, uu, rb, re, cnt);
             }
         }
+        // per-warp edge count (statistics only, off the critical path)
+        {
+            const u32 wsum = __reduce_add_sync(FULL, nedges);
+            if (lane == 0 && wsum) ptx::reds_add64(&sm.acc.edges, wsum);
+        }
         __syncthreads();
-        // ---- level end: one thread, shared memory only
+        DBG_STAMP(6, tid);
+        // ---- level end: thread 0, state in registers
         if (tid == 0) {
             Ctrl* C = E.C;
+            const u32 tail = sm.acc.q_tail[side];
+            const u32 found = tail - base_tail;
+            u32 stop = 0;
             if (sm.hub) {
                 // the level is not over: publish and let the grid expand the deferred rows
                 const u64 hp = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&C->hub_packed));
@@ -944,49 +980,64 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
                 st.prev_phase = PH_TD_SOLO;
                 st.phase = PH_TD_HUB;
                 C->hub_packed = 0;
-                sm.acc.new_count = sm.acc.q_tail[side] - base_tail;
-                sm.qcur[side] ^= 1u; sm.qvalid[side] = 0; sm.hub = 0;
+                sm.acc.new_count = found;
+                sm.hub = 0;
+                if (side) { cur1 ^= 1u; val1 = 0; } else { cur0 ^= 1u; val0 = 0; }
+                stop = 1;
             } else {
-                const u32 tail = sm.acc.q_tail[side];
-                const u32 found = tail - base_tail;
                 const u32 meet = sm.acc.meet_local;
-                const u32 expanded = st.nf[side];
                 const u64 ed = sm.acc.edges;
-                st.nf[side] = found;
-                st.depth[side] += 1;
-                st.levels += 1;
-                st.fbm_valid[side] = 0;
-                st.q_lo[side] = base_tail;
-                st.q_hi[side] = tail;
-                sm.pend_edges += ed;
-                sm.pend_visited += found;
-                sm.acc.edges = 0; sm.acc.new_count = 0; sm.acc.meet_local = NO_V;
-                sm.qcur[side] ^= 1u;
-                sm.qvalid[side] = found <= SOLO_CAP ? 1u : 0u;
+                const u32 expanded = side ? nf1 : nf0;
+                if (side) { nf1 = found; d1 += 1; qlo1 = base_tail; qhi1 = tail; cur1 ^= 1u; val1 = found <= SOLO_CAP; }
+                else      { nf0 = found; d0 += 1; qlo0 = base_tail; qhi0 = tail; cur0 ^= 1u; val0 = found <= SOLO_CAP; }
+                levels += 1;
+                pend_edges += ed; pend_vis += found;
+                sm.acc.edges = 0;
                 if (K.flags & BIBFS_F_TRACE) trace_level(K, E, side, PH_TD_SOLO, expanded, found, ed, ptx::globaltimer_ns());
                 if (meet != NO_V) {
-                    st.length = (i32)(st.depth[0] + st.depth[1]);
+                    sm.acc.meet_local = NO_V;
+                    st.length = (i32)(d0 + d1);
                     st.meet = meet;
                     st.phase = PH_DONE;
+                    stop = 1;
                 } else {
-                    const u32 ns = st.nf[0] <= st.nf[1] ? 0u : 1u;
+                    const u32 ns = nf0 <= nf1 ? 0u : 1u;           // smaller frontier first, ties -> source (v1)
+                    const u32 nfn = ns ? nf1 : nf0;
+                    const u32 lf = ns ? qhi1 - qlo1 : qhi0 - qlo0;
                     st.side = ns;
-                    const u32 lf = st.q_hi[ns] - st.q_lo[ns];
                     st.local_front = lf;
-                    if (st.nf[ns] == 0) { st.length = -1; st.phase = PH_DONE; }
-                    else if (lf > K.solo_threshold || (K.flags & (BIBFS_F_FORCE_BU | BIBFS_F_FORCE_GRID))) decide_next(K, st);
-                    else if (!(K.flags & BIBFS_F_FORCE_TD) && K.bu_div != 0xFFFFFFFFu && st.nf[ns] > K.n / K.bu_div) decide_next(K, st);
+                    if (nfn == 0) { st.length = -1; st.phase = PH_DONE; stop = 1; }
+                    else if (lf > K.solo_threshold || (K.flags & (BIBFS_F_FORCE_BU | BIBFS_F_FORCE_GRID)) ||
+                             (!(K.flags & BIBFS_F_FORCE_TD) && K.bu_div != 0xFFFFFFFFu && nfn > K.n / K.bu_div)) stop = 2;
+                    else {
+                        SoloLevel lv;
+                        lv.side_flags = ns | ((ns ? val1 : val0) ? 2u : 0u) | ((ns ? cur1 : cur0) ? 4u : 0u);
+                        lv.total = lf;
+                        lv.q_lo = ns ? qlo1 : qlo0;
+                        lv.base_tail = ns ? qhi1 : qhi0;
+                        s_lv = lv;
+                    }
                 }
             }
-            if (st.phase != PH_TD_SOLO) {
-                C->edges_total += sm.pend_edges;
-                C->res.vertices_visited += sm.pend_visited;
-                sm.pend_edges = 0; sm.pend_visited = 0;
+            if (stop) {
+                // write the register state back before anyone else looks at it
+                st.nf[0] = nf0; st.nf[1] = nf1; st.depth[0] = d0; st.depth[1] = d1; st.levels = levels;
+                st.q_lo[0] = qlo0; st.q_lo[1] = qlo1; st.q_hi[0] = qhi0; st.q_hi[1] = qhi1;
+                st.fbm_valid[0] = 0; st.fbm_valid[1] = 0;
+                sm.qcur[0] = cur0; sm.qcur[1] = cur1; sm.qvalid[0] = val0; sm.qvalid[1] = val1;
+                sm.acc.new_count = (st.phase == PH_TD_HUB) ? sm.acc.new_count : 0;
+                if (stop == 2) decide_next(K, st);
+                C->edges_total += pend_edges;
+                C->res.vertices_visited += pend_vis;
                 if (st.phase == PH_DONE) write_result(K, C, st);
+                s_lv.side_flags = 8u;
             }
         }
+        DBG_STAMP(7, st.phase);
+#ifdef BIBFS_FINE_TRACE
+        if (blockIdx.x == 0 && threadIdx.x == 0) g_dbg_level++;
+#endif
         __syncthreads();
-        if (st.phase != PH_TD_SOLO) return;
     }
 }
 
