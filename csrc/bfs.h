@@ -12,7 +12,8 @@
 //   fbm   u32[2][2][NW]       frontier bitmaps for bottom-up levels (side x double buffer), replicated
 //   parent u32[2][B]          BFS-tree parent of owned vertices per side (global ids)
 //   q     u32[2][B]           append-only queue of owned vertices discovered locally, per side
-//   rq    u32[2][P][B]        (P>1) per-sender segments: owned vertices discovered by rank p
+//   rq    u64[2][P][B]        (P>1) per-sender segments: owned vertices discovered by rank p, each entry
+//                             = vertex | epoch tag << 32 so the owner can tell a landed entry from a stale one
 //   path  u32[max_path]       path output (rank 0 of the context group writes it)
 //   trace LevelTrace[TRACE_CAP]
 // The frontier of a side is a WINDOW [lo,hi) of its queue plus one window per sender segment;
@@ -25,15 +26,22 @@ namespace bibfs {
 constexpr u32 MAXR = BIBFS_MAX_RANKS;
 constexpr u32 NO_V = 0xFFFFFFFFu;
 constexpr u32 TRACE_CAP = 32768;
-constexpr int BFS_THREADS = 1024;
+constexpr int BFS_THREADS = 512;     // 512 threads x 1 CTA per SM: up to 128 registers, so eight claims per lane stay in flight
 
 enum Phase : u32 { PH_TD_SOLO = 0, PH_TD_GRID = 1, PH_BU = 2, PH_DONE = 3, PH_TD_HUB = 4 };
 
-struct Slot {          // one 16-byte store per peer per level
+struct Slot {          // what a rank tells every peer at the end of a level
     u32 count;         // vertices this rank discovered in the level (local + remote)
     u32 meet;          // smallest meeting vertex it saw, NO_V if none
     u32 rq_tail;       // cumulative entries it has appended to the receiver's segment (this side)
-    u32 edges;         // adjacency entries it inspected (low 32 bits, trace only)
+    u32 edges;         // adjacency entries it inspected (low 32 bits, statistics)
+};
+// On the wire every 32-bit field travels in its own 8-byte word together with the 32-bit epoch
+// tag of the exchange ("LL" style): the receiver polls the words until all tags match, so no
+// release fence / acquire load pair is needed (fence.acq_rel.sys costs ~1.35 us on B200 and an
+// acquire/release ping-pong 5.3 us round trip, against 2.4 us for relaxed stores and polls).
+struct LSlot {
+    u64 w[4];
 };
 
 struct LevelState {
@@ -44,6 +52,7 @@ struct LevelState {
     u32 nf[2];                 // global frontier size per side
     u32 q_lo[2], q_hi[2];      // local queue window per side
     u32 rq_lo[2][MAXR], rq_hi[2][MAXR];
+    u32 rq_tag[2];             // epoch tag carried by the entries of the current rq windows, per side
     u32 fbm_cur[2], fbm_valid[2];
     u32 local_front;           // vertices this rank expands in the coming level
     u32 hub_entries, hub_chunks; // hub phase work (PH_TD_HUB)
@@ -93,9 +102,8 @@ struct Ctrl {
     // local grid barrier
     alignas(128) u32 bar_count;
     alignas(128) u64 bar_gen;            // (launch seq << 32) | wake-ups
-    // cross-rank barrier flags: arrive[p] is written by rank p
-    alignas(128) u64 arrive[MAXR];
-    alignas(128) Slot slot[2][MAXR];     // [epoch parity][sender]
+    // cross-rank exchange: slot[parity][p] is written by rank p (tagged words, relaxed stores)
+    alignas(128) LSlot slot[2][MAXR];    // [epoch parity][sender]
     // accumulators, reset by the leader each level / query
     alignas(128) Acc acc;
     unsigned long long hub_packed;       // (entries << 40) | chunks, appended atomically
@@ -123,7 +131,7 @@ inline Layout make_layout(u32 B, u32 P, u32 max_path) {
     L.off_fbm = o;    o += al((size_t)L.nw * 4 * 4);
     L.off_parent = o; o += al((size_t)B * 4 * 2);
     L.off_q = o;      o += al((size_t)B * 4 * 2);
-    L.off_rq = o;     o += (P > 1) ? al((size_t)B * 4 * 2 * P) : 0;
+    L.off_rq = o;     o += (P > 1) ? al((size_t)B * 8 * 2 * P) : 0;   // tagged 8-byte entries
     L.off_path = o;   o += al((size_t)max_path * 4);
     L.off_trace = o;  o += al((size_t)TRACE_CAP * sizeof(bibfs_level_trace));
     L.off_hub = o;    o += al((size_t)HUB_CAP * sizeof(HubEntry));

@@ -88,6 +88,9 @@ struct Env {
     u32 sq_base;       // queue index of sq[0]
     u32* s_hub;        // solo mode: shared flag "a hub row was deferred" (else null)
     bool filter;       // read the visited word before the atomic (pays off on large frontiers only)
+    u32 tag;           // epoch tag stamped on entries sent to other ranks in the current level
+    u32* s_sent;       // solo mode: shared copy of Ctrl::sent ([2][MAXR])
+    u32* s_rnew;       // solo mode: shared counter of vertices discovered at other ranks
     u64* vis;
     u32* parent[2];
     u32* q[2];
@@ -106,8 +109,8 @@ __device__ __forceinline__ u32* parent_of(const KParams& K, u32 r, u32 side) {
 __device__ __forceinline__ u32* q_of(const KParams& K, u32 r, u32 side) {
     return reinterpret_cast<u32*>(K.arena[r] + K.L.off_q) + (size_t)side * K.B;
 }
-__device__ __forceinline__ u32* rq_of(const KParams& K, u32 r, u32 side, u32 sender) {
-    return reinterpret_cast<u32*>(K.arena[r] + K.L.off_rq) + ((size_t)side * K.P + sender) * K.B;
+__device__ __forceinline__ u64* rq_of(const KParams& K, u32 r, u32 side, u32 sender) {
+    return reinterpret_cast<u64*>(K.arena[r] + K.L.off_rq) + ((size_t)side * K.P + sender) * K.B;
 }
 __device__ __forceinline__ bibfs_level_trace* trace_of(const KParams& K, u32 r) {
     return reinterpret_cast<bibfs_level_trace*>(K.arena[r] + K.L.off_trace);
@@ -165,12 +168,18 @@ __device__ bool wait_count(Ctrl* C, u32 want, u64 deadline) {
     return true;
 }
 
-__device__ bool wait_arrive(Ctrl* C, u32 p, u64 want, u64 deadline) {
+// poll the four tagged words a peer writes into this rank's slot until they carry `tag`
+__device__ bool wait_slot(Ctrl* C, const LSlot* sl, u32 tag, Slot& out, u64 deadline) {
     u32 spins = 0;
-    while (ptx::ld_acquire_sys(&C->arrive[p]) < want) {
+    while (true) {
+        const u64 a = ptx::ld_relaxed_sys(&sl->w[0]), b = ptx::ld_relaxed_sys(&sl->w[1]);
+        const u64 c = ptx::ld_relaxed_sys(&sl->w[2]), d = ptx::ld_relaxed_sys(&sl->w[3]);
+        if ((u32)(a >> 32) == tag && (u32)(b >> 32) == tag && (u32)(c >> 32) == tag && (u32)(d >> 32) == tag) {
+            out.count = (u32)a; out.meet = (u32)b; out.rq_tail = (u32)c; out.edges = (u32)d;
+            return true;
+        }
         if (++spins > 64 && (spins & 255u) == 0 && expired(C, deadline)) return false;
     }
-    return true;
 }
 
 // accumulators are updated with atomics that live in L2: read them around the L1
@@ -220,27 +229,30 @@ __device__ __noinline__ void write_result(const KParams& K, Ctrl* C, const Level
 }
 
 // Cross-rank handshake executed by the leader warp (lanes 0..P-1 each talk to one peer).
-// Writes `mine` into slot[parity][me] of every peer, raises arrive[me] there, waits until every
-// peer has done the same here and returns the peer's slot in `got`.  Returns false on timeout.
+// Writes `mine` as four tagged words into slot[parity][me] of every peer with relaxed system-scope
+// stores and polls this rank's own slots until every peer's words carry the epoch tag.  `fenced`
+// adds a fence.acq_rel.sys on both sides: needed only when bulk data that is read with plain loads
+// (bottom-up bitmap slices, parents at the end of the query) must be ordered with the exchange;
+// queue entries are tagged themselves and need no fence.  Returns false on timeout.
 template <bool MULTI>
-__device__ __noinline__ bool cross_exchange(const KParams& K, const Env& E, LevelState& G, const Slot mine_for_lane, Slot& got, u64 deadline) {
+__device__ __noinline__ bool cross_exchange(const KParams& K, const Env& E, LevelState& G, const Slot mine_for_lane, Slot& got, u64 deadline,
+                                            bool fenced) {
     const u32 lane = threadIdx.x & 31;
     got = mine_for_lane;
     if (!MULTI) return true;
     const u64 epoch = G.xepoch + 1;
     const u32 par = (u32)(epoch & 1);
+    const u64 tag = (u64)(u32)epoch << 32;
     bool ok = true;
     if (lane < K.P) {
-        Ctrl* PC = ctrl_of(K, lane);
-        ptx::st_peer_v4(reinterpret_cast<u32*>(&PC->slot[par][E.me]), mine_for_lane.count, mine_for_lane.meet,
-                        mine_for_lane.rq_tail, mine_for_lane.edges);
-        ptx::fence_sys();
-        ptx::st_release_sys(&PC->arrive[E.me], epoch);
-        ok = wait_arrive(E.C, lane, epoch, deadline);
-        if (ok) {
-            const volatile Slot* s = &E.C->slot[par][lane];
-            got.count = s->count; got.meet = s->meet; got.rq_tail = s->rq_tail; got.edges = s->edges;
-        }
+        if (fenced) ptx::fence_sys();
+        LSlot* dst = &ctrl_of(K, lane)->slot[par][E.me];
+        ptx::st_relaxed_sys(&dst->w[0], tag | mine_for_lane.count);
+        ptx::st_relaxed_sys(&dst->w[1], tag | mine_for_lane.meet);
+        ptx::st_relaxed_sys(&dst->w[2], tag | mine_for_lane.rq_tail);
+        ptx::st_relaxed_sys(&dst->w[3], tag | mine_for_lane.edges);
+        ok = wait_slot(E.C, &E.C->slot[par][lane], (u32)epoch, got, deadline);
+        if (fenced) ptx::fence_sys();
     } else {
         got.count = 0; got.meet = NO_V; got.rq_tail = 0; got.edges = 0;
     }
@@ -287,7 +299,8 @@ __device__ __noinline__ bool leader_sync(const KParams& K, const Env& E, LevelSt
     const u64 my_edges = A.edges;
     mine.edges = (u32)my_edges;
     Slot got;
-    const bool ok = cross_exchange<MULTI>(K, E, G, mine, got, deadline);
+    const bool fenced = (level_mode == PH_BU);     // bitmap slices were pushed with plain stores
+    const bool ok = cross_exchange<MULTI>(K, E, G, mine, got, deadline, fenced);
     if (!MULTI && lane != 0) { got.count = 0; got.meet = NO_V; got.edges = 0; }   // single rank: lane 0 holds the totals
     if (!ok) {
         if (lane == 0) {
@@ -312,6 +325,7 @@ __device__ __noinline__ bool leader_sync(const KParams& K, const Env& E, LevelSt
         G.rq_lo[side][lane] = G.rq_hi[side][lane];
         G.rq_hi[side][lane] = got.rq_tail;
     }
+    if (MULTI && lane == 0) G.rq_tag[side] = (u32)G.xepoch;    // the tag this level's senders stamped
     __syncwarp();
     DBG_STAMP2(1, total + meetmin);
     if (lane == 0) {
@@ -342,8 +356,16 @@ __device__ __noinline__ bool leader_sync(const KParams& K, const Env& E, LevelSt
         } else {
             decide_next(K, G);
         }
-        if (G.phase == PH_DONE) write_result(K, C, G);
     }
+    __syncwarp();
+    if (MULTI && G.phase == PH_DONE) {
+        // every rank reaches the same verdict: one fenced exchange makes all remote parent stores
+        // of the query visible before any rank's path kernel walks them
+        Slot z; z.count = 0; z.meet = NO_V; z.rq_tail = 0; z.edges = 0;
+        Slot g2;
+        cross_exchange<MULTI>(K, E, G, z, g2, deadline, true);
+    }
+    if (lane == 0 && G.phase == PH_DONE) write_result(K, C, G);
     DBG_STAMP2(2, G.phase);
     __syncwarp();
     return true;
@@ -375,6 +397,7 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
         }
         G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 0; G.pad = 0;
         G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
+        G.rq_tag[0] = G.rq_tag[1] = 0;
         G.xepoch = C->xepoch;
         const bool bad = src >= K.n || dst >= K.n;
         if (bad) { G.status = 2; G.phase = PH_DONE; }
@@ -400,7 +423,7 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
         // before anybody's remote traffic can arrive
         Slot z; z.count = 0; z.meet = NO_V; z.rq_tail = 0; z.edges = 0;
         Slot got;
-        ok = cross_exchange<MULTI>(K, E, G, z, got, deadline);
+        ok = cross_exchange<MULTI>(K, E, G, z, got, deadline, false);
     }
     if (lane == 0) {
         if (!ok) { atomicExch(&C->abort_flag, 1u); G.status = 1; G.phase = PH_DONE; }
@@ -424,7 +447,35 @@ __device__ __forceinline__ u32 fetch_frontier(const KParams& K, const Env& E, co
 #pragma unroll 1
     for (u32 p = 0; p < K.P; ++p) {
         const u32 lo = st.rq_lo[side][p], c = st.rq_hi[side][p] - lo;
-        if (i < c) { v = __ldcg(rq_of(K, E.me, side, p) + lo + i); break; }
+        if (i < c) {
+            // the sender's count may overtake its entries on the wire: wait for the tagged word
+            const u64* e = rq_of(K, E.me, side, p) + lo + i;
+            const u32 tag = st.rq_tag[side];
+            u64 w = ptx::ld_relaxed_sys(e);
+            for (u32 spins = 0; (u32)(w >> 32) != tag && spins < (1u << 24); ++spins) w = ptx::ld_relaxed_sys(e);
+            if ((u32)(w >> 32) != tag) atomicExch(&E.C->abort_flag, 1u);
+            v = (u32)w;
+            break;
+        }
+        i -= c;
+    }
+    return v;
+}
+
+// entry i of the concatenated sender-segment windows (i counts past the local window)
+__device__ __forceinline__ u32 fetch_rq(const KParams& K, const Env& E, const LevelState& st, u32 side, u32 i, u32 tag) {
+    u32 v = 0;
+#pragma unroll 1
+    for (u32 p = 0; p < K.P; ++p) {
+        const u32 lo = st.rq_lo[side][p], c = st.rq_hi[side][p] - lo;
+        if (i < c) {
+            const u64* e = rq_of(K, E.me, side, p) + lo + i;
+            u64 w = ptx::ld_relaxed_sys(e);
+            for (u32 spins = 0; (u32)(w >> 32) != tag && spins < (1u << 24); ++spins) w = ptx::ld_relaxed_sys(e);
+            if ((u32)(w >> 32) != tag) atomicExch(&E.C->abort_flag, 1u);
+            v = (u32)w;
+            break;
+        }
         i -= c;
     }
     return v;
@@ -503,9 +554,12 @@ __device__ __forceinline__ void enqueue(const KParams& K, const Env& E, u32 side
                 if (E.sq && slot - E.sq_base < SOLO_CAP) E.sq[slot - E.sq_base] = v;
                 ptx::prefetch_l2(E.row_ptr + (v - E.lo));
             } else {
-                if (lane == leader) base = atomicAdd(&E.C->sent[side][c.dest], (u32)__popc(grp));
+                if (lane == leader) {
+                    if (E.solo) { base = ptx::atoms_add(&E.s_sent[side * MAXR + c.dest], (u32)__popc(grp)); ptx::reds_add(E.s_rnew, (u32)__popc(grp)); }
+                    else base = atomicAdd(&E.C->sent[side][c.dest], (u32)__popc(grp));
+                }
                 base = __shfl_sync(grp, base, leader);
-                ptx::st_peer(rq_of(K, c.dest, side, E.me) + base + rank_in, v);
+                ptx::st_relaxed_sys(rq_of(K, c.dest, side, E.me) + base + rank_in, (u64)v | ((u64)E.tag << 32));
                 ptx::st_peer(parent_of(K, c.dest, side) + (v - c.dest * K.B), u);
             }
         }
@@ -857,33 +911,47 @@ __device__ __noinline__ void solo_push_hub(const KParams& K, const Env& E, Smem&
 // 16-byte descriptor.  Nothing is published to the grid until it is needed.
 struct SoloLevel {          // written by thread 0 at the end of a level, read by everybody
     u32 side_flags;         // bit 0 side, bit 1 frontier is in the shared mirror, bit 2 which mirror buffer, bit 3 stop
-    u32 total;              // frontier vertices
-    u32 q_lo;               // window start in the global queue (used when not mirrored)
-    u32 base_tail;          // queue cursor at the start of the level (== window end)
+    u32 total;              // frontier vertices of this rank (local window + windows of the sender segments)
+    u32 q_lo;               // local window start in the global queue (used when not mirrored)
+    u32 base_tail;          // local queue cursor at the start of the level (== local window end)
+    u32 nq;                 // size of the local window
+    u32 tag;                // epoch tag for entries sent to other ranks in this level
+    u32 rq_tag;             // tag carried by the entries of the sender-segment windows
+    u32 pad;
 };
-static_assert(sizeof(SoloLevel) == 16, "one LDS.128");
+static_assert(sizeof(SoloLevel) == 32, "two LDS.128");
 
 constexpr int SW = 8;       // adjacency entries per lane per round
 
-__device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
-    const u32 tid = threadIdx.x, lane = tid & 31;
+template <bool MULTI>
+__device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 deadline) {
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     LevelState& st = sm.st;
-    E.solo = true; E.A = &sm.acc; E.sA = &sm.acc; E.filter = false; E.s_hub = &sm.hub;
     __shared__ __align__(16) SoloLevel s_lv;
+    __shared__ u32 s_sent[2][MAXR];      // MULTI: entries appended to each peer's segment (cumulative, per side)
+    __shared__ u32 s_rnew;               // MULTI: vertices discovered at other ranks in this level
+    __shared__ u64 s_mail[2];            // MULTI: reduced (edges, meet<<32 | discovered) handed from the leader warp to thread 0
+    E.solo = true; E.A = &sm.acc; E.sA = &sm.acc; E.filter = false; E.s_hub = &sm.hub;
+    E.s_sent = &s_sent[0][0]; E.s_rnew = &s_rnew;
     // thread 0 keeps the level state in registers across levels
     u32 nf0 = st.nf[0], nf1 = st.nf[1], d0 = st.depth[0], d1 = st.depth[1], levels = st.levels;
     u32 qlo0 = st.q_lo[0], qlo1 = st.q_lo[1], qhi0 = st.q_hi[0], qhi1 = st.q_hi[1];
     u32 cur0 = sm.qcur[0], cur1 = sm.qcur[1], val0 = sm.qvalid[0], val1 = sm.qvalid[1];
     u64 pend_edges = 0, pend_vis = 0;
-    if (tid == 0) {
-        const u32 sd = st.side;
+    auto make_level = [&](u32 sd) {
         SoloLevel lv;
         lv.side_flags = sd | ((sd ? val1 : val0) ? 2u : 0u) | ((sd ? cur1 : cur0) ? 4u : 0u);
         lv.total = st.local_front;
         lv.q_lo = sd ? qlo1 : qlo0;
         lv.base_tail = sd ? qhi1 : qhi0;
+        lv.nq = lv.base_tail - lv.q_lo;
+        lv.tag = (u32)(st.xepoch + 1);
+        lv.rq_tag = st.rq_tag[sd];
+        lv.pad = 0;
         s_lv = lv;
-    }
+    };
+    if (MULTI && tid < 2 * MAXR) s_sent[tid / MAXR][tid % MAXR] = ptx::ld_relaxed_gpu(&E.C->sent[tid / MAXR][tid % MAXR]);
+    if (tid == 0) { make_level(st.side); s_rnew = 0; }
     __syncthreads();
     while (true) {
         DBG_STAMP(0, tid);
@@ -893,10 +961,17 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
         const u32 cur = (raw.x >> 2) & 1u;
         u32* const out = sm.q[side][cur ^ 1u];
         const u32 sh = 32u * side, osh = 32u - sh;
+        u32 nq = total, tag = 0, rq_tag = 0;
+        if (MULTI) {
+            const uint4 raw2 = *(reinterpret_cast<const uint4*>(&s_lv) + 1);
+            nq = raw2.x; tag = raw2.y; rq_tag = raw2.z;
+            E.tag = tag;
+        }
         u32 u = 0;
         u64 r0 = 0, r1 = 0;
         if (tid < total) {
-            u = (raw.x & 2u) ? sm.q[side][cur][tid] : __ldcg(E.q[side] + raw.z + tid);
+            if (!MULTI || tid < nq) u = (raw.x & 2u) ? sm.q[side][cur][tid] : __ldcg(E.q[side] + raw.z + tid);
+            else u = fetch_rq(K, E, st, side, tid - nq, rq_tag);     // entry of a sender segment (tagged, polled)
             r0 = __ldg(E.row_ptr + (u - E.lo));
             r1 = __ldg(E.row_ptr + (u - E.lo) + 1);
         }
@@ -910,27 +985,56 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
         for (u32 e0 = 0; __any_sync(FULL, e0 < sdeg); e0 += SW) {
             u32 v[SW];
             u64 old[SW];
+            // branch-free issue: idle slots re-read the row's first entry and OR a zero into a private
+            // scratch word, so that all SW loads and then all SW claims are in flight together
+            u64* const dummy = reinterpret_cast<u64*>(fbm_of(K, E.me, 0, 0)) + tid;
 #pragma unroll
-            for (int k = 0; k < SW; ++k) v[k] = (e0 + k < sdeg) ? __ldg(E.col + r0 + e0 + k) : 0u;
-#pragma unroll
-            for (int k = 0; k < SW; ++k)
-                old[k] = (e0 + k < sdeg) ? ptx::atom_or_gpu(&E.vis[v[k] >> 5], 1ull << ((v[k] & 31u) + sh)) : ~0ull;
-            DBG_STAMP(3, v[0] + v[SW - 1]);
-            u32 newmask = 0, meetmask = 0;
+            for (int k = 0; k < SW; ++k) v[k] = __ldg(E.col + r0 + ((e0 + k < sdeg) ? e0 + k : 0u));
 #pragma unroll
             for (int k = 0; k < SW; ++k) {
-                const u64 w = old[k] >> (v[k] & 31u);
-                const u32 isnew = ((u32)(w >> sh) & 1u) ^ 1u;
-                newmask |= isnew << k;
-                meetmask |= (isnew & (u32)(w >> osh)) << k;
+                const bool act = e0 + k < sdeg;
+                old[k] = ptx::atom_or_gpu(act ? &E.vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
             }
-            DBG_STAMP(4, newmask);
-            if (newmask) {
-                const u32 cntnew = __popc(newmask);
-                u32 slot = ptx::atoms_add(&sm.acc.q_tail[side], cntnew);
+#pragma unroll
+            for (int k = 0; k < SW; ++k)
+                if (!(e0 + k < sdeg)) old[k] = ~0ull;
+            DBG_STAMP(3, v[0] + v[SW - 1]);
+            u32 newmask = 0, meetmask = 0, remmask = 0;
+#pragma unroll
+            for (int k = 0; k < SW; ++k) {
+                const u32 isnew = ((u32)(old[k] >> ((v[k] & 31u) + sh)) & 1u) ^ 1u;
+                newmask |= isnew << k;
+            }
+            if (MULTI && __any_sync(FULL, newmask != 0)) {
+                // vertices of other ranks: the local bit was only a "not forwarded yet" filter — claim at the
+                // owner.  Branch-free again so that the NVLink round trips (1.6 us each) overlap.
+                u64* const dummy = reinterpret_cast<u64*>(fbm_of(K, E.me, 0, 0)) + tid;
+                u64 rold[SW];
 #pragma unroll
                 for (int k = 0; k < SW; ++k) {
-                    if ((newmask >> k) & 1u) {
+                    const bool rem = ((newmask >> k) & 1u) && (v[k] - E.lo) >= K.B;
+                    remmask |= rem ? (1u << k) : 0u;
+                    u64* const addr = rem ? (vis_of(K, v[k] / K.B) + (v[k] >> 5)) : dummy;
+                    rold[k] = ptx::atom_or_sys(addr, rem ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
+                }
+#pragma unroll
+                for (int k = 0; k < SW; ++k) {
+                    if ((remmask >> k) & 1u) {
+                        old[k] = rold[k];
+                        if ((rold[k] >> ((v[k] & 31u) + sh)) & 1ull) { newmask &= ~(1u << k); remmask &= ~(1u << k); }
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < SW; ++k)
+                meetmask |= (((newmask >> k) & 1u) & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
+            DBG_STAMP(4, newmask);
+            const u32 locmask = newmask & ~remmask;
+            if (locmask) {
+                u32 slot = ptx::atoms_add(&sm.acc.q_tail[side], (u32)__popc(locmask));
+#pragma unroll
+                for (int k = 0; k < SW; ++k) {
+                    if ((locmask >> k) & 1u) {
                         E.q[side][slot] = v[k];
                         E.parent[side][v[k] - E.lo] = u;
                         if (slot - base_tail < SOLO_CAP) out[slot - base_tail] = v[k];
@@ -938,11 +1042,23 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
                         ++slot;
                     }
                 }
-                if (meetmask) {
+            }
+            if (MULTI && remmask) {
 #pragma unroll
-                    for (int k = 0; k < SW; ++k)
-                        if ((meetmask >> k) & 1u) ptx::reds_min(&sm.acc.meet_local, v[k]);
+                for (int k = 0; k < SW; ++k) {
+                    if ((remmask >> k) & 1u) {
+                        const u32 dest = v[k] / K.B;
+                        const u32 slot = ptx::atoms_add(&s_sent[side][dest], 1u);
+                        ptx::st_relaxed_sys(rq_of(K, dest, side, E.me) + slot, (u64)v[k] | ((u64)tag << 32));
+                        ptx::st_peer(parent_of(K, dest, side) + (v[k] - dest * K.B), u);
+                    }
                 }
+                ptx::reds_add(&s_rnew, (u32)__popc(remmask));
+            }
+            if (meetmask) {
+#pragma unroll
+                for (int k = 0; k < SW; ++k)
+                    if ((meetmask >> k) & 1u) ptx::reds_min(&sm.acc.meet_local, v[k]);
             }
         }
         DBG_STAMP(5, sdeg);
@@ -950,14 +1066,15 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
         u32 big = __ballot_sync(FULL, deg >= 32u);
         if (big) {
             E.sq = out; E.sq_base = base_tail;
-            u32 cnt = 0;
+            u32 cnt = 0;     // (discoveries are derived from the queue cursor and s_rnew)
             while (big) {
                 const u32 sl = __ffs(big) - 1;
                 big &= big - 1;
                 const u32 uu = __shfl_sync(FULL, u, sl);
                 const u64 rb = __shfl_sync(FULL, r0, sl), re = __shfl_sync(FULL, r1, sl);
-                expand_range<false>(K, E, side, uu, rb, re, cnt);
+                expand_range<MULTI>(K, E, side, uu, rb, re, cnt);
             }
+            (void)cnt;
         }
         // per-warp edge count (statistics only, off the critical path)
         {
@@ -966,13 +1083,50 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
         }
         __syncthreads();
         DBG_STAMP(6, tid);
-        // ---- level end: thread 0, state in registers
+        // ---- level end
+        u32 found = 0, meet = NO_V;
+        if (MULTI) {
+            // leader warp: exchange this rank's counts with every peer (tagged words over NVLink).
+            // Not when a hub row was deferred: then the level is not over yet.
+            if (warp == 0 && !sm.hub) {
+                Slot mine, got;
+                mine.count = (sm.acc.q_tail[side] - base_tail) + s_rnew;      // local cursor advance + claims at other ranks
+                mine.meet = sm.acc.meet_local;
+                mine.edges = (u32)sm.acc.edges;
+                mine.rq_tail = lane < K.P ? s_sent[side][lane] : 0u;
+                const bool ok = cross_exchange<MULTI>(K, E, st, mine, got, deadline, false);
+                u32 total_new = got.count, meetmin = got.meet;
+                u64 etot = got.edges;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) {
+                    total_new += __shfl_xor_sync(FULL, total_new, d);
+                    meetmin = min(meetmin, __shfl_xor_sync(FULL, meetmin, d));
+                    etot += __shfl_xor_sync(FULL, etot, d);
+                }
+                if (lane < K.P) { st.rq_lo[side][lane] = st.rq_hi[side][lane]; st.rq_hi[side][lane] = got.rq_tail; }
+                if (lane == 0) {
+                    st.rq_tag[side] = (u32)st.xepoch;
+                    s_mail[0] = etot;
+                    s_mail[1] = ((u64)meetmin << 32) | total_new;
+                    if (!ok) { sm.fail = 1; atomicExch(&E.C->abort_flag, 1u); }
+                }
+                __syncwarp();
+            }
+            if (tid == 0) {
+                if (sm.hub) { found = (sm.acc.q_tail[side] - base_tail) + s_rnew; }
+                else { found = (u32)s_mail[1]; meet = (u32)(s_mail[1] >> 32); }
+            }
+        } else if (tid == 0) {
+            found = sm.acc.q_tail[side] - base_tail;
+            meet = sm.acc.meet_local;
+        }
         if (tid == 0) {
             Ctrl* C = E.C;
             const u32 tail = sm.acc.q_tail[side];
-            const u32 found = tail - base_tail;
             u32 stop = 0;
-            if (sm.hub) {
+            if (MULTI && sm.fail) {
+                st.status = 1; st.length = -1; st.phase = PH_DONE; stop = 1;
+            } else if (sm.hub) {
                 // the level is not over: publish and let the grid expand the deferred rows
                 const u64 hp = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&C->hub_packed));
                 st.hub_entries = (u32)(hp >> 40);
@@ -985,15 +1139,17 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
                 if (side) { cur1 ^= 1u; val1 = 0; } else { cur0 ^= 1u; val0 = 0; }
                 stop = 1;
             } else {
-                const u32 meet = sm.acc.meet_local;
-                const u64 ed = sm.acc.edges;
+                const u64 ed_local = sm.acc.edges;
+                const u64 ed = MULTI ? s_mail[0] : ed_local;
                 const u32 expanded = side ? nf1 : nf0;
-                if (side) { nf1 = found; d1 += 1; qlo1 = base_tail; qhi1 = tail; cur1 ^= 1u; val1 = found <= SOLO_CAP; }
-                else      { nf0 = found; d0 += 1; qlo0 = base_tail; qhi0 = tail; cur0 ^= 1u; val0 = found <= SOLO_CAP; }
+                const u32 lfound = tail - base_tail;
+                if (side) { nf1 = found; d1 += 1; qlo1 = base_tail; qhi1 = tail; cur1 ^= 1u; val1 = lfound <= SOLO_CAP; }
+                else      { nf0 = found; d0 += 1; qlo0 = base_tail; qhi0 = tail; cur0 ^= 1u; val0 = lfound <= SOLO_CAP; }
                 levels += 1;
                 pend_edges += ed; pend_vis += found;
                 sm.acc.edges = 0;
-                if (K.flags & BIBFS_F_TRACE) trace_level(K, E, side, PH_TD_SOLO, expanded, found, ed, ptx::globaltimer_ns());
+                if (MULTI) { s_rnew = 0; sm.acc.new_count = 0; }
+                if (K.flags & BIBFS_F_TRACE) trace_level(K, E, side, PH_TD_SOLO, expanded, found, ed_local, ptx::globaltimer_ns());
                 if (meet != NO_V) {
                     sm.acc.meet_local = NO_V;
                     st.length = (i32)(d0 + d1);
@@ -1003,20 +1159,15 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
                 } else {
                     const u32 ns = nf0 <= nf1 ? 0u : 1u;           // smaller frontier first, ties -> source (v1)
                     const u32 nfn = ns ? nf1 : nf0;
-                    const u32 lf = ns ? qhi1 - qlo1 : qhi0 - qlo0;
+                    u32 lf = ns ? qhi1 - qlo1 : qhi0 - qlo0;
+                    if (MULTI)
+                        for (u32 p = 0; p < K.P; ++p) lf += st.rq_hi[ns][p] - st.rq_lo[ns][p];
                     st.side = ns;
                     st.local_front = lf;
                     if (nfn == 0) { st.length = -1; st.phase = PH_DONE; stop = 1; }
                     else if (lf > K.solo_threshold || (K.flags & (BIBFS_F_FORCE_BU | BIBFS_F_FORCE_GRID)) ||
                              (!(K.flags & BIBFS_F_FORCE_TD) && K.bu_div != 0xFFFFFFFFu && nfn > K.n / K.bu_div)) stop = 2;
-                    else {
-                        SoloLevel lv;
-                        lv.side_flags = ns | ((ns ? val1 : val0) ? 2u : 0u) | ((ns ? cur1 : cur0) ? 4u : 0u);
-                        lv.total = lf;
-                        lv.q_lo = ns ? qlo1 : qlo0;
-                        lv.base_tail = ns ? qhi1 : qhi0;
-                        s_lv = lv;
-                    }
+                    else make_level(ns);
                 }
             }
             if (stop) {
@@ -1029,7 +1180,8 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
                 if (stop == 2) decide_next(K, st);
                 C->edges_total += pend_edges;
                 C->res.vertices_visited += pend_vis;
-                if (st.phase == PH_DONE) write_result(K, C, st);
+                if (MULTI)
+                    for (u32 p = 0; p < MAXR; ++p) { C->sent[0][p] = s_sent[0][p]; C->sent[1][p] = s_sent[1][p]; }
                 s_lv.side_flags = 8u;
             }
         }
@@ -1039,6 +1191,15 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm) {
 #endif
         __syncthreads();
     }
+    // leaving solo mode
+    if (MULTI && st.phase == PH_DONE && warp == 0 && !sm.fail) {
+        // every rank reaches the same verdict: one fenced exchange makes all remote parent stores visible
+        Slot z; z.count = 0; z.meet = NO_V; z.rq_tail = 0; z.edges = 0;
+        Slot g2;
+        cross_exchange<MULTI>(K, E, st, z, g2, deadline, true);
+    }
+    if (tid == 0 && st.phase == PH_DONE) write_result(K, E.C, st);
+    __syncthreads();
 }
 
 }  // namespace
@@ -1067,7 +1228,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     E.C = ctrl_of(K, E.me);
     E.A = &E.C->acc;
     E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = true;
-    E.sA = &s_acc; E.solo = false;
+    E.sA = &s_acc; E.solo = false; E.tag = 0; E.s_sent = nullptr; E.s_rnew = nullptr;
     E.vis = vis_of(K, E.me);
     E.parent[0] = parent_of(K, E.me, 0); E.parent[1] = parent_of(K, E.me, 1);
     E.q[0] = q_of(K, E.me, 0); E.q[1] = q_of(K, E.me, 1);
@@ -1130,7 +1291,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         __syncthreads();
         if (!is_leader_cta) {
             if (tid == 0) {
-                if (MULTI) ptx::fence_sys();
+                if (MULTI && mode == PH_BU) ptx::fence_sys();   // bitmap slices pushed with plain stores
                 ptx::red_release_gpu_add(&C->bar_count, 1u);
                 if (!wait_gen(C, genbase | (u64)(st.wake + 1u), deadline)) s_fail = 1;
             }
@@ -1170,8 +1331,9 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 load_state();
                 continue;
             }
-            if (!MULTI) {
-                solo_run(K, E, sm);
+            {
+                solo_run<MULTI>(K, E, sm, deadline);
+                if (s_fail) { if (warp == 0) publish_and_wake(); __syncthreads(); alive = false; break; }
                 if (warp == 0) publish_and_wake();      // left solo mode: the grid is needed (or the query is done)
                 __syncthreads();
                 continue;
@@ -1184,6 +1346,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 const u32 cur = s_qcur[side];
                 const u32* front = (s_qvalid[side] && nq <= SOLO_CAP) ? s_q[side][cur] : nullptr;
                 E.A = &s_acc; E.solo = true;
+                E.tag = (u32)(st.xepoch + 1);
                 E.sq = s_q[side][cur ^ 1u];
                 E.sq_base = st.q_hi[side];           // == current tail of this side's queue
                 E.s_hub = &s_hub;
@@ -1210,10 +1373,12 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
             if (s_fail) { alive = false; break; }
         } else if (phase == PH_TD_GRID) {
             E.A = &C->acc;
+            E.tag = (u32)(st.xepoch + 1);
             expand_td<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
             alive = sync_grid(SYNC_LEVEL, PH_TD_GRID);
         } else if (phase == PH_TD_HUB) {
             E.A = &C->acc;
+            E.tag = (u32)(st.xepoch + 1);
             expand_hubs<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
             alive = sync_grid(SYNC_LEVEL, PH_TD_HUB);
         } else {  // PH_BU
