@@ -120,8 +120,16 @@ class Graph:
         dev = torch.device(device)
         g = Graph(self.n, self.nranks, dev, {}, self.m_records, self.spec, self.name)
         for r, s in self.shards.items():
-            g.shards[r] = Shard(r, s.lo, s.hi, s.row_ptr.to(dev), s.col.to(dev))
+            g.shards[r] = Shard(r, s.lo, s.hi, s.row_ptr.to(dev), padded_col(s.col, dev))
         return g
+
+
+def padded_col(col: torch.Tensor, device) -> torch.Tensor:
+    """Copy of `col` on `device` whose storage has 4 spare entries after the last one: the hub phase
+    fetches adjacency chunks with 16-byte bulk copies that may read up to 12 bytes past a row's end."""
+    out = torch.zeros(col.numel() + 4, dtype=col.dtype, device=device)
+    out[: col.numel()].copy_(col)
+    return out[: col.numel()]
 
 
 def edge_list(spec: GenSpec, device="cpu") -> np.ndarray:

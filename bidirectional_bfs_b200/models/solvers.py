@@ -42,8 +42,8 @@ def _as_single(graph: Graph, device) -> Graph:
         cols.append(s.col.cpu())
     rps.append(torch.tensor([base], dtype=torch.int64))
     g = Graph(graph.n, 1, dev, {}, graph.m_records, graph.spec, graph.name)
-    from ..graph import Shard
-    g.shards[0] = Shard(0, 0, graph.n, torch.cat(rps).to(dev), torch.cat(cols).to(dev))
+    from ..graph import Shard, padded_col
+    g.shards[0] = Shard(0, 0, graph.n, torch.cat(rps).to(dev), padded_col(torch.cat(cols), dev))
     return g
 
 

@@ -92,7 +92,10 @@ struct HubEntry {      // a frontier vertex whose row is expanded by the whole g
     u64 chunk_base;    // first global chunk id of this row
 };
 constexpr u32 HUB_ROW = 1024;     // rows at least this long are deferred to the hub phase
-constexpr u32 HUB_CHUNK = 512;    // adjacency entries per hub work item (2 KB: one bulk copy)
+constexpr u32 HUB_CHUNK = 256;    // adjacency entries per hub work item (1 KB: one bulk copy, 16-byte aligned in col)
+// chunk i of a row [r0,r1) covers col[A + i*HUB_CHUNK, A + (i+1)*HUB_CHUNK) with A = r0 rounded down to 4 entries,
+// so that every chunk starts on a 16-byte boundary (cp.async.bulk requirement)
+BIBFS_HD u32 hub_nchunks(u64 r0, u64 r1) { return (u32)((r1 - (r0 & ~3ull) + HUB_CHUNK - 1) / HUB_CHUNK); }
 constexpr u32 HUB_CAP = 16384;    // hub entries per level per rank (overflow: expanded in place)
 
 struct Ctrl {

@@ -89,6 +89,7 @@ struct Env {
     u32* s_hub;        // solo mode: shared flag "a hub row was deferred" (else null)
     bool filter;       // read the visited word before the atomic (pays off on large frontiers only)
     u32 tag;           // epoch tag stamped on entries sent to other ranks in the current level
+    bool smem_src;     // visit_batch reads the adjacency entries from shared memory (hub chunks staged by TMA)
     u32* s_sent;       // solo mode: shared copy of Ctrl::sent ([2][MAXR])
     u32* s_rnew;       // solo mode: shared counter of vertices discovered at other ranks
     u64* vis;
@@ -585,7 +586,7 @@ __device__ __noinline__ u32 visit_batch(const KParams& K, const Env& E, u32 side
     u64 seen[UNR];
     Claim c[UNR];
 #pragma unroll
-    for (int k = 0; k < UNR; ++k) v[k] = ok[k] ? __ldg(vp[k]) : 0u;
+    for (int k = 0; k < UNR; ++k) v[k] = ok[k] ? (E.smem_src ? *vp[k] : __ldg(vp[k])) : 0u;
     DBG_STAMP(4, v[0] + v[1] + v[2] + v[3]);
 #pragma unroll
     for (int k = 0; k < UNR; ++k) seen[k] = ok[k] ? (E.filter ? E.vis[v[k] >> 5] : 0ull) : ~0ull;   // filter only; may be stale
@@ -670,7 +671,7 @@ __device__ __noinline__ void expand_td(const KParams& K, const Env& E, const Lev
         edges += deg;
         // hub rows: hand them to the whole grid (hub phase) unless the list is full
         if (deg >= HUB_ROW) {
-            const u32 nch = (u32)((deg + HUB_CHUNK - 1) / HUB_CHUNK);
+            const u32 nch = hub_nchunks(r0, r1);
             const unsigned long long inc = (1ull << 40) | (unsigned long long)nch;
             const unsigned long long old = atomicAdd(&E.C->hub_packed, inc);
             const u32 slot = (u32)(old >> 40);
@@ -747,29 +748,79 @@ __device__ __noinline__ void expand_td(const KParams& K, const Env& E, const Lev
 #endif
 }
 
-// hub phase: every warp of the rank takes 2 KB chunks of the deferred rows
+// hub phase: every warp of the rank takes 1 KB chunks of the deferred rows.  The chunk is fetched
+// by the TMA engine (cp.async.bulk global -> shared, completion on an mbarrier; SASS UBLKCP) into a
+// per-warp double buffer, so the next chunk streams in while the current one is being claimed.
+struct HubChunk {
+    u32 uu;            // frontier vertex the row belongs to
+    u32 lo, hi;        // valid entries of the staged chunk: stage[lo..hi)
+    u32 bytes;         // size of the bulk copy
+    const u32* src;    // 16-byte aligned start of the chunk in col
+    bool valid;
+};
+
+__device__ __forceinline__ HubChunk hub_lookup(const HubEntry* H, u32 ne, const u32* col, u32 c) {
+    HubChunk h;
+    // entries are ordered by chunk_base (slot and base come from one atomic): binary search
+    u32 lo = 0, hi = ne;
+    while (hi - lo > 1) {
+        const u32 mid = (lo + hi) >> 1;
+        if (__ldcg(&H[mid].chunk_base) <= c) lo = mid; else hi = mid;
+    }
+    const u64 base = __ldcg(&H[lo].chunk_base);
+    const u32 nch = __ldcg(&H[lo].nchunks);
+    h.valid = ne != 0 && (c - base) < nch;          // false: chunk of an entry that did not fit in the list
+    const u64 r0 = __ldcg(&H[lo].r0), r1 = __ldcg(&H[lo].r1);
+    h.uu = __ldcg(&H[lo].u);
+    const u64 A = (r0 & ~3ull) + (u64)(c - base) * HUB_CHUNK;     // 16-byte aligned
+    const u64 Aend = min(A + HUB_CHUNK, r1);
+    h.lo = (u32)(max(A, r0) - A);
+    h.hi = (u32)(Aend - A);
+    h.bytes = ((h.hi * 4u) + 15u) & ~15u;
+    h.src = col + A;
+    return h;
+}
+
 template <bool MULTI>
-__device__ __noinline__ void expand_hubs(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps) {
+__device__ __noinline__ void expand_hubs(const KParams& K, const Env& E0, const LevelState& st, u32 warp_gid, u32 nwarps,
+                                         u32* stage /* this warp's 2 x HUB_CHUNK words */, u64* bars /* this warp's 2 mbarriers */, u32& parity) {
     const u32 lane = threadIdx.x & 31;
     const u32 side = st.side;
-    const HubEntry* H = hub_of(K, E.me);
+    const HubEntry* H = hub_of(K, E0.me);
     const u32 ne = min(st.hub_entries, HUB_CAP);
+    Env E = E0;
+    E.smem_src = true;
     u32 cnt = 0;
-    for (u32 c = warp_gid; c < st.hub_chunks; c += nwarps) {
-        // entries are ordered by chunk_base (slot and base come from one atomic): binary search
-        u32 lo = 0, hi = ne;
-        while (hi - lo > 1) {
-            const u32 mid = (lo + hi) >> 1;
-            if (__ldcg(&H[mid].chunk_base) <= c) lo = mid; else hi = mid;
+    u32 c = warp_gid;
+    HubChunk cur = hub_lookup(H, ne, E.col, c < st.hub_chunks ? c : 0);
+    cur.valid = cur.valid && c < st.hub_chunks;
+    if (lane == 0 && cur.valid) { ptx::mbar_expect_tx(&bars[0], cur.bytes); ptx::bulk_g2s(stage, cur.src, cur.bytes, &bars[0]); }
+    for (u32 i = 0; c < st.hub_chunks; c += nwarps, ++i) {
+        const u32 buf = i & 1u;
+        // start the copy of this warp's next chunk into the other buffer
+        const u32 cn = c + nwarps;
+        HubChunk nxt = hub_lookup(H, ne, E.col, cn < st.hub_chunks ? cn : 0);
+        nxt.valid = nxt.valid && cn < st.hub_chunks;
+        if (lane == 0 && nxt.valid) {
+            ptx::fence_proxy_async();       // this buffer was read through the generic proxy two iterations ago
+            ptx::mbar_expect_tx(&bars[buf ^ 1u], nxt.bytes);
+            ptx::bulk_g2s(stage + (buf ^ 1u) * HUB_CHUNK, nxt.src, nxt.bytes, &bars[buf ^ 1u]);
         }
-        const u64 base = __ldcg(&H[lo].chunk_base);
-        const u32 nch = __ldcg(&H[lo].nchunks);
-        if (c - base >= nch) continue;        // chunk of an entry that did not fit in the list
-        const u64 r0 = __ldcg(&H[lo].r0), r1 = __ldcg(&H[lo].r1);
-        const u32 uu = __ldcg(&H[lo].u);
-        const u64 b = r0 + (c - base) * HUB_CHUNK;
-        const u64 e = min(r1, b + HUB_CHUNK);
-        expand_range<MULTI>(K, E, side, uu, b, e, cnt);
+        if (cur.valid) {
+            ptx::mbar_wait(&bars[buf], (parity >> buf) & 1u);
+            parity ^= 1u << buf;
+            const u32* sbuf = stage + buf * HUB_CHUNK;
+            for (u32 p = cur.lo; p < cur.hi; p += 32 * UNR) {
+                const u32 i0 = p + lane;
+                u32 okmask = 0;
+#pragma unroll
+                for (int k = 0; k < UNR; ++k) okmask |= (i0 + k * 32 < cur.hi) ? (1u << k) : 0u;
+                const u32* s0 = sbuf + i0;
+                cnt += visit_batch<MULTI>(K, E, side, okmask, cur.uu, cur.uu, cur.uu, cur.uu, s0, s0 + 32, s0 + 64, s0 + 96);
+            }
+        }
+        __syncwarp();
+        cur = nxt;
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(FULL, cnt, d);
@@ -876,8 +927,10 @@ struct Smem {
     u32 fail, hub;
     u32 qcur[2], qvalid[2];
     unsigned long long pend_edges, pend_visited;   // solo levels: totals not yet added to Ctrl
-    u32 q[2][2][SOLO_CAP];
+    u64 hub_bar[WPC][2];                           // hub phase: one mbarrier per warp and buffer
+    alignas(128) u32 q[2][2][SOLO_CAP];            // solo: frontier mirrors; hub phase: per-warp TMA staging (WPC x 2 KB)
 };
+static_assert(sizeof(u32) * 2 * 2 * SOLO_CAP >= WPC * 2 * HUB_CHUNK * sizeof(u32), "staging area too small");
 
 __device__ __noinline__ void trace_level(const KParams& K, const Env& E, u32 side, u32 mode, u32 expanded, u32 discovered, u64 edges,
                                          u64 t_expand) {
@@ -889,8 +942,7 @@ __device__ __noinline__ void trace_level(const KParams& K, const Env& E, u32 sid
 }
 
 __device__ __noinline__ void solo_push_hub(const KParams& K, const Env& E, Smem& sm, u32 u, u64 r0, u64 r1) {
-    const u64 deg = r1 - r0;
-    const u32 nch = (u32)((deg + HUB_CHUNK - 1) / HUB_CHUNK);
+    const u32 nch = hub_nchunks(r0, r1);
     const unsigned long long inc = (1ull << 40) | (unsigned long long)nch;
     const unsigned long long old = atomicAdd(&E.C->hub_packed, inc);
     const u32 slot = (u32)(old >> 40);
@@ -977,9 +1029,9 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         }
         u32 deg = (u32)min(r1 - r0, (u64)0xFFFFFFFFu);
         DBG_STAMP(1, deg);
+        const u32 nedges = deg;                      // statistics: hub rows count as inspected here
         if (deg >= HUB_ROW) { solo_push_hub(K, E, sm, u, r0, r1); deg = 0; }
         u32 sdeg = deg < 32u ? deg : 0u;
-        u32 nedges = deg;
         DBG_STAMP(2, sdeg);
         // rows shorter than a warp: each lane walks its own row, SW entries per round
         for (u32 e0 = 0; __any_sync(FULL, e0 < sdeg); e0 += SW) {
@@ -1228,7 +1280,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     E.C = ctrl_of(K, E.me);
     E.A = &E.C->acc;
     E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = true;
-    E.sA = &s_acc; E.solo = false; E.tag = 0; E.s_sent = nullptr; E.s_rnew = nullptr;
+    E.sA = &s_acc; E.solo = false; E.tag = 0; E.smem_src = false; E.s_sent = nullptr; E.s_rnew = nullptr;
     E.vis = vis_of(K, E.me);
     E.parent[0] = parent_of(K, E.me, 0); E.parent[1] = parent_of(K, E.me, 1);
     E.q[0] = q_of(K, E.me, 0); E.q[1] = q_of(K, E.me, 1);
@@ -1239,6 +1291,8 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     const u64 genbase = (u64)K.seq << 32;
     const bool is_leader_cta = (E.cta == 0);
     if (tid == 0) { s_fail = 0; s_hub = 0; s_qvalid[0] = 0; s_qvalid[1] = 0; s_qcur[0] = 0; s_qcur[1] = 0; sm.pend_edges = 0; sm.pend_visited = 0; }
+    if (lane == 0) { ptx::mbar_init(&sm.hub_bar[warp][0], 1); ptx::mbar_init(&sm.hub_bar[warp][1], 1); ptx::mbar_fence_init(); }
+    u32 hub_parity = 0;            // phase bits of this warp's two hub barriers
     __syncthreads();
 
     // non-leader CTAs: copy the published level state global -> shared after a wake-up
@@ -1379,7 +1433,8 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         } else if (phase == PH_TD_HUB) {
             E.A = &C->acc;
             E.tag = (u32)(st.xepoch + 1);
-            expand_hubs<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
+            if (is_leader_cta && tid == 0) { s_qvalid[0] = 0; s_qvalid[1] = 0; }    // the mirrors double as TMA staging
+            expand_hubs<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC, &sm.q[0][0][0] + warp * 2 * HUB_CHUNK, sm.hub_bar[warp], hub_parity);
             alive = sync_grid(SYNC_LEVEL, PH_TD_HUB);
         } else {  // PH_BU
             E.A = &C->acc;
