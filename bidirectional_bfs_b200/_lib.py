@@ -114,6 +114,9 @@ def _declare(lib):
         "bibfs_ctx_trace": (C.c_int, [vp, u32, P(LevelTrace), u32, P(u32)]),
         "bibfs_batch_workspace_bytes": (C.c_size_t, [u32]),
         "bibfs_batch_query_device": (C.c_int, [u32, vp, vp, vp, vp, u32, vp, vp, vp, C.c_size_t, P(C.c_float), vp]),
+        "bibfs_pool_create": (C.c_int, [P(vp), P(CtxDesc), u32, u32]),
+        "bibfs_pool_query": (C.c_int, [vp, vp, vp, u32, vp, vp, vp, vp, P(C.c_float)]),
+        "bibfs_pool_destroy": (C.c_int, [vp]),
         "bibfs_naive_levelsync_device": (C.c_int, [u32, vp, vp, u32, u32, P(i32), P(C.c_float), vp]),
     }
     for name, (res, args) in sig.items():

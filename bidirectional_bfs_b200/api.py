@@ -35,9 +35,10 @@ def bibfs(graph: Graph, src: int, dst: int, variant: str | None = None, want_pat
         solver.close()
 
 
-def bibfs_batch(graph: Graph, srcs, dsts, device=None) -> list[int | None]:
-    """Hop counts for many (src, dst) pairs, 64 queries per bit-parallel pass (GPU)."""
-    solver = BatchSolver(graph, device=device)
+def bibfs_batch(graph: Graph, srcs, dsts, device=None, engine: str = "concurrent", lanes: int = 32) -> list[int | None]:
+    """Hop counts for many (src, dst) pairs on the GPU: concurrent single-CTA searches (default) or
+    the bit-parallel 64-queries-per-sweep engine."""
+    solver = BatchSolver(graph, device=device, engine=engine, lanes=lanes)
     try:
         return solver.query_batch(srcs, dsts)
     finally:

@@ -181,28 +181,69 @@ class NaiveGpuSolver:
 
 
 class BatchSolver:
-    """Bit-parallel bidirectional MS-BFS: up to 64 queries per sweep (csrc/msbfs_dev.cu)."""
+    """Many queries at once.
+
+    engine="concurrent" (default): a pool of `lanes` single-CTA search contexts on their own streams
+        (csrc/ctx.cu, bibfs_pool_*): independent latency-bound searches run side by side on the 148 SMs.
+    engine="bitparallel": bit-parallel bidirectional MS-BFS, 64 queries per sweep (csrc/msbfs_dev.cu);
+        pays off only when the searches are heavy and overlap, because every level sweeps all N vertices.
+    """
     variant = "batch"
 
-    def __init__(self, graph: Graph, device=None):
+    def __init__(self, graph: Graph, device=None, engine: str = "concurrent", lanes: int = 32, ctas_per_lane: int = 1):
         if graph.device.type != "cuda" or graph.nranks != 1:
             graph = _as_single(graph, device or "cuda:0")
         self.graph = graph
-        with torch.cuda.device(graph.device):
-            self._ws = torch.empty(lib().bibfs_batch_workspace_bytes(graph.n), dtype=torch.uint8, device=graph.device)
+        self.engine = engine
         self.last_ms = 0.0
+        self.last_meet: list[int] = []
+        self.last_levels: list[int] = []
+        self.last_edges: list[int] = []
+        self._pool = C.c_void_p()
+        self._ws = None
+        with torch.cuda.device(graph.device):
+            if engine == "bitparallel":
+                self._ws = torch.empty(lib().bibfs_batch_workspace_bytes(graph.n), dtype=torch.uint8, device=graph.device)
+            elif engine == "concurrent":
+                from .._lib import CtxDesc
+                s = graph.single()
+                d = CtxDesc()
+                d.n, d.nranks, d.rank_lo, d.vranks = graph.n, 1, 0, 1
+                d.d_row_ptr[0] = s.row_ptr.data_ptr()
+                d.d_col[0] = s.col.data_ptr() if s.col.numel() else s.row_ptr.data_ptr()
+                free, _ = torch.cuda.mem_get_info(graph.device)
+                per_lane = 20 * graph.n + (1 << 22)            # parents + queues + bitmaps, roughly
+                lanes = max(1, min(lanes, int(free * 0.6 // per_lane)))
+                self.lanes = lanes
+                check(lib().bibfs_pool_create(C.byref(self._pool), C.byref(d), lanes, ctas_per_lane))
+            else:
+                raise ValueError("engine must be 'concurrent' or 'bitparallel'")
 
     def query_batch(self, srcs, dsts) -> list[int | None]:
         srcs = np.ascontiguousarray(np.asarray(srcs, dtype=np.uint32))
         dsts = np.ascontiguousarray(np.asarray(dsts, dtype=np.uint32))
         assert srcs.shape == dsts.shape
-        s = self.graph.single()
-        out: list[int | None] = []
-        self.last_ms = 0.0
-        self.last_meet = []
+        nq = int(srcs.size)
         with torch.cuda.device(self.graph.device):
+            if self.engine == "concurrent":
+                lens = np.empty(nq, dtype=np.int32)
+                meet = np.empty(nq, dtype=np.uint32)
+                lev = np.empty(nq, dtype=np.uint32)
+                edg = np.empty(nq, dtype=np.uint64)
+                ms = C.c_float(0)
+                check(lib().bibfs_pool_query(self._pool, srcs.ctypes.data, dsts.ctypes.data, nq, lens.ctypes.data, meet.ctypes.data,
+                                             lev.ctypes.data, edg.ctypes.data, C.byref(ms)))
+                self.last_ms = float(ms.value)
+                self.last_meet = [int(x) for x in meet]
+                self.last_levels = [int(x) for x in lev]
+                self.last_edges = [int(x) for x in edg]
+                return [int(x) if x >= 0 else None for x in lens]
+            s = self.graph.single()
+            out: list[int | None] = []
+            self.last_ms = 0.0
+            self.last_meet = []
             st = torch.cuda.current_stream(self.graph.device).cuda_stream
-            for i in range(0, srcs.size, 64):
+            for i in range(0, nq, 64):
                 a, b = srcs[i:i + 64], dsts[i:i + 64]
                 lens = np.empty(a.size, dtype=np.int32)
                 meet = np.empty(a.size, dtype=np.uint32)
@@ -213,10 +254,19 @@ class BatchSolver:
                 self.last_ms += float(ms.value)
                 out += [int(x) if x >= 0 else None for x in lens]
                 self.last_meet += [int(x) for x in meet]
-        return out
+            return out
 
     def close(self):
         self._ws = None
+        if self._pool:
+            lib().bibfs_pool_destroy(self._pool)
+            self._pool = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def make_solver(graph: Graph, variant: str = "gpu", **kw):

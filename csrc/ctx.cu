@@ -253,3 +253,109 @@ extern "C" int bibfs_ctx_trace(bibfs_ctx* c, uint32_t i, bibfs_level_trace* out,
     }
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// query pool: many independent queries in flight at once
+//
+// A bidirectional search touches a sliver of the graph and is bound by the latency of its
+// level chain, not by bandwidth, so one query cannot use more than a few SMs — but 148 SMs can
+// chase 148 chains at once.  The pool owns `lanes` single-rank contexts, each launching a small
+// cooperative grid (default 1 CTA) on its own stream; queries are dealt round-robin and the
+// 64-byte results are copied into pinned memory in stream order.  (The bit-parallel MS-BFS engine
+// of msbfs_dev.cu sweeps all N vertices per level instead: better only when the searches are
+// heavy and overlap.)  No counterpart in the reference (one query per process).
+// ------------------------------------------------------------------------------------------
+struct bibfs_pool {
+    std::vector<bibfs_ctx*> ctx;
+    std::vector<cudaStream_t> st;
+    std::vector<cudaEvent_t> done;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    Result* h_res = nullptr;
+    size_t h_cap = 0;
+    int device = 0;
+};
+
+extern "C" int bibfs_pool_destroy(bibfs_pool* p) {
+    if (!p) return 0;
+    DeviceGuard g(p->device);
+    cudaDeviceSynchronize();
+    for (auto c : p->ctx) bibfs_ctx_destroy(c);
+    for (auto s : p->st) cudaStreamDestroy(s);
+    for (auto e : p->done) cudaEventDestroy(e);
+    if (p->ev0) cudaEventDestroy(p->ev0);
+    if (p->ev1) cudaEventDestroy(p->ev1);
+    if (p->h_res) cudaFreeHost(p->h_res);
+    delete p;
+    return 0;
+}
+
+extern "C" int bibfs_pool_create(bibfs_pool** out, const bibfs_ctx_desc* desc, uint32_t lanes, uint32_t ctas_per_lane) {
+    if (!out || !desc) return fail("NULL argument");
+    if (desc->nranks != 1 || desc->vranks != 1) return fail("the query pool works on an unpartitioned graph (nranks = 1)");
+    if (lanes < 1 || lanes > 1024) return fail("lanes must be 1..1024");
+    bibfs_pool* p = new bibfs_pool();
+    cudaGetDevice(&p->device);
+    bibfs_ctx_desc d = *desc;
+    d.max_ctas = ctas_per_lane ? ctas_per_lane : 1;
+    d.max_path = 16;                       // the pool returns lengths and meeting vertices, not paths
+    for (uint32_t i = 0; i < lanes; ++i) {
+        bibfs_ctx* c = nullptr;
+        if (bibfs_ctx_create(&c, &d)) { std::string why = bibfs_last_error(); bibfs_pool_destroy(p); return fail("lane %u: %s", i, why.c_str()); }
+        p->ctx.push_back(c);
+        cudaStream_t s;
+        cudaEvent_t e;
+        if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) {
+            bibfs_pool_destroy(p);
+            return fail("stream/event creation failed");
+        }
+        p->st.push_back(s);
+        p->done.push_back(e);
+    }
+    cudaEventCreate(&p->ev0);
+    cudaEventCreate(&p->ev1);
+    *out = p;
+    return 0;
+}
+
+extern "C" int bibfs_pool_query(bibfs_pool* p, const uint32_t* h_src, const uint32_t* h_dst, uint32_t nq,
+                                int32_t* h_len, uint32_t* h_meet, uint32_t* h_levels, uint64_t* h_edges, float* ms) {
+    if (!p || !h_src || !h_dst) return fail("NULL argument");
+    DeviceGuard g(p->device);
+    if (nq > p->h_cap) {
+        if (p->h_res) cudaFreeHost(p->h_res);
+        p->h_res = nullptr;
+        p->h_cap = 0;
+        const size_t cap = nq < 1024 ? 1024 : nq;
+        BIBFS_CUDA_TRY(cudaHostAlloc((void**)&p->h_res, cap * sizeof(Result), cudaHostAllocDefault));
+        p->h_cap = cap;
+    }
+    const size_t L = p->ctx.size();
+    BIBFS_CUDA_TRY(cudaEventRecord(p->ev0, p->st[0]));
+    for (size_t i = 1; i < L; ++i) BIBFS_CUDA_TRY(cudaStreamWaitEvent(p->st[i], p->ev0, 0));
+    for (uint32_t q = 0; q < nq; ++q) {
+        const size_t lane = q % L;
+        bibfs_ctx* c = p->ctx[lane];
+        KParams K;
+        fill_params(c, K, h_src[q], h_dst[q], false, BIBFS_F_NO_PATH);
+        if (bfs_launch(K, false, p->st[lane])) return 1;
+        BIBFS_CUDA_TRY(cudaMemcpyAsync(&p->h_res[q], c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, p->st[lane]));
+    }
+    for (size_t i = 1; i < L; ++i) {
+        BIBFS_CUDA_TRY(cudaEventRecord(p->done[i], p->st[i]));
+        BIBFS_CUDA_TRY(cudaStreamWaitEvent(p->st[0], p->done[i], 0));
+    }
+    BIBFS_CUDA_TRY(cudaEventRecord(p->ev1, p->st[0]));
+    BIBFS_CUDA_TRY(cudaEventSynchronize(p->ev1));
+    if (ms) BIBFS_CUDA_TRY(cudaEventElapsedTime(ms, p->ev0, p->ev1));
+    int bad = 0;
+    for (uint32_t q = 0; q < nq; ++q) {
+        const Result& r = p->h_res[q];
+        if (r.status == 1) bad = 1;
+        if (h_len) h_len[q] = r.status == 0 ? r.length : -1;
+        if (h_meet) h_meet[q] = r.meet;
+        if (h_levels) h_levels[q] = r.levels;
+        if (h_edges) h_edges[q] = r.edges_scanned;
+    }
+    if (bad) return fail("a pooled query was aborted by the device watchdog");
+    return 0;
+}

@@ -239,6 +239,17 @@ int bibfs_batch_query_device(uint32_t n, const uint64_t* d_row_ptr, const uint32
                              int32_t* h_lengths, uint32_t* h_meet, void* d_ws, size_t ws_bytes,
                              float* search_ms, void* stream);
 
+/* Query pool: `lanes` single-rank contexts with small grids (ctas_per_lane, 0 -> 1) on their own
+ * streams; nq queries are dealt round-robin and run concurrently.  A bidirectional search is bound
+ * by the latency of its level chain, so independent queries scale with the number of SMs.  Outputs
+ * may be NULL.  ms = device time from the first launch to the last completion.  Out-of-range
+ * queries report length -1.  No counterpart in the reference. */
+typedef struct bibfs_pool bibfs_pool;
+int bibfs_pool_create(bibfs_pool** out, const bibfs_ctx_desc* desc, uint32_t lanes, uint32_t ctas_per_lane);
+int bibfs_pool_query(bibfs_pool* pool, const uint32_t* h_src, const uint32_t* h_dst, uint32_t nq,
+                     int32_t* h_len, uint32_t* h_meet, uint32_t* h_levels, uint64_t* h_edges, float* ms);
+int bibfs_pool_destroy(bibfs_pool* pool);
+
 /* ------------------------------------------------------------------------------------------
  * reference-style level-synchronous GPU baseline (one thread per vertex over all N, int flag
  * arrays, host in the loop) — OUR restatement of the v3 algorithm (v3/bibfs_cuda_only.cu:173-203)

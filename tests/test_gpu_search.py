@@ -143,8 +143,26 @@ def test_batch_vs_oracle(bb):
         oracle = bb.SerialSolver(g_cpu, policy=1)
         pairs = query_pairs(spec.n, 100, 9)
         want = [oracle.query(s, t, want_path=False).length for s, t in pairs]
-        got = bb.bibfs_batch(bb.Graph.generate(spec, device="cuda:0"), [p[0] for p in pairs], [p[1] for p in pairs])
-        assert got == want, name
+        g = bb.Graph.generate(spec, device="cuda:0")
+        for engine in ("concurrent", "bitparallel"):
+            got = bb.bibfs_batch(g, [p[0] for p in pairs], [p[1] for p in pairs], engine=engine)
+            assert got == want, (name, engine)
+
+
+def test_batch_pool_many_queries_and_lanes(bb):
+    spec = bb.rmat_spec(13, edgefactor=16, seed=4)
+    g_cpu = bb.Graph.generate(spec)
+    oracle = bb.SerialSolver(g_cpu, policy=1)
+    rng = np.random.default_rng(1)
+    pairs = rng.integers(0, spec.n, size=(700, 2))
+    want = [oracle.query(int(s), int(t), want_path=False).length for s, t in pairs]
+    g = bb.Graph.generate(spec, device="cuda:0")
+    for lanes, cpl in ((1, 1), (7, 1), (32, 1), (8, 4)):
+        b = bb.BatchSolver(g, lanes=lanes, ctas_per_lane=cpl)
+        assert b.query_batch(pairs[:, 0], pairs[:, 1]) == want
+        assert b.query_batch(pairs[:50, 0], pairs[:50, 1]) == want[:50]      # the pool is reusable
+        assert b.last_ms > 0 and len(b.last_meet) == 50
+        b.close()
 
 
 def test_naive_baseline_agrees(bb):
