@@ -96,7 +96,8 @@ constexpr u32 HUB_CHUNK = 256;    // adjacency entries per hub work item (1 KB: 
 // chunk i of a row [r0,r1) covers col[A + i*HUB_CHUNK, A + (i+1)*HUB_CHUNK) with A = r0 rounded down to 4 entries,
 // so that every chunk starts on a 16-byte boundary (cp.async.bulk requirement)
 BIBFS_HD u32 hub_nchunks(u64 r0, u64 r1) { return (u32)((r1 - (r0 & ~3ull) + HUB_CHUNK - 1) / HUB_CHUNK); }
-constexpr u32 HUB_CAP = 16384;    // hub entries per level per rank (overflow: expanded in place)
+constexpr u32 HUB_CAP = 16384;
+constexpr u32 DUMMY_WORDS = 512 * 512;   // one private scratch word per thread of up to 512 CTAs: target of no-op atomics    // hub entries per level per rank (overflow: expanded in place)
 
 struct Ctrl {
     // written by the host (H2D copy from pinned memory) before the launch
@@ -121,7 +122,7 @@ struct Ctrl {
 };
 
 struct Layout {
-    size_t off_vis, off_fbm, off_parent, off_q, off_rq, off_path, off_trace, off_hub, total;
+    size_t off_vis, off_fbm, off_parent, off_q, off_rq, off_path, off_trace, off_hub, off_dummy, total;
     u32 nw;           // bitmap words covering P*B vertices
 };
 
@@ -138,6 +139,7 @@ inline Layout make_layout(u32 B, u32 P, u32 max_path) {
     L.off_path = o;   o += al((size_t)max_path * 4);
     L.off_trace = o;  o += al((size_t)TRACE_CAP * sizeof(bibfs_level_trace));
     L.off_hub = o;    o += al((size_t)HUB_CAP * sizeof(HubEntry));
+    L.off_dummy = o;  o += al((size_t)DUMMY_WORDS * 8);
     L.total = o;
     return L;
 }

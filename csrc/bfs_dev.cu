@@ -75,7 +75,8 @@ constexpr u32 BIG_ROW = 64;          // rows at least this long are strip-mined 
 constexpr int UNR = 4;               // independent edges in flight per lane
 constexpr u32 WPC = BFS_THREADS / 32;
 constexpr u32 SOLO_CAP = 2048;       // entries of the shared-memory queue mirror per side
-constexpr u32 FILTER_MIN = 4096;     // frontiers at least this large pre-check the visited word
+constexpr u32 FILTER_MIN = 4096;
+constexpr u32 STAGE_CAP = 4096;      // grid mode: discoveries a CTA stages in shared memory before one queue reservation     // frontiers at least this large pre-check the visited word
 
 struct Env {
     u32 me, lo, P, B, n, nw;
@@ -90,6 +91,9 @@ struct Env {
     bool filter;       // read the visited word before the atomic (pays off on large frontiers only)
     u32 tag;           // epoch tag stamped on entries sent to other ranks in the current level
     bool smem_src;     // visit_batch reads the adjacency entries from shared memory (hub chunks staged by TMA)
+    // grid mode: per-CTA staging (same-address L2 atomics serialise: ~2400 warps bumping one queue cursor
+    // cost 100+ us per level, 148 CTAs do not)
+    u32* stage; u32* stage_cnt; u32* cta_new; unsigned long long* cta_edges;
     u32* s_sent;       // solo mode: shared copy of Ctrl::sent ([2][MAXR])
     u32* s_rnew;       // solo mode: shared counter of vertices discovered at other ranks
     u64* vis;
@@ -120,26 +124,61 @@ __device__ __forceinline__ HubEntry* hub_of(const KParams& K, u32 r) {
     return reinterpret_cast<HubEntry*>(K.arena[r] + K.L.off_hub);
 }
 
+// private scratch word of the calling thread: where the branch-free claim code sends its no-op atomics
+__device__ __forceinline__ u64* dummy_of(const KParams& K, u32 r) {
+    return reinterpret_cast<u64*>(K.arena[r] + K.L.off_dummy) + ((blockIdx.x * BFS_THREADS + threadIdx.x) % DUMMY_WORDS);
+}
+
 __device__ __forceinline__ u32 lanemask_lt() {
     u32 m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
     return m;
 }
 
-// accumulator updates: shared-window atomics in solo mode, global (L2) atomics in grid mode
-__device__ __forceinline__ u32 acc_take_slots(const Env& E, u32 side, u32 n) {
-    return E.solo ? ptx::atoms_add(&E.sA->q_tail[side], n) : atomicAdd(&E.A->q_tail[side], n);
+// Append the vertices held by the lanes of `mask` (exactly those lanes call this, together) to the
+// local queue of `side`.  Solo mode: shared-memory cursor, entries go straight to the queue (and its
+// shared mirror).  Grid mode: entries are staged in the CTA's shared memory and written to the queue
+// with ONE cursor reservation per CTA at the next synchronisation point (cta_flush); what does not
+// fit in the stage falls back to a warp-sized reservation.
+__device__ __forceinline__ void q_append(const Env& E, u32 side, u32 mask, u32 v) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 leader = __ffs(mask) - 1;
+    const u32 n = __popc(mask), r = __popc(mask & lanemask_lt());
+    if (E.solo) {
+        u32 base = 0;
+        if (lane == leader) base = ptx::atoms_add(&E.sA->q_tail[side], n);
+        base = __shfl_sync(mask, base, leader);
+        const u32 slot = base + r;
+        E.q[side][slot] = v;
+        if (E.sq && slot - E.sq_base < SOLO_CAP) E.sq[slot - E.sq_base] = v;
+    } else {
+        u32 s0 = 0, g = 0;
+        if (lane == leader) {
+            s0 = ptx::atoms_add(E.stage_cnt, n);
+            if (s0 + n > STAGE_CAP) g = atomicAdd(&E.A->q_tail[side], s0 + n - max(s0, STAGE_CAP));
+        }
+        s0 = __shfl_sync(mask, s0, leader);
+        g = __shfl_sync(mask, g, leader);
+        const u32 idx = s0 + r;
+        if (idx < STAGE_CAP) E.stage[idx] = v;
+        else E.q[side][g + (idx - max(s0, STAGE_CAP))] = v;
+    }
 }
 __device__ __forceinline__ void acc_note_meet(const Env& E, u32 v) {
     if (E.solo) ptx::reds_min(&E.sA->meet_local, v); else atomicMin(&E.A->meet_local, v);
+}
+// Has this rank already seen a meeting vertex in the current level?  Every hit of a level gives the
+// same path length, so the rest of the level can be skipped (what v1's `break` does, v1/main-v1.cpp:61).
+__device__ __forceinline__ bool acc_meet_seen(const Env& E) {
+    return (E.solo ? *reinterpret_cast<volatile u32*>(&E.sA->meet_local) : ptx::ld_relaxed_gpu(&E.A->meet_local)) != NO_V;
 }
 __device__ __forceinline__ void acc_flush(const Env& E, u32 cnt, u64 edges) {
     if (E.solo) {
         if (cnt) ptx::reds_add(&E.sA->new_count, cnt);
         if (edges) ptx::reds_add64(&E.sA->edges, edges);
     } else {
-        if (cnt) atomicAdd(&E.A->new_count, cnt);
-        if (edges) atomicAdd(&E.A->edges, (unsigned long long)edges);
+        if (cnt) ptx::reds_add(E.cta_new, cnt);
+        if (edges) ptx::reds_add64(E.cta_edges, edges);
     }
 }
 
@@ -526,18 +565,10 @@ __device__ __forceinline__ void enqueue(const KParams& K, const Env& E, u32 side
     const u32 lane = threadIdx.x & 31;
     if (!MULTI) {
         const u32 m = __ballot_sync(FULL, c.isnew);
-        if (m) {
-            const u32 leader = __ffs(m) - 1;
-            u32 base = 0;
-            if (lane == leader) base = acc_take_slots(E, side, (u32)__popc(m));
-            base = __shfl_sync(FULL, base, leader);
-            if (c.isnew) {
-                const u32 slot = base + __popc(m & lanemask_lt());
-                E.q[side][slot] = v;
-                E.parent[side][v - E.lo] = u;
-                if (E.sq && slot - E.sq_base < SOLO_CAP) E.sq[slot - E.sq_base] = v;
-                ptx::prefetch_l2(E.row_ptr + (v - E.lo));
-            }
+        if (c.isnew) {
+            q_append(E, side, m, v);
+            E.parent[side][v - E.lo] = u;
+            ptx::prefetch_l2(E.row_ptr + (v - E.lo));
         }
     } else {
         const u32 key = c.isnew ? c.dest : 0xFFu;
@@ -547,12 +578,8 @@ __device__ __forceinline__ void enqueue(const KParams& K, const Env& E, u32 side
             const u32 rank_in = __popc(grp & lanemask_lt());
             u32 base = 0;
             if (c.dest == E.me) {
-                if (lane == leader) base = acc_take_slots(E, side, (u32)__popc(grp));
-                base = __shfl_sync(grp, base, leader);
-                const u32 slot = base + rank_in;
-                E.q[side][slot] = v;
+                q_append(E, side, grp, v);
                 E.parent[side][v - E.lo] = u;
-                if (E.sq && slot - E.sq_base < SOLO_CAP) E.sq[slot - E.sq_base] = v;
                 ptx::prefetch_l2(E.row_ptr + (v - E.lo));
             } else {
                 if (lane == leader) {
@@ -590,35 +617,55 @@ __device__ __noinline__ u32 visit_batch(const KParams& K, const Env& E, u32 side
     DBG_STAMP(4, v[0] + v[1] + v[2] + v[3]);
 #pragma unroll
     for (int k = 0; k < UNR; ++k) seen[k] = ok[k] ? (E.filter ? E.vis[v[k] >> 5] : 0ull) : ~0ull;   // filter only; may be stale
+    {
+        // Branch-free issue (measured: the branchy form serialises the round trips).  Slots with nothing to
+        // claim OR a zero into a private scratch word, so all UNR local atomics, and then all UNR owner-side
+        // atomics of the multi-rank case, are in flight together.
+        u64* const dummy = dummy_of(K, E.me);
+        const u32 sh = 32u * side, osh = 32u - sh;
+        u64 old[UNR];
+        bool act[UNR];
 #pragma unroll
-    for (int k = 0; k < UNR; ++k) c[k] = claim<MULTI>(K, E, side, ok[k], v[k], seen[k]);
+        for (int k = 0; k < UNR; ++k) {
+            act[k] = ok[k] && !((seen[k] >> ((v[k] & 31u) + sh)) & 1ull);
+            old[k] = ptx::atom_or_gpu(act[k] ? &E.vis[v[k] >> 5] : dummy, act[k] ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
+        }
+#pragma unroll
+        for (int k = 0; k < UNR; ++k) {
+            c[k].dest = E.me;
+            c[k].isnew = act[k] && !((old[k] >> ((v[k] & 31u) + sh)) & 1ull);
+        }
+        if (MULTI) {
+            bool rem[UNR];
+            u64 rold[UNR];
+#pragma unroll
+            for (int k = 0; k < UNR; ++k) {
+                const u32 dest = c[k].isnew ? v[k] / K.B : E.me;
+                rem[k] = dest != E.me;
+                c[k].dest = dest;
+                rold[k] = ptx::atom_or_sys(rem[k] ? (vis_of(K, dest) + (v[k] >> 5)) : dummy, rem[k] ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
+            }
+#pragma unroll
+            for (int k = 0; k < UNR; ++k)
+                if (rem[k]) { old[k] = rold[k]; c[k].isnew = !((rold[k] >> ((v[k] & 31u) + sh)) & 1ull); }
+        }
+#pragma unroll
+        for (int k = 0; k < UNR; ++k) c[k].meet = c[k].isnew && ((old[k] >> ((v[k] & 31u) + osh)) & 1ull);
+    }
     DBG_STAMP(5, (u32)c[0].isnew + (u32)c[1].isnew + (u32)c[2].isnew + (u32)c[3].isnew);
     if (MULTI) {
 #pragma unroll
         for (int k = 0; k < UNR; ++k) enqueue<MULTI>(K, E, side, c[k], uu[k], v[k], cnt);
     } else {
-        // one queue-cursor atomic for the whole batch
-        const u32 lane = threadIdx.x & 31;
-        u32 m[UNR];
-        u32 total = 0;
 #pragma unroll
-        for (int k = 0; k < UNR; ++k) { m[k] = __ballot_sync(FULL, c[k].isnew); total += __popc(m[k]); }
-        if (total) {
-            u32 base = 0;
-            if (lane == 0) base = acc_take_slots(E, side, total);
-            base = __shfl_sync(FULL, base, 0);
-#pragma unroll
-            for (int k = 0; k < UNR; ++k) {
-                if (c[k].isnew) {
-                    const u32 slot = base + __popc(m[k] & lanemask_lt());
-                    E.q[side][slot] = v[k];
-                    E.parent[side][v[k] - E.lo] = uu[k];
-                    if (E.sq && slot - E.sq_base < SOLO_CAP) E.sq[slot - E.sq_base] = v[k];
-                    ptx::prefetch_l2(E.row_ptr + (v[k] - E.lo));
-                    ++cnt;
-                    if (c[k].meet) acc_note_meet(E, v[k]);
-                }
-                base += __popc(m[k]);
+        for (int k = 0; k < UNR; ++k) {
+            const u32 m = __ballot_sync(FULL, c[k].isnew);
+            if (c[k].isnew) {
+                q_append(E, side, m, v[k]);
+                E.parent[side][v[k] - E.lo] = uu[k];
+                ptx::prefetch_l2(E.row_ptr + (v[k] - E.lo));
+                ++cnt;
+                if (c[k].meet) acc_note_meet(E, v[k]);
             }
         }
     }
@@ -655,6 +702,7 @@ __device__ __noinline__ void expand_td(const KParams& K, const Env& E, const Lev
     u64 edges = 0;
     const u32 nbatches = (total + vpw - 1) / vpw;
     for (u32 b = warp_gid; b < nbatches; b += nwarps) {
+        if (acc_meet_seen(E)) break;               // the search is over: any hit of this level is a shortest path
         const u32 i = b * vpw + lane;
         u32 u = 0;
         u64 r0 = 0, r1 = 0;
@@ -797,6 +845,11 @@ __device__ __noinline__ void expand_hubs(const KParams& K, const Env& E0, const 
     if (lane == 0 && cur.valid) { ptx::mbar_expect_tx(&bars[0], cur.bytes); ptx::bulk_g2s(stage, cur.src, cur.bytes, &bars[0]); }
     for (u32 i = 0; c < st.hub_chunks; c += nwarps, ++i) {
         const u32 buf = i & 1u;
+        if (acc_meet_seen(E)) {
+            // stop early, but drain the copy already in flight so that the barrier phase stays in step
+            if (cur.valid) { ptx::mbar_wait(&bars[buf], (parity >> buf) & 1u); parity ^= 1u << buf; }
+            break;
+        }
         // start the copy of this warp's next chunk into the other buffer
         const u32 cn = c + nwarps;
         HubChunk nxt = hub_lookup(H, ne, E.col, cn < st.hub_chunks ? cn : 0);
@@ -876,16 +929,13 @@ __device__ __noinline__ void expand_bu(const KParams& K, const Env& E, const Lev
         }
         const u32 newmask = __ballot_sync(FULL, found);
         if (newmask) {
-            u32 base = 0;
             if (lane == 0) {
                 E.vis[wg] = word | ((u64)newmask << (32u * side));
                 const u32 meetmask = newmask & (u32)(word >> (32u * (1u - side)));
                 if (meetmask) atomicMin(&E.A->meet_local, E.lo + wl * 32u + (u32)(__ffs(meetmask) - 1));
-                base = atomicAdd(&E.A->q_tail[side], (u32)__popc(newmask));
             }
-            base = __shfl_sync(FULL, base, 0);
             if (found) {
-                E.q[side][base + __popc(newmask & lanemask_lt())] = v;
+                q_append(E, side, newmask, v);
                 E.parent[side][v - E.lo] = par;
                 ++cnt;
             }
@@ -928,6 +978,9 @@ struct Smem {
     u32 qcur[2], qvalid[2];
     unsigned long long pend_edges, pend_visited;   // solo levels: totals not yet added to Ctrl
     u64 hub_bar[WPC][2];                           // hub phase: one mbarrier per warp and buffer
+    u32 stage_cnt, stage_base, cta_new, pad0;      // grid mode: per-CTA staging of discoveries / counters
+    unsigned long long cta_edges;
+    u32 stage[STAGE_CAP];
     alignas(128) u32 q[2][2][SOLO_CAP];            // solo: frontier mirrors; hub phase: per-warp TMA staging (WPC x 2 KB)
 };
 static_assert(sizeof(u32) * 2 * 2 * SOLO_CAP >= WPC * 2 * HUB_CHUNK * sizeof(u32), "staging area too small");
@@ -974,6 +1027,9 @@ struct SoloLevel {          // written by thread 0 at the end of a level, read b
 static_assert(sizeof(SoloLevel) == 32, "two LDS.128");
 
 constexpr int SW = 8;       // adjacency entries per lane per round
+constexpr u32 SOLO_HUB_ROW = 128;   // solo mode packs the frontier into few warps: longer rows are shared by the CTA or the grid
+constexpr u32 CL_CAP = 64;          // rows the CTA keeps for itself per level ...
+constexpr u32 CL_MAX_EDGES = 16384; // ... as long as they add up to no more than this many entries
 
 template <bool MULTI>
 __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 deadline) {
@@ -982,7 +1038,10 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
     __shared__ __align__(16) SoloLevel s_lv;
     __shared__ u32 s_sent[2][MAXR];      // MULTI: entries appended to each peer's segment (cumulative, per side)
     __shared__ u32 s_rnew;               // MULTI: vertices discovered at other ranks in this level
-    __shared__ u64 s_mail[2];            // MULTI: reduced (edges, meet<<32 | discovered) handed from the leader warp to thread 0
+    __shared__ u64 s_mail[2];
+    // rows of 128..: first choice is the CTA itself (all 16 warps share them, no grid wake-up needed)
+    __shared__ u32 s_cl_n, s_cl_edges, s_cl_u[CL_CAP];
+    __shared__ u64 s_cl_r0[CL_CAP], s_cl_r1[CL_CAP];            // MULTI: reduced (edges, meet<<32 | discovered) handed from the leader warp to thread 0
     E.solo = true; E.A = &sm.acc; E.sA = &sm.acc; E.filter = false; E.s_hub = &sm.hub;
     E.s_sent = &s_sent[0][0]; E.s_rnew = &s_rnew;
     // thread 0 keeps the level state in registers across levels
@@ -1003,7 +1062,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         s_lv = lv;
     };
     if (MULTI && tid < 2 * MAXR) s_sent[tid / MAXR][tid % MAXR] = ptx::ld_relaxed_gpu(&E.C->sent[tid / MAXR][tid % MAXR]);
-    if (tid == 0) { make_level(st.side); s_rnew = 0; }
+    if (tid == 0) { make_level(st.side); s_rnew = 0; s_cl_n = 0; s_cl_edges = 0; }
     __syncthreads();
     while (true) {
         DBG_STAMP(0, tid);
@@ -1030,7 +1089,12 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         u32 deg = (u32)min(r1 - r0, (u64)0xFFFFFFFFu);
         DBG_STAMP(1, deg);
         const u32 nedges = deg;                      // statistics: hub rows count as inspected here
-        if (deg >= HUB_ROW) { solo_push_hub(K, E, sm, u, r0, r1); deg = 0; }
+        if (deg >= SOLO_HUB_ROW) {
+            const u32 slot = deg < HUB_ROW * 8u ? ptx::atoms_add(&s_cl_n, 1u) : CL_CAP;
+            if (slot < CL_CAP) { s_cl_u[slot] = u; s_cl_r0[slot] = r0; s_cl_r1[slot] = r1; ptx::reds_add(&s_cl_edges, deg); }
+            else solo_push_hub(K, E, sm, u, r0, r1);          // very long row, or the CTA list is full: whole grid
+            deg = 0;
+        }
         u32 sdeg = deg < 32u ? deg : 0u;
         DBG_STAMP(2, sdeg);
         // rows shorter than a warp: each lane walks its own row, SW entries per round
@@ -1039,7 +1103,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             u64 old[SW];
             // branch-free issue: idle slots re-read the row's first entry and OR a zero into a private
             // scratch word, so that all SW loads and then all SW claims are in flight together
-            u64* const dummy = reinterpret_cast<u64*>(fbm_of(K, E.me, 0, 0)) + tid;
+            u64* const dummy = dummy_of(K, E.me);
 #pragma unroll
             for (int k = 0; k < SW; ++k) v[k] = __ldg(E.col + r0 + ((e0 + k < sdeg) ? e0 + k : 0u));
 #pragma unroll
@@ -1060,7 +1124,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             if (MULTI && __any_sync(FULL, newmask != 0)) {
                 // vertices of other ranks: the local bit was only a "not forwarded yet" filter — claim at the
                 // owner.  Branch-free again so that the NVLink round trips (1.6 us each) overlap.
-                u64* const dummy = reinterpret_cast<u64*>(fbm_of(K, E.me, 0, 0)) + tid;
+                u64* const dummy = dummy_of(K, E.me);
                 u64 rold[SW];
 #pragma unroll
                 for (int k = 0; k < SW; ++k) {
@@ -1134,6 +1198,26 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             if (lane == 0 && wsum) ptx::reds_add64(&sm.acc.edges, wsum);
         }
         __syncthreads();
+        if (s_cl_n) {
+            // long rows collected by this level: shared by all warps of the CTA in 128-entry pieces, unless there
+            // is so much of it that the grid should take over (hub phase)
+            const u32 ncl = min(s_cl_n, CL_CAP);
+            if (s_cl_edges <= CL_MAX_EDGES && !sm.hub) {
+                E.sq = out; E.sq_base = base_tail;
+                u32 cnt = 0, piece = 0;
+                for (u32 i = 0; i < ncl; ++i) {
+                    const u64 rb = s_cl_r0[i], re = s_cl_r1[i];
+                    const u32 uu = s_cl_u[i];
+                    for (u64 p = rb; p < re; p += 32 * UNR, ++piece)
+                        if (piece % WPC == warp) expand_range<MULTI>(K, E, side, uu, p, min(re, p + 32 * UNR), cnt);
+                }
+                (void)cnt;
+            } else if (tid < ncl) {
+                solo_push_hub(K, E, sm, s_cl_u[tid], s_cl_r0[tid], s_cl_r1[tid]);
+            }
+            __syncthreads();
+            if (tid == 0) { s_cl_n = 0; s_cl_edges = 0; }
+        }
         DBG_STAMP(6, tid);
         // ---- level end
         u32 found = 0, meet = NO_V;
@@ -1261,7 +1345,8 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
 // ------------------------------------------------------------------------------------------
 template <bool MULTI>
 __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant__ KParams K) {
-    __shared__ Smem sm;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
     LevelState& st = sm.st;        // this CTA's copy of the level state (the leader CTA's is authoritative)
     Acc& s_acc = sm.acc;           // leader CTA: accumulators of solo levels / staging at sync points
     u32& s_fail = sm.fail;
@@ -1280,7 +1365,8 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     E.C = ctrl_of(K, E.me);
     E.A = &E.C->acc;
     E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = true;
-    E.sA = &s_acc; E.solo = false; E.tag = 0; E.smem_src = false; E.s_sent = nullptr; E.s_rnew = nullptr;
+    E.sA = &s_acc; E.solo = false; E.tag = 0; E.smem_src = false;
+    E.stage = sm.stage; E.stage_cnt = &sm.stage_cnt; E.cta_new = &sm.cta_new; E.cta_edges = &sm.cta_edges; E.s_sent = nullptr; E.s_rnew = nullptr;
     E.vis = vis_of(K, E.me);
     E.parent[0] = parent_of(K, E.me, 0); E.parent[1] = parent_of(K, E.me, 1);
     E.q[0] = q_of(K, E.me, 0); E.q[1] = q_of(K, E.me, 1);
@@ -1290,7 +1376,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     const u64 deadline = ptx::globaltimer_ns() + (u64)K.watchdog_ms * 1000000ull;
     const u64 genbase = (u64)K.seq << 32;
     const bool is_leader_cta = (E.cta == 0);
-    if (tid == 0) { s_fail = 0; s_hub = 0; s_qvalid[0] = 0; s_qvalid[1] = 0; s_qcur[0] = 0; s_qcur[1] = 0; sm.pend_edges = 0; sm.pend_visited = 0; }
+    if (tid == 0) { s_fail = 0; s_hub = 0; s_qvalid[0] = 0; s_qvalid[1] = 0; s_qcur[0] = 0; s_qcur[1] = 0; sm.pend_edges = 0; sm.pend_visited = 0; sm.stage_cnt = 0; sm.cta_new = 0; sm.cta_edges = 0; }
     if (lane == 0) { ptx::mbar_init(&sm.hub_bar[warp][0], 1); ptx::mbar_init(&sm.hub_bar[warp][1], 1); ptx::mbar_fence_init(); }
     u32 hub_parity = 0;            // phase bits of this warp's two hub barriers
     __syncthreads();
@@ -1343,6 +1429,21 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     // Synchronisation point of grid-mode phases.  Returns false if the query was aborted.
     auto sync_grid = [&](int kind, u32 mode) -> bool {
         __syncthreads();
+        // ---- CTA flush: one queue reservation and one counter update per CTA
+        if (tid == 0) {
+            const u32 cnt = min(sm.stage_cnt, STAGE_CAP);
+            sm.stage_base = cnt ? atomicAdd(&C->acc.q_tail[st.side], cnt) : 0u;
+            if (sm.cta_new) atomicAdd(&C->acc.new_count, sm.cta_new);
+            if (sm.cta_edges) atomicAdd(&C->acc.edges, sm.cta_edges);
+        }
+        __syncthreads();
+        {
+            const u32 cnt = min(sm.stage_cnt, STAGE_CAP);
+            u32* qd = E.q[st.side] + sm.stage_base;
+            for (u32 i = tid; i < cnt; i += BFS_THREADS) qd[i] = sm.stage[i];
+        }
+        __syncthreads();
+        if (tid == 0) { sm.stage_cnt = 0; sm.cta_new = 0; sm.cta_edges = 0; }
         if (!is_leader_cta) {
             if (tid == 0) {
                 if (MULTI && mode == PH_BU) ptx::fence_sys();   // bitmap slices pushed with plain stores
@@ -1525,12 +1626,22 @@ __global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) 
 // ------------------------------------------------------------------------------------------
 // launch helpers used by ctx.cu
 // ------------------------------------------------------------------------------------------
+static int bfs_prepare(bool multi) {
+    static bool done[2] = {false, false};
+    if (done[multi]) return 0;
+    if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    done[multi] = true;      // (per process; every device of the process gets the attribute on first use below)
+    return 0;
+}
+
 int bfs_max_ctas_per_device(bool multi, int* out) {
     int dev = 0, sms = 0, per = 0;
     BIBFS_CUDA_TRY(cudaGetDevice(&dev));
     BIBFS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    if (multi) BIBFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_bibfs<true>, BFS_THREADS, 0));
-    else BIBFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_bibfs<false>, BFS_THREADS, 0));
+    if (bfs_prepare(multi)) return 1;
+    if (multi) BIBFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_bibfs<true>, BFS_THREADS, sizeof(Smem)));
+    else BIBFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_bibfs<false>, BFS_THREADS, sizeof(Smem)));
     if (per < 1) return fail("search kernel does not fit on an SM");
     *out = sms * per;
     return 0;
@@ -1539,8 +1650,10 @@ int bfs_max_ctas_per_device(bool multi, int* out) {
 int bfs_launch(const KParams& K, bool multi, cudaStream_t st) {
     void* args[] = {(void*)&K};
     dim3 grid(K.cpr * K.vranks), block(BFS_THREADS);
-    if (multi) BIBFS_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_bibfs<true>, grid, block, args, 0, st));
-    else BIBFS_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_bibfs<false>, grid, block, args, 0, st));
+    if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    if (multi) BIBFS_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_bibfs<true>, grid, block, args, sizeof(Smem), st));
+    else BIBFS_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_bibfs<false>, grid, block, args, sizeof(Smem), st));
     count_launch();
     return 0;
 }
