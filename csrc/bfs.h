@@ -63,9 +63,11 @@ struct LevelState {
     u32 wake;                  // number of local wake-ups issued so far (gen low word)
     u32 pad;
     u64 xepoch;                // cross-rank barrier epoch
+    u64 edges_total;           // adjacency entries inspected so far (all ranks)
+    u64 visited_total;         // vertices reached so far (all ranks, both sides)
 };
 
-struct alignas(16) Result {
+struct alignas(16) Result {   // 64 bytes (PATH_HDR_WORDS words)
     i32 length;
     u32 meet;
     u32 depth_s, depth_t;
@@ -96,6 +98,8 @@ constexpr u32 HUB_CHUNK = 256;    // adjacency entries per hub work item (1 KB: 
 // chunk i of a row [r0,r1) covers col[A + i*HUB_CHUNK, A + (i+1)*HUB_CHUNK) with A = r0 rounded down to 4 entries,
 // so that every chunk starts on a 16-byte boundary (cp.async.bulk requirement)
 BIBFS_HD u32 hub_nchunks(u64 r0, u64 r1) { return (u32)((r1 - (r0 & ~3ull) + HUB_CHUNK - 1) / HUB_CHUNK); }
+constexpr u32 BAR_WAYS = 16;
+constexpr u32 PATH_HDR_WORDS = 16;   // sizeof(Result) / 4
 constexpr u32 HUB_CAP = 16384;
 constexpr u32 DUMMY_WORDS = 512 * 512;   // one private scratch word per thread of up to 512 CTAs: target of no-op atomics    // hub entries per level per rank (overflow: expanded in place)
 
@@ -104,7 +108,9 @@ struct Ctrl {
     alignas(128) u32 q_src;
     u32 q_dst;
     // local grid barrier
-    alignas(128) u32 bar_count;
+    // arrive counters: CTA c bumps counter c % BAR_WAYS (one 128-byte line each); 148 arrivals on ONE word serialise
+    // in the L2 atomic unit for ~2 us, sixteen words are bumped in parallel
+    struct alignas(128) BarWay { u32 count; } bar_way[BAR_WAYS];
     alignas(128) u64 bar_gen;            // (launch seq << 32) | wake-ups
     // cross-rank exchange: slot[parity][p] is written by rank p (tagged words, relaxed stores)
     alignas(128) LSlot slot[2][MAXR];    // [epoch parity][sender]
@@ -136,7 +142,7 @@ inline Layout make_layout(u32 B, u32 P, u32 max_path) {
     L.off_parent = o; o += al((size_t)B * 4 * 2);
     L.off_q = o;      o += al((size_t)B * 4 * 2);
     L.off_rq = o;     o += (P > 1) ? al((size_t)B * 8 * 2 * P) : 0;   // tagged 8-byte entries
-    L.off_path = o;   o += al((size_t)max_path * 4);
+    L.off_path = o;   o += al((size_t)max_path * 4 + PATH_HDR_WORDS * 4);   // [copy of Result | path]: one D2H fetches both
     L.off_trace = o;  o += al((size_t)TRACE_CAP * sizeof(bibfs_level_trace));
     L.off_hub = o;    o += al((size_t)HUB_CAP * sizeof(HubEntry));
     L.off_dummy = o;  o += al((size_t)DUMMY_WORDS * 8);

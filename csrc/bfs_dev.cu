@@ -63,7 +63,16 @@ __device__ u32 g_dbg_level;
             g_dbg2[g_dbg_level - 1][slot] = _t;                                                  \
         }                                                                                        \
     } while (0)
+#define DBG_STAMP3(slot, dep)                                                                    \
+    do {                                                                                         \
+        if (blockIdx.x == 1 && threadIdx.x == 0 && g_dbg_level > 0 && g_dbg_level <= 256) {       \
+            u64 _t;                                                                              \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t) : "l"((u64)(dep)) : "memory"); \
+            g_dbg2[g_dbg_level - 1][slot] = _t;                                                  \
+        }                                                                                        \
+    } while (0)
 #else
+#define DBG_STAMP3(slot, dep) do { } while (0)
 #define DBG_STAMP(slot, dep) do { } while (0)
 #define DBG_STAMP2(slot, dep) do { } while (0)
 #endif
@@ -189,10 +198,11 @@ __device__ __forceinline__ bool expired(Ctrl* C, u64 deadline) {
     return ptx::globaltimer_ns() > deadline || ptx::ld_relaxed_gpu(&C->abort_flag) != 0;
 }
 
-__device__ bool wait_gen(Ctrl* C, u64 want, u64 deadline) {
+// `parked`: the CTA may wait for many levels (solo mode) -> back off; otherwise the release is imminent -> poll hard
+__device__ bool wait_gen(Ctrl* C, u64 want, u64 deadline, bool parked = true) {
     u32 spins = 0;
     while (ptx::ld_acquire_gpu(&C->bar_gen) < want) {
-        if (++spins > 64) {
+        if (++spins > (parked ? 64u : 4096u)) {
             ptx::nanosleep(32);
             if ((spins & 255u) == 0 && expired(C, deadline)) return false;
         }
@@ -200,12 +210,20 @@ __device__ bool wait_gen(Ctrl* C, u64 want, u64 deadline) {
     return true;
 }
 
-__device__ bool wait_count(Ctrl* C, u32 want, u64 deadline) {
-    u32 spins = 0;
-    while (ptx::ld_acquire_gpu(&C->bar_count) < want) {
-        if (++spins > 64 && (spins & 255u) == 0 && expired(C, deadline)) return false;
+// leader warp: lane w < BAR_WAYS waits until every non-leader CTA mapped to way w has arrived, then resets the way
+__device__ bool wait_count(Ctrl* C, u32 cpr, u64 deadline) {
+    const u32 lane = threadIdx.x & 31;
+    bool ok = true;
+    if (lane < BAR_WAYS) {
+        // CTAs 1..cpr-1 arrive; CTA c uses way c % BAR_WAYS
+        const u32 want = lane < cpr ? (cpr - 1u - lane) / BAR_WAYS + (lane != 0 ? 1u : 0u) : 0u;
+        u32 spins = 0;
+        while (want && ptx::ld_acquire_gpu(&C->bar_way[lane].count) < want) {
+            if (++spins > 64 && (spins & 255u) == 0 && expired(C, deadline)) { ok = false; break; }
+        }
+        if (want) ptx::st_relaxed_gpu(&C->bar_way[lane].count, 0u);
     }
-    return true;
+    return __all_sync(FULL, ok);
 }
 
 // poll the four tagged words a peer writes into this rank's slot until they carry `tag`
@@ -263,7 +281,8 @@ __device__ __noinline__ void write_result(const KParams& K, Ctrl* C, const Level
     R.levels_bu = G.levels_bu;
     R.status = (i32)G.status;
     R.path_len = 0;
-    R.edges_scanned = C->edges_total;
+    R.edges_scanned = G.edges_total;
+    R.vertices_visited = G.visited_total;
     R.t_end_ns = ptx::globaltimer_ns();
     C->xepoch = G.xepoch;
 }
@@ -378,8 +397,8 @@ __device__ __noinline__ bool leader_sync(const KParams& K, const Env& E, LevelSt
         else G.fbm_valid[side] = 0;
         G.q_lo[side] = G.q_hi[side];
         G.q_hi[side] = A.q_tail[side];
-        C->edges_total += etot;   // all ranks' adjacency entries of this level
-        C->res.vertices_visited += total;
+        G.edges_total += etot;    // all ranks' adjacency entries of this level
+        G.visited_total += total;
         if ((K.flags & BIBFS_F_TRACE) && C->trace_count < TRACE_CAP) {
             bibfs_level_trace& T = trace_of(K, E.me)[C->trace_count++];
             T.side = side; T.mode = mode | (level_mode == PH_TD_HUB ? 8u : 0u); T.frontier = expanded; T.discovered = total;
@@ -418,14 +437,13 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
     const u32 lane = threadIdx.x & 31;
     const u32 src = K.query_in_ctrl ? C->q_src : K.src, dst = K.query_in_ctrl ? C->q_dst : K.dst;
     if (lane == 0) {
-        C->bar_count = 0;
+        for (u32 w = 0; w < BAR_WAYS; ++w) C->bar_way[w].count = 0;
         A.q_tail[0] = 0; A.q_tail[1] = 0;
         A.new_count = 0; A.meet_local = NO_V; A.edges = 0;
         C->hub_packed = 0;
         for (u32 p = 0; p < MAXR; ++p) { C->sent[0][p] = 0; C->sent[1][p] = 0; }
-        C->edges_total = 0;
         C->trace_count = 0;
-        C->res.vertices_visited = 2;
+        G.edges_total = 0; G.visited_total = 2;
         C->res.t_begin_ns = ptx::globaltimer_ns();
         G.phase = PH_TD_SOLO; G.side = 0; G.levels = 0; G.levels_bu = 0;
         G.depth[0] = G.depth[1] = 0;
@@ -441,7 +459,7 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
         G.xepoch = C->xepoch;
         const bool bad = src >= K.n || dst >= K.n;
         if (bad) { G.status = 2; G.phase = PH_DONE; }
-        else if (src == dst) { G.length = 0; G.meet = src; G.phase = PH_DONE; C->res.vertices_visited = 1; }
+        else if (src == dst) { G.length = 0; G.meet = src; G.phase = PH_DONE; G.visited_total = 1; }
         else {
             const u32 hi = min(K.n, E.lo + K.B);
             if (src >= E.lo && src < hi) {
@@ -1314,8 +1332,8 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
                 sm.qcur[0] = cur0; sm.qcur[1] = cur1; sm.qvalid[0] = val0; sm.qvalid[1] = val1;
                 sm.acc.new_count = (st.phase == PH_TD_HUB) ? sm.acc.new_count : 0;
                 if (stop == 2) decide_next(K, st);
-                C->edges_total += pend_edges;
-                C->res.vertices_visited += pend_vis;
+                st.edges_total += pend_edges;
+                st.visited_total += pend_vis;
                 if (MULTI)
                     for (u32 p = 0; p < MAXR; ++p) { C->sent[0][p] = s_sent[0][p]; C->sent[1][p] = s_sent[1][p]; }
                 s_lv.side_flags = 8u;
@@ -1429,40 +1447,40 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     // Synchronisation point of grid-mode phases.  Returns false if the query was aborted.
     auto sync_grid = [&](int kind, u32 mode) -> bool {
         __syncthreads();
-        // ---- CTA flush: one queue reservation and one counter update per CTA
-        if (tid == 0) {
-            const u32 cnt = min(sm.stage_cnt, STAGE_CAP);
-            sm.stage_base = cnt ? atomicAdd(&C->acc.q_tail[st.side], cnt) : 0u;
-            if (sm.cta_new) atomicAdd(&C->acc.new_count, sm.cta_new);
-            if (sm.cta_edges) atomicAdd(&C->acc.edges, sm.cta_edges);
+        // ---- CTA flush: one queue reservation and one counter update per CTA (skipped by CTAs that found nothing)
+        if (sm.stage_cnt | sm.cta_new | (u32)(sm.cta_edges != 0)) {
+            if (tid == 0) {
+                const u32 cnt = min(sm.stage_cnt, STAGE_CAP);
+                sm.stage_base = cnt ? atomicAdd(&C->acc.q_tail[st.side], cnt) : 0u;
+                if (sm.cta_new) atomicAdd(&C->acc.new_count, sm.cta_new);
+                if (sm.cta_edges) atomicAdd(&C->acc.edges, sm.cta_edges);
+            }
+            __syncthreads();
+            {
+                const u32 cnt = min(sm.stage_cnt, STAGE_CAP);
+                u32* qd = E.q[st.side] + sm.stage_base;
+                for (u32 i = tid; i < cnt; i += BFS_THREADS) qd[i] = sm.stage[i];
+            }
+            __syncthreads();
+            if (tid == 0) { sm.stage_cnt = 0; sm.cta_new = 0; sm.cta_edges = 0; }
         }
-        __syncthreads();
-        {
-            const u32 cnt = min(sm.stage_cnt, STAGE_CAP);
-            u32* qd = E.q[st.side] + sm.stage_base;
-            for (u32 i = tid; i < cnt; i += BFS_THREADS) qd[i] = sm.stage[i];
-        }
-        __syncthreads();
-        if (tid == 0) { sm.stage_cnt = 0; sm.cta_new = 0; sm.cta_edges = 0; }
         if (!is_leader_cta) {
             if (tid == 0) {
                 if (MULTI && mode == PH_BU) ptx::fence_sys();   // bitmap slices pushed with plain stores
-                ptx::red_release_gpu_add(&C->bar_count, 1u);
-                if (!wait_gen(C, genbase | (u64)(st.wake + 1u), deadline)) s_fail = 1;
+                ptx::red_release_gpu_add(&C->bar_way[E.cta % BAR_WAYS].count, 1u);
+                DBG_STAMP3(4, tid);      // arrived
+                if (!wait_gen(C, genbase | (u64)(st.wake + 1u), deadline, false)) s_fail = 1;
+                DBG_STAMP3(5, tid);      // released
             }
             __syncthreads();
             if (s_fail) return false;
             load_state();
+            DBG_STAMP3(6, st.phase);     // state loaded
             return true;
         }
         if (warp == 0) {
-            bool ok = true;
-            if (lane == 0) {
-                ok = wait_count(C, E.cpr - 1u, deadline);
-                ptx::st_relaxed_gpu(&C->bar_count, 0u);
-                pull_acc(s_acc, &C->acc);               // the grid's accumulators -> shared memory
-            }
-            ok = __shfl_sync(FULL, ok, 0);
+            bool ok = wait_count(C, E.cpr, deadline);
+            if (lane == 0) pull_acc(s_acc, &C->acc);    // the grid's accumulators -> shared memory
             if (lane == 0 && kind == SYNC_LEVEL) s_qvalid[st.side] = 0;   // grid levels do not feed the solo mirror
             __syncwarp();
             if (ok) ok = leader_sync<MULTI>(K, E, st, s_acc, kind, mode, deadline, true);
@@ -1529,6 +1547,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         } else if (phase == PH_TD_GRID) {
             E.A = &C->acc;
             E.tag = (u32)(st.xepoch + 1);
+            E.filter = st.nf[st.side] >= FILTER_MIN;
             expand_td<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
             alive = sync_grid(SYNC_LEVEL, PH_TD_GRID);
         } else if (phase == PH_TD_HUB) {
@@ -1598,12 +1617,12 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
 __global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) {
     Ctrl* C = ctrl_of(K, K.rank_lo);
     Result& R = C->res;
-    u32* path = reinterpret_cast<u32*>(K.arena[K.rank_lo] + K.L.off_path);
-    if (R.status != 0 || R.length < 0) return;
-    const u32 L = (u32)R.length;
-    if (L + 1u > K.max_path) return;
+    u32* hdr = reinterpret_cast<u32*>(K.arena[K.rank_lo] + K.L.off_path);   // [copy of Result | path]
+    u32* path = hdr + PATH_HDR_WORDS;
+    const bool ok = R.status == 0 && R.length >= 0 && (u32)R.length + 1u <= K.max_path;
+    const u32 L = ok ? (u32)R.length : 0u;
     const u32 ds = R.depth_s;
-    if (threadIdx.x == 0) {
+    if (ok && threadIdx.x == 0) {
         u32 cur = R.meet;
         for (u32 pos = ds;; --pos) {
             path[pos] = cur;
@@ -1611,7 +1630,7 @@ __global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) 
             const u32 o = cur / K.B;
             cur = __ldcg(parent_of(K, o, 0) + (cur - o * K.B));
         }
-    } else if (threadIdx.x == 32) {
+    } else if (ok && threadIdx.x == 32) {
         u32 cur = R.meet;
         for (u32 pos = ds; pos < L && cur < K.n; ++pos) {
             const u32 o = cur / K.B;
@@ -1620,7 +1639,10 @@ __global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) 
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0) R.path_len = L + 1u;
+    if (threadIdx.x == 0) R.path_len = ok ? L + 1u : 0u;
+    __syncthreads();
+    static_assert(sizeof(Result) == PATH_HDR_WORDS * 4, "result header size");
+    if (threadIdx.x < PATH_HDR_WORDS) hdr[threadIdx.x] = reinterpret_cast<const u32*>(&R)[threadIdx.x];
 }
 
 // ------------------------------------------------------------------------------------------

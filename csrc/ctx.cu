@@ -86,7 +86,7 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
         c->arena_all[desc->rank_lo + i] = c->arena_local[i];
     }
     for (int k = 0; k < 3; ++k) cudaEventCreate(&c->ev[k]);
-    c->h_stage_bytes = 256 + (size_t)c->d.max_path * 4;
+    c->h_stage_bytes = 256 + sizeof(Result) + (size_t)c->d.max_path * 4;
     if (cudaHostAlloc((void**)&c->h_stage, c->h_stage_bytes, cudaHostAllocDefault) != cudaSuccess) {
         bibfs_ctx_destroy(c);
         return fail("pinned staging allocation failed");
@@ -203,8 +203,14 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     DeviceGuard g(c->device);
     cudaStream_t st = (cudaStream_t)stream;
     Result* hr = reinterpret_cast<Result*>(c->h_stage);
-    u32* hp = reinterpret_cast<u32*>(c->h_stage + 256);
-    BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, st));
+    u32* hp = reinterpret_cast<u32*>(c->h_stage + sizeof(Result));
+    const bool has_path = !(c->last_flags & BIBFS_F_NO_PATH);
+    // the path kernel leaves [Result | path] contiguous: one copy brings the result and the first entries
+    const u32 first = path && has_path ? (c->d.max_path < 240u ? c->d.max_path : 240u) : 0u;
+    if (has_path)
+        BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + c->L.off_path, sizeof(Result) + (size_t)first * 4, cudaMemcpyDeviceToHost, st));
+    else
+        BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, st));
     BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
     *res = bibfs_result();
     res->length = hr->length;
@@ -223,9 +229,12 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     cudaGetLastError();
     if (hr->status == 1) return fail("search aborted by the device watchdog (a rank did not arrive); reset the context");
     if (hr->status == 2) return fail("src/dst out of range (n=%u)", c->d.n);
-    if (path && hr->path_len && hr->path_len <= path_cap) {
-        BIBFS_CUDA_TRY(cudaMemcpyAsync(hp, c->arena_local[0] + c->L.off_path, (size_t)hr->path_len * 4, cudaMemcpyDeviceToHost, st));
-        BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
+    if (path && has_path && hr->path_len && hr->path_len <= path_cap) {
+        if (hr->path_len > first) {
+            BIBFS_CUDA_TRY(cudaMemcpyAsync(hp + first, c->arena_local[0] + c->L.off_path + sizeof(Result) + (size_t)first * 4,
+                                           (size_t)(hr->path_len - first) * 4, cudaMemcpyDeviceToHost, st));
+            BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
+        }
         memcpy(path, hp, (size_t)hr->path_len * 4);
         res->path_len = hr->path_len;
     }
