@@ -177,11 +177,12 @@ def run_ours(args):
 
     # ---- end to end through the public API -----------------------------------------------
     pinned = torch.empty(2, dtype=torch.int32).pin_memory()
+    pinned_np = pinned.numpy()            # same memory; numpy item stores cost ~0.1 us, torch ones ~10 us
     barrier()
     e0 = time.perf_counter()
     d2h = 0
     for i, (s, t, length) in enumerate(queries[W:W + K]):
-        pinned[0], pinned[1] = s, t
+        pinned_np[0], pinned_np[1] = s, t
         r = solver.query(-1 & 0x7FFFFFFF, -1 & 0x7FFFFFFF, want_path=True, pinned_query=pinned)
         assert r.length == length
         d2h += 64 + 4 * (length + 1)

@@ -110,6 +110,7 @@ def _declare(lib):
         "bibfs_ctx_reset": (C.c_int, [vp, vp]),
         "bibfs_ctx_query": (C.c_int, [vp, u32, u32, vp, u32, vp]),
         "bibfs_ctx_result": (C.c_int, [vp, P(Result), vp, u32, vp]),
+        "bibfs_ctx_query_result": (C.c_int, [vp, u32, u32, vp, u32, P(Result), vp, u32, vp]),
         "bibfs_ctx_timing": (C.c_int, [vp, P(C.c_float), P(C.c_float)]),
         "bibfs_ctx_trace": (C.c_int, [vp, u32, P(LevelTrace), u32, P(u32)]),
         "bibfs_batch_workspace_bytes": (C.c_size_t, [u32]),

@@ -104,8 +104,12 @@ class SearchContext:
         return result_from_c(src, dst, r, self._path, variant)
 
     def query(self, src, dst, flags=0, want_path=True, pinned_query=None, variant="gpu") -> PathResult:
-        self.launch(src, dst, flags, pinned_query)
-        return self.fetch(src, dst, want_path, variant)
+        r = Result()
+        q = pinned_query.data_ptr() if pinned_query is not None else None
+        check(lib().bibfs_ctx_query_result(self._h, int(src), int(dst), q, flags, C.byref(r),
+                                           self._path.ctypes.data if want_path else None, self.max_path if want_path else 0,
+                                           self._stream()))
+        return result_from_c(src, dst, r, self._path, variant)
 
     def timing(self) -> tuple[float, float]:
         a, b = C.c_float(0), C.c_float(0)

@@ -66,8 +66,7 @@ class DistributedSolver:
     def query(self, src, dst, want_path=True, flags=0, pinned_query=None) -> PathResult:
         if not want_path:
             flags |= F_NO_PATH
-        self.ctx.launch(src, dst, flags, pinned_query)
-        return self.ctx.fetch(src, dst, want_path, self.variant)
+        return self.ctx.query(src, dst, flags, want_path, pinned_query, self.variant)
 
     def close(self):
         torch.cuda.synchronize(self.graph.device)

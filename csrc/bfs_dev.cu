@@ -435,7 +435,10 @@ template <bool MULTI>
 __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelState& G, Acc& A, u64 deadline) {
     Ctrl* C = E.C;
     const u32 lane = threadIdx.x & 31;
-    const u32 src = K.query_in_ctrl ? C->q_src : K.src, dst = K.query_in_ctrl ? C->q_dst : K.dst;
+    // the query: by value, or straight from the caller's pinned host memory (one PCIe read, no copy engine involved)
+    u32 src = K.src, dst = K.dst;
+    if (K.h_query) { src = *reinterpret_cast<const volatile u32*>(K.h_query); dst = *reinterpret_cast<const volatile u32*>(K.h_query + 1); }
+    if (lane == 0) { C->q_src = src; C->q_dst = dst; }
     if (lane == 0) {
         for (u32 w = 0; w < BAR_WAYS; ++w) C->bar_way[w].count = 0;
         A.q_tail[0] = 0; A.q_tail[1] = 0;
@@ -1429,7 +1432,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
             const bool ok = leader_init<MULTI>(K, E, st, s_acc, deadline);
             if (!ok && lane == 0) s_fail = 1;
             if (lane == 0) {   // the seeds are the first mirrored entries
-                const u32 src = K.query_in_ctrl ? C->q_src : K.src, dst = K.query_in_ctrl ? C->q_dst : K.dst;
+                const u32 src = C->q_src, dst = C->q_dst;     // as resolved by leader_init
                 if (s_acc.q_tail[0] == 1) { s_q[0][0][0] = src; s_qvalid[0] = 1; }
                 if (s_acc.q_tail[1] == 1) { s_q[1][0][0] = dst; s_qvalid[1] = 1; }
             }
@@ -1643,17 +1646,22 @@ __global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) 
     __syncthreads();
     static_assert(sizeof(Result) == PATH_HDR_WORDS * 4, "result header size");
     if (threadIdx.x < PATH_HDR_WORDS) hdr[threadIdx.x] = reinterpret_cast<const u32*>(&R)[threadIdx.x];
+    // short answers go straight to the caller's pinned buffer (posted PCIe writes): the host only waits for the stream
+    if (K.h_out) {
+        const u32 plen = ok ? L + 1u : 0u;
+        const u32 words = PATH_HDR_WORDS + (plen <= K.h_out_words ? plen : 0u);
+        for (u32 i = threadIdx.x; i < words; i += blockDim.x) K.h_out[i] = hdr[i];
+        __threadfence_system();
+    }
 }
 
 // ------------------------------------------------------------------------------------------
 // launch helpers used by ctx.cu
 // ------------------------------------------------------------------------------------------
+// opt in to the kernel's dynamic shared memory; the attribute is per device, so contexts call this at creation
 static int bfs_prepare(bool multi) {
-    static bool done[2] = {false, false};
-    if (done[multi]) return 0;
     if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
     else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-    done[multi] = true;      // (per process; every device of the process gets the attribute on first use below)
     return 0;
 }
 
@@ -1672,8 +1680,6 @@ int bfs_max_ctas_per_device(bool multi, int* out) {
 int bfs_launch(const KParams& K, bool multi, cudaStream_t st) {
     void* args[] = {(void*)&K};
     dim3 grid(K.cpr * K.vranks), block(BFS_THREADS);
-    if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-    else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
     if (multi) BIBFS_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_bibfs<true>, grid, block, args, sizeof(Smem), st));
     else BIBFS_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_bibfs<false>, grid, block, args, sizeof(Smem), st));
     count_launch();

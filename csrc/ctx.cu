@@ -31,6 +31,7 @@ struct bibfs_ctx {
 };
 
 namespace {
+constexpr u32 HOST_PATH_WORDS = 240;   // path entries the path kernel writes straight into the pinned result buffer
 struct DeviceGuard {
     int prev = -1;
     bool active = false;
@@ -167,7 +168,8 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     K.max_path = c->d.max_path;
     K.seq = ++c->seq;
     K.watchdog_ms = c->d.watchdog_ms;
-    K.src = src; K.dst = dst; K.query_in_ctrl = in_ctrl ? 1u : 0u;
+    K.src = src; K.dst = dst; K.query_in_ctrl = 0u;
+    K.h_query = nullptr; K.h_out = nullptr; K.h_out_words = 0;
     K.L = c->L;
     for (u32 r = 0; r < MAXR; ++r) K.arena[r] = c->arena_all[r];
     for (u32 i = 0; i < c->d.vranks; ++i) {
@@ -183,11 +185,10 @@ extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const u
         if (!c->arena_all[r]) return fail("rank %u is not attached", r);
     DeviceGuard g(c->device);
     cudaStream_t st = (cudaStream_t)stream;
-    if (h_query_pinned)
-        for (u32 i = 0; i < c->d.vranks; ++i)
-            BIBFS_CUDA_TRY(cudaMemcpyAsync(c->arena_local[i] + offsetof(Ctrl, q_src), h_query_pinned, 8, cudaMemcpyHostToDevice, st));
     KParams K;
-    fill_params(c, K, src, dst, h_query_pinned != nullptr, flags);
+    fill_params(c, K, src, dst, false, flags);
+    K.h_query = h_query_pinned;          // read by the kernel itself: pinned memory is device-visible under UVA
+    if (!(flags & BIBFS_F_NO_PATH)) { K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = HOST_PATH_WORDS; }
     c->last_flags = flags;
     BIBFS_CUDA_TRY(cudaEventRecord(c->ev[0], st));
     if (bfs_launch(K, c->multi, st)) return 1;
@@ -205,11 +206,9 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     Result* hr = reinterpret_cast<Result*>(c->h_stage);
     u32* hp = reinterpret_cast<u32*>(c->h_stage + sizeof(Result));
     const bool has_path = !(c->last_flags & BIBFS_F_NO_PATH);
-    // the path kernel leaves [Result | path] contiguous: one copy brings the result and the first entries
-    const u32 first = path && has_path ? (c->d.max_path < 240u ? c->d.max_path : 240u) : 0u;
-    if (has_path)
-        BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + c->L.off_path, sizeof(Result) + (size_t)first * 4, cudaMemcpyDeviceToHost, st));
-    else
+    // with a path kernel the answer ([Result | first path entries]) was written into h_stage by the device itself
+    const u32 first = has_path ? HOST_PATH_WORDS : 0u;
+    if (!has_path)
         BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, st));
     BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
     *res = bibfs_result();
@@ -230,15 +229,22 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     if (hr->status == 1) return fail("search aborted by the device watchdog (a rank did not arrive); reset the context");
     if (hr->status == 2) return fail("src/dst out of range (n=%u)", c->d.n);
     if (path && has_path && hr->path_len && hr->path_len <= path_cap) {
-        if (hr->path_len > first) {
-            BIBFS_CUDA_TRY(cudaMemcpyAsync(hp + first, c->arena_local[0] + c->L.off_path + sizeof(Result) + (size_t)first * 4,
-                                           (size_t)(hr->path_len - first) * 4, cudaMemcpyDeviceToHost, st));
+        if (hr->path_len > first) {      // long path: fetch all of it from the device buffer
+            BIBFS_CUDA_TRY(cudaMemcpyAsync(hp, c->arena_local[0] + c->L.off_path + sizeof(Result), (size_t)hr->path_len * 4,
+                                           cudaMemcpyDeviceToHost, st));
             BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
         }
         memcpy(path, hp, (size_t)hr->path_len * 4);
         res->path_len = hr->path_len;
     }
     return 0;
+}
+
+// query + result in one call (one FFI crossing per query for interpreted callers)
+extern "C" int bibfs_ctx_query_result(bibfs_ctx* c, uint32_t src, uint32_t dst, const uint32_t* h_query_pinned, uint32_t flags,
+                                      bibfs_result* res, uint32_t* path, uint32_t path_cap, void* stream) {
+    if (bibfs_ctx_query(c, src, dst, h_query_pinned, flags, stream)) return 1;
+    return bibfs_ctx_result(c, res, path, path_cap, stream);
 }
 
 extern "C" int bibfs_ctx_timing(bibfs_ctx* c, float* search_ms, float* path_ms) {

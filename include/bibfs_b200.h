@@ -214,6 +214,9 @@ int bibfs_ctx_query(bibfs_ctx* ctx, uint32_t src, uint32_t dst, const uint32_t* 
  * (>= 64 + 4*path_cap bytes of pinned memory) the D2H copies land there. */
 int bibfs_ctx_result(bibfs_ctx* ctx, bibfs_result* res, uint32_t* path, uint32_t path_cap,
                      void* stream);
+/* bibfs_ctx_query + bibfs_ctx_result in one call. */
+int bibfs_ctx_query_result(bibfs_ctx* ctx, uint32_t src, uint32_t dst, const uint32_t* h_query_pinned, uint32_t flags,
+                           bibfs_result* res, uint32_t* path, uint32_t path_cap, void* stream);
 /* device timing of the last query as measured by cudaEvents around each kernel */
 int bibfs_ctx_timing(bibfs_ctx* ctx, float* search_ms, float* path_ms);
 
