@@ -153,6 +153,7 @@ inline Layout make_layout(u32 B, u32 P, u32 max_path) {
 struct KParams {
     u32 n, B, P;
     u32 rank_lo, vranks, cpr;      // ranks hosted by this launch, CTAs per rank
+    u32 cluster;                   // thread-block cluster size of the launch (single rank; 1 = no clusters)
     u32 solo_threshold, bu_div, flags, max_path;
     u32 seq;                       // launch sequence number (local barrier generation prefix)
     u32 watchdog_ms;
@@ -168,6 +169,7 @@ struct KParams {
 
 // implemented in bfs_dev.cu
 int bfs_max_ctas_per_device(bool multi, int* out);
+int bfs_max_ctas_clustered(u32 cluster, int* out);
 #if defined(__CUDACC__) || defined(BIBFS_WITH_CUDA_RUNTIME)
 int bfs_launch(const KParams& K, bool multi, cudaStream_t st);
 int path_launch(const KParams& K, cudaStream_t st);

@@ -992,6 +992,20 @@ __device__ __noinline__ void push_fbm_slice(const KParams& K, const Env& E, u32 
 // ------------------------------------------------------------------------------------------
 // shared memory of the search kernel
 // ------------------------------------------------------------------------------------------
+struct SoloLevel {          // written by thread 0 at the end of a level, read by everybody
+    u32 side_flags;         // bit 0 side, bit 1 frontier is in the shared mirror, bit 2 which mirror buffer, bit 3 stop
+    u32 total;              // frontier vertices of this rank (local window + windows of the sender segments)
+    u32 q_lo;               // local window start in the global queue (used when not mirrored)
+    u32 base_tail;          // local queue cursor at the start of the level (== local window end)
+    u32 nq;                 // size of the local window
+    u32 tag;                // epoch tag for entries sent to other ranks in this level
+    u32 rq_tag;             // tag carried by the entries of the sender-segment windows
+    u32 pad;
+};
+static_assert(sizeof(SoloLevel) == 32, "two LDS.128");
+
+enum : u32 { CL_HELP = 1, CL_EXIT = 2 };   // commands of the leader CTA to the other CTAs of its cluster
+
 struct Smem {
     LevelState st;
     Acc acc;
@@ -1000,6 +1014,8 @@ struct Smem {
     unsigned long long pend_edges, pend_visited;   // solo levels: totals not yet added to Ctrl
     u64 hub_bar[WPC][2];                           // hub phase: one mbarrier per warp and buffer
     u32 stage_cnt, stage_base, cta_new, pad0;      // grid mode: per-CTA staging of discoveries / counters
+    alignas(16) SoloLevel lv;                      // solo mode: descriptor of the current level (read over DSMEM by cluster helpers)
+    u32 cl_seq, cl_cmd;                            // cluster tier: sequence number / command for the helper CTAs
     unsigned long long cta_edges;
     u32 stage[STAGE_CAP];
     alignas(128) u32 q[2][2][SOLO_CAP];            // solo: frontier mirrors; hub phase: per-warp TMA staging (WPC x 2 KB)
@@ -1035,28 +1051,16 @@ __device__ __noinline__ void solo_push_hub(const KParams& K, const Env& E, Smem&
 //   -> one shared-memory cursor atomic per discovering lane -> stores.
 // The level bookkeeping runs in registers of thread 0; the other threads only ever read the
 // 16-byte descriptor.  Nothing is published to the grid until it is needed.
-struct SoloLevel {          // written by thread 0 at the end of a level, read by everybody
-    u32 side_flags;         // bit 0 side, bit 1 frontier is in the shared mirror, bit 2 which mirror buffer, bit 3 stop
-    u32 total;              // frontier vertices of this rank (local window + windows of the sender segments)
-    u32 q_lo;               // local window start in the global queue (used when not mirrored)
-    u32 base_tail;          // local queue cursor at the start of the level (== local window end)
-    u32 nq;                 // size of the local window
-    u32 tag;                // epoch tag for entries sent to other ranks in this level
-    u32 rq_tag;             // tag carried by the entries of the sender-segment windows
-    u32 pad;
-};
-static_assert(sizeof(SoloLevel) == 32, "two LDS.128");
-
 constexpr int SW = 8;       // adjacency entries per lane per round
 constexpr u32 SOLO_HUB_ROW = 128;   // solo mode packs the frontier into few warps: longer rows are shared by the CTA or the grid
 constexpr u32 CL_CAP = 64;          // rows the CTA keeps for itself per level ...
 constexpr u32 CL_MAX_EDGES = 16384; // ... as long as they add up to no more than this many entries
 
 template <bool MULTI>
-__device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 deadline) {
+__device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 deadline, u32 cl_n) {
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     LevelState& st = sm.st;
-    __shared__ __align__(16) SoloLevel s_lv;
+    SoloLevel& s_lv = sm.lv;
     __shared__ u32 s_sent[2][MAXR];      // MULTI: entries appended to each peer's segment (cumulative, per side)
     __shared__ u32 s_rnew;               // MULTI: vertices discovered at other ranks in this level
     __shared__ u64 s_mail[2];
@@ -1081,6 +1085,11 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         lv.rq_tag = st.rq_tag[sd];
         lv.pad = 0;
         s_lv = lv;
+        // a frontier larger than this CTA: the other CTAs of the cluster take the slices beyond the first
+        if (!MULTI && cl_n > 1 && lv.total > (u32)BFS_THREADS) {
+            sm.cl_cmd = CL_HELP;
+            ptx::dsmem_st_release(ptx::smem_addr(&sm.cl_seq), sm.cl_seq + 1u);
+        }
     };
     if (MULTI && tid < 2 * MAXR) s_sent[tid / MAXR][tid % MAXR] = ptx::ld_relaxed_gpu(&E.C->sent[tid / MAXR][tid % MAXR]);
     if (tid == 0) { make_level(st.side); s_rnew = 0; s_cl_n = 0; s_cl_edges = 0; }
@@ -1090,6 +1099,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         const uint4 raw = *reinterpret_cast<const uint4*>(&s_lv);
         const u32 side = raw.x & 1u, total = raw.y, base_tail = raw.w;
         if (raw.x & 8u) break;
+        const bool cluster_level = !MULTI && cl_n > 1 && total > (u32)BFS_THREADS;
         const u32 cur = (raw.x >> 2) & 1u;
         u32* const out = sm.q[side][cur ^ 1u];
         const u32 sh = 32u * side, osh = 32u - sh;
@@ -1218,7 +1228,8 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             const u32 wsum = __reduce_add_sync(FULL, nedges);
             if (lane == 0 && wsum) ptx::reds_add64(&sm.acc.edges, wsum);
         }
-        __syncthreads();
+        if (cluster_level) ptx::cluster_sync_all();      // the helpers' slices are done, their DSMEM updates visible
+        else __syncthreads();
         if (s_cl_n) {
             // long rows collected by this level: shared by all warps of the CTA in 128-entry pieces, unless there
             // is so much of it that the grid should take over (hub phase)
@@ -1359,6 +1370,116 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
     __syncthreads();
 }
 
+// ------------------------------------------------------------------------------------------
+// cluster tier: the CTAs that share a thread-block cluster with the leader CTA help it with
+// frontiers of 513..cl_n*512 vertices.  They find the level descriptor, the frontier mirror and
+// the accumulators in the LEADER's shared memory through DSMEM (mapa + ld/st/atom.shared::cluster)
+// and meet the leader at a hardware cluster barrier, which costs ~0.2 us where waking the whole
+// grid through global memory costs ~7 us per level.  Single rank only.
+// ------------------------------------------------------------------------------------------
+__device__ __noinline__ void cluster_helper(const KParams& K, const Env& E, Smem& sm, u32 cl_rank, u32& seen_seq, u64 deadline) {
+    const u32 tid = threadIdx.x, lane = tid & 31;
+    __shared__ u32 s_cmd, s_seq;
+    __shared__ __align__(16) SoloLevel s_lvc;
+    // leader-side addresses (same layout in every CTA of the kernel)
+    const u32 a_seq = ptx::dsmem_map(ptx::smem_addr(&sm.cl_seq), 0), a_cmd = ptx::dsmem_map(ptx::smem_addr(&sm.cl_cmd), 0);
+    const u32 a_lv = ptx::dsmem_map(ptx::smem_addr(&sm.lv), 0);
+    const u32 a_hub = ptx::dsmem_map(ptx::smem_addr(&sm.hub), 0);
+    const u32 a_meet = ptx::dsmem_map(ptx::smem_addr(&sm.acc.meet_local), 0);
+    const u32 a_edges = ptx::dsmem_map(ptx::smem_addr(&sm.acc.edges), 0);
+    while (true) {
+        if (tid == 0) {
+            u32 v, spins = 0;
+            bool dead = false;
+            while ((v = ptx::dsmem_ld(a_seq)) == seen_seq) {
+                // back off: every poll is a request to the LEADER's shared-memory port, which it needs itself
+                ptx::nanosleep(96);
+                if (++spins > 4096u && (spins & 1023u) == 0 && expired(E.C, deadline)) { dead = true; break; }
+            }
+            v = ptx::dsmem_ld_acquire(a_seq);
+            s_seq = v;
+            s_cmd = dead ? (u32)CL_EXIT : ptx::dsmem_ld(a_cmd);
+            if (!dead && s_cmd == CL_HELP) {
+                u32* d = reinterpret_cast<u32*>(&s_lvc);
+                for (u32 i = 0; i < sizeof(SoloLevel) / 4; ++i) d[i] = ptx::dsmem_ld(a_lv + 4 * i);
+            }
+        }
+        __syncthreads();
+        seen_seq = s_seq;
+        if (s_cmd != CL_HELP) return;
+        const u32 side = s_lvc.side_flags & 1u, cur = (s_lvc.side_flags >> 2) & 1u;
+        const u32 total = s_lvc.total, base_tail = s_lvc.base_tail;
+        const u32 sh = 32u * side, osh = 32u - sh;
+        const u32 i = cl_rank * (u32)BFS_THREADS + tid;
+        const u32 a_tail = ptx::dsmem_map(ptx::smem_addr(&sm.acc.q_tail[side]), 0);
+        const u32 a_out = ptx::dsmem_map(ptx::smem_addr(&sm.q[side][cur ^ 1u][0]), 0);
+        u32 u = 0;
+        u64 r0 = 0, r1 = 0;
+        if (i < total) {
+            u = (s_lvc.side_flags & 2u) ? ptx::dsmem_ld(ptx::dsmem_map(ptx::smem_addr(&sm.q[side][cur][i]), 0))
+                                        : __ldcg(E.q[side] + s_lvc.q_lo + i);
+            r0 = __ldg(E.row_ptr + (u - E.lo));
+            r1 = __ldg(E.row_ptr + (u - E.lo) + 1);
+        }
+        u32 deg = (u32)min(r1 - r0, (u64)0xFFFFFFFFu);
+        const u32 nedges = deg;
+        if (deg >= 32u) {
+            // long rows go to the grid-wide hub phase (the leader sees the flag after the cluster barrier)
+            const u32 nch = hub_nchunks(r0, r1);
+            const unsigned long long inc = (1ull << 40) | (unsigned long long)nch;
+            const unsigned long long old = atomicAdd(&E.C->hub_packed, inc);
+            const u32 slot = (u32)(old >> 40);
+            HubEntry h;
+            h.u = u; h.nchunks = nch; h.r0 = r0; h.r1 = r1; h.chunk_base = old & 0xFFFFFFFFFFull;
+            if (slot < HUB_CAP) hub_of(K, E.me)[slot] = h;
+            ptx::dsmem_st(a_hub, 1u);
+            deg = 0;
+        }
+        u64* const dummy = dummy_of(K, E.me);
+        for (u32 e0 = 0; __any_sync(FULL, e0 < deg); e0 += SW) {
+            u32 v[SW];
+            u64 old[SW];
+#pragma unroll
+            for (int k = 0; k < SW; ++k) v[k] = __ldg(E.col + r0 + ((e0 + k < deg) ? e0 + k : 0u));
+#pragma unroll
+            for (int k = 0; k < SW; ++k) {
+                const bool act = e0 + k < deg;
+                old[k] = ptx::atom_or_gpu(act ? &E.vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
+            }
+            u32 newmask = 0, meetmask = 0;
+#pragma unroll
+            for (int k = 0; k < SW; ++k) {
+                const u32 isnew = (e0 + k < deg) ? (((u32)(old[k] >> ((v[k] & 31u) + sh)) & 1u) ^ 1u) : 0u;
+                newmask |= isnew << k;
+                meetmask |= (isnew & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
+            }
+            if (newmask) {
+                u32 slot = ptx::dsmem_atom_add(a_tail, (u32)__popc(newmask));     // the leader's queue cursor
+#pragma unroll
+                for (int k = 0; k < SW; ++k) {
+                    if ((newmask >> k) & 1u) {
+                        E.q[side][slot] = v[k];
+                        E.parent[side][v[k] - E.lo] = u;
+                        if (slot - base_tail < SOLO_CAP) ptx::dsmem_st(a_out + 4u * (slot - base_tail), v[k]);
+                        ptx::prefetch_l2(E.row_ptr + (v[k] - E.lo));
+                        ++slot;
+                    }
+                }
+                if (meetmask) {
+#pragma unroll
+                    for (int k = 0; k < SW; ++k)
+                        if ((meetmask >> k) & 1u) ptx::dsmem_red_min(a_meet, v[k]);
+                }
+            }
+        }
+        {
+            const u32 wsum = __reduce_add_sync(FULL, nedges);
+            if (lane == 0 && wsum) ptx::dsmem_red_add64(a_edges, wsum);
+        }
+        ptx::cluster_sync_all();
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------
@@ -1397,10 +1518,15 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     const u64 deadline = ptx::globaltimer_ns() + (u64)K.watchdog_ms * 1000000ull;
     const u64 genbase = (u64)K.seq << 32;
     const bool is_leader_cta = (E.cta == 0);
+    const u32 cl_n = MULTI ? 1u : ptx::cluster_nctarank(), cl_rank = ptx::cluster_ctarank();
+    const bool in_leader_cluster = cl_n > 1 && blockIdx.x < cl_n;       // shares a cluster (and DSMEM) with the leader CTA
+    u32 cl_seen = 0;
     if (tid == 0) { s_fail = 0; s_hub = 0; s_qvalid[0] = 0; s_qvalid[1] = 0; s_qcur[0] = 0; s_qcur[1] = 0; sm.pend_edges = 0; sm.pend_visited = 0; sm.stage_cnt = 0; sm.cta_new = 0; sm.cta_edges = 0; }
     if (lane == 0) { ptx::mbar_init(&sm.hub_bar[warp][0], 1); ptx::mbar_init(&sm.hub_bar[warp][1], 1); ptx::mbar_fence_init(); }
     u32 hub_parity = 0;            // phase bits of this warp's two hub barriers
+    if (tid == 0) { sm.cl_seq = 0; sm.cl_cmd = 0; }
     __syncthreads();
+    if (cl_n > 1) ptx::cluster_sync_all();     // the helpers may now poll the leader's command word
 
     // non-leader CTAs: copy the published level state global -> shared after a wake-up
     auto load_state = [&]() {
@@ -1410,7 +1536,14 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         __syncthreads();
     };
     // leader warp: publish the shared state + accumulators and wake the other CTAs
+    bool helpers_listening = cl_n > 1;      // leader CTA: the cluster helpers are waiting for commands (initially, and during solo phases)
     auto publish_and_wake = [&]() {
+        if (helpers_listening) {
+            // the helpers of this cluster leave their command loop before the grid-wide release goes out
+            if (lane == 0) { sm.cl_cmd = CL_EXIT; ptx::dsmem_st_release(ptx::smem_addr(&sm.cl_seq), sm.cl_seq + 1u); }
+            __syncwarp();
+        }
+        helpers_listening = cl_n > 1 && st.phase == PH_TD_SOLO;
         if (lane == 0) st.wake += 1;
         __syncwarp();
         u32* g = reinterpret_cast<u32*>(&C->st);
@@ -1441,6 +1574,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         }
         __syncthreads();
     } else {
+        if (in_leader_cluster) cluster_helper(K, E, sm, cl_rank, cl_seen, deadline);   // may be needed before the first release
         if (tid == 0 && !wait_gen(C, genbase | 1u, deadline)) s_fail = 1;
         __syncthreads();
         if (!s_fail) load_state();
@@ -1501,6 +1635,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         if (phase == PH_DONE) break;
         if (phase == PH_TD_SOLO) {
             if (!is_leader_cta) {   // parked until the leader wakes the grid
+                if (in_leader_cluster) cluster_helper(K, E, sm, cl_rank, cl_seen, deadline);   // ... helping it meanwhile
                 if (tid == 0 && !wait_gen(C, genbase | (u64)(st.wake + 1u), deadline)) s_fail = 1;
                 __syncthreads();
                 if (s_fail) { alive = false; break; }
@@ -1508,7 +1643,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 continue;
             }
             {
-                solo_run<MULTI>(K, E, sm, deadline);
+                solo_run<MULTI>(K, E, sm, deadline, cl_n);
                 if (s_fail) { if (warp == 0) publish_and_wake(); __syncthreads(); alive = false; break; }
                 if (warp == 0) publish_and_wake();      // left solo mode: the grid is needed (or the query is done)
                 __syncthreads();
@@ -1678,24 +1813,43 @@ int bfs_max_ctas_per_device(bool multi, int* out) {
 }
 
 int bfs_launch(const KParams& K, bool multi, cudaStream_t st) {
-    void* args[] = {(void*)&K};
-    dim3 grid(K.cpr * K.vranks), block(BFS_THREADS);
-    if (multi) BIBFS_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_bibfs<true>, grid, block, args, sizeof(Smem), st));
-    else BIBFS_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_bibfs<false>, grid, block, args, sizeof(Smem), st));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(K.cpr * K.vranks);
+    cfg.blockDim = dim3(BFS_THREADS);
+    cfg.dynamicSmemBytes = sizeof(Smem);
+    cfg.stream = st;
+    cudaLaunchAttribute attrs[2];
+    attrs[0].id = cudaLaunchAttributeCooperative;
+    attrs[0].val.cooperative = 1;
+    cfg.numAttrs = 1;
+    if (!multi && K.cluster > 1) {
+        attrs[1].id = cudaLaunchAttributeClusterDimension;
+        attrs[1].val.clusterDim.x = K.cluster; attrs[1].val.clusterDim.y = 1; attrs[1].val.clusterDim.z = 1;
+        cfg.numAttrs = 2;
+    }
+    cfg.attrs = attrs;
+    if (multi) BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_bibfs<true>, K));
+    else BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_bibfs<false>, K));
     count_launch();
     return 0;
 }
 
-#ifdef BIBFS_FINE_TRACE
-extern "C" int bibfs_debug_read(uint64_t* out, uint32_t* levels) {
-    cudaMemcpyFromSymbol(out, g_dbg, sizeof(u64) * 256 * 8);
-    cudaMemcpyFromSymbol(out + 256 * 8, g_dbg2, sizeof(u64) * 256 * 8);
-    cudaMemcpyFromSymbol(levels, g_dbg_level, 4);
-    u32 z = 0;
-    cudaMemcpyToSymbol(g_dbg_level, &z, 4);
+// how many CTAs can be co-resident when the single-rank kernel is launched in clusters of `cluster`
+int bfs_max_ctas_clustered(u32 cluster, int* out) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cluster * 64);
+    cfg.blockDim = dim3(BFS_THREADS);
+    cfg.dynamicSmemBytes = sizeof(Smem);
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    BIBFS_CUDA_TRY(cudaOccupancyMaxActiveClusters(&n, k_bibfs<false>, &cfg));
+    *out = n * (int)cluster;
     return 0;
 }
-#endif
 
 int path_launch(const KParams& K, cudaStream_t st) {
     k_path<<<1, 64, 0, st>>>(K);

@@ -23,6 +23,7 @@ struct bibfs_ctx {
     bool ipc_opened[MAXR] = {};
     u32 seq = 0;
     u32 cpr = 0;
+    u32 cluster = 1;
     bool multi = false;
     cudaEvent_t ev[3] = {};
     char* h_stage = nullptr;        // pinned: Result + path
@@ -75,6 +76,17 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     if (desc->max_ctas && desc->max_ctas < per_rank) per_rank = desc->max_ctas;
     if (per_rank < 1) { delete c; return fail("not enough SMs for %u hosted ranks", desc->vranks); }
     c->cpr = per_rank;
+    // single rank: launch in clusters of 4 so that the leader CTA can enlist three neighbours over DSMEM
+    // (frontiers up to 2048 vertices stay off the grid-wide barrier)
+    if (!c->multi && desc->vranks == 1 && per_rank >= 8) {
+        int fit = 0;
+        if (bfs_max_ctas_clustered(4, &fit) == 0 && fit >= 8) {
+            c->cluster = 4;
+            c->cpr = (per_rank < (u32)fit ? per_rank : (u32)fit) / 4 * 4;
+            if (c->d.solo_threshold == (u32)BFS_THREADS) c->d.solo_threshold = 4 * BFS_THREADS;
+        }
+        cudaGetLastError();
+    }
 
     for (u32 i = 0; i < desc->vranks; ++i) {
         cudaError_t e = cudaMalloc((void**)&c->arena_local[i], c->L.total);
@@ -162,6 +174,7 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     memset(&K, 0, sizeof(K));
     K.n = c->d.n; K.B = c->B; K.P = c->d.nranks;
     K.rank_lo = c->d.rank_lo; K.vranks = c->d.vranks; K.cpr = c->cpr;
+    K.cluster = c->cluster;
     K.solo_threshold = c->d.solo_threshold;
     K.bu_div = c->d.bottom_up_div;
     K.flags = flags;

@@ -172,6 +172,26 @@ __device__ __forceinline__ u32 dsmem_ld(u32 a) {
     asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
     return v;
 }
+// remote shared memory of another CTA of the cluster (addresses from dsmem_map)
+__device__ __forceinline__ u32 dsmem_atom_add(u32 a, u32 v) {
+    u32 old;
+    asm volatile("atom.relaxed.cluster.shared::cluster.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(a), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void dsmem_red_min(u32 a, u32 v) {
+    asm volatile("red.relaxed.cluster.shared::cluster.min.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void dsmem_red_add64(u32 a, u64 v) {
+    asm volatile("red.relaxed.cluster.shared::cluster.add.u64 [%0], %1;" ::"r"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ u32 dsmem_ld_acquire(u32 a) {
+    u32 v;
+    asm volatile("ld.acquire.cluster.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void dsmem_st_release(u32 a, u32 v) {
+    asm volatile("st.release.cluster.shared::cluster.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
 __device__ __forceinline__ void dsmem_st(u32 a, u32 v) { asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 
 }  // namespace ptx
