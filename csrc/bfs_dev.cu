@@ -651,10 +651,11 @@ __device__ __noinline__ u32 visit_batch(const KParams& K, const Env& E, u32 side
             act[k] = ok[k] && !((seen[k] >> ((v[k] & 31u) + sh)) & 1ull);
             old[k] = ptx::atom_or_gpu(act[k] ? &E.vis[v[k] >> 5] : dummy, act[k] ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
         }
+        const u32 shz = sh + ptx::zero_after(old[UNR - 1]);     // == sh; keeps the tests below behind the last atomic
 #pragma unroll
         for (int k = 0; k < UNR; ++k) {
             c[k].dest = E.me;
-            c[k].isnew = act[k] && !((old[k] >> ((v[k] & 31u) + sh)) & 1ull);
+            c[k].isnew = act[k] && !((old[k] >> ((v[k] & 31u) + shz)) & 1ull);
         }
         if (MULTI) {
             bool rem[UNR];
@@ -666,9 +667,10 @@ __device__ __noinline__ u32 visit_batch(const KParams& K, const Env& E, u32 side
                 c[k].dest = dest;
                 rold[k] = ptx::atom_or_sys(rem[k] ? (vis_of(K, dest) + (v[k] >> 5)) : dummy, rem[k] ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
             }
+            const u32 shr = sh + ptx::zero_after(rold[UNR - 1]);
 #pragma unroll
             for (int k = 0; k < UNR; ++k)
-                if (rem[k]) { old[k] = rold[k]; c[k].isnew = !((rold[k] >> ((v[k] & 31u) + sh)) & 1ull); }
+                if (rem[k]) { old[k] = rold[k]; c[k].isnew = !((rold[k] >> ((v[k] & 31u) + shr)) & 1ull); }
         }
 #pragma unroll
         for (int k = 0; k < UNR; ++k) c[k].meet = c[k].isnew && ((old[k] >> ((v[k] & 31u) + osh)) & 1ull);
@@ -1015,7 +1017,7 @@ struct Smem {
     u64 hub_bar[WPC][2];                           // hub phase: one mbarrier per warp and buffer
     u32 stage_cnt, stage_base, cta_new, pad0;      // grid mode: per-CTA staging of discoveries / counters
     alignas(16) SoloLevel lv;                      // solo mode: descriptor of the current level (read over DSMEM by cluster helpers)
-    u32 cl_seq, cl_cmd;                            // cluster tier: sequence number / command for the helper CTAs
+    u32 cl_seq, cl_cmd, cl_n, pad1;                // cluster tier: sequence number / command for the helper CTAs, cluster size
     unsigned long long cta_edges;
     u32 stage[STAGE_CAP];
     alignas(128) u32 q[2][2][SOLO_CAP];            // solo: frontier mirrors; hub phase: per-warp TMA staging (WPC x 2 KB)
@@ -1057,7 +1059,7 @@ constexpr u32 CL_CAP = 64;          // rows the CTA keeps for itself per level .
 constexpr u32 CL_MAX_EDGES = 16384; // ... as long as they add up to no more than this many entries
 
 template <bool MULTI>
-__device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 deadline, u32 cl_n) {
+__device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 deadline) {
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     LevelState& st = sm.st;
     SoloLevel& s_lv = sm.lv;
@@ -1069,6 +1071,12 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
     __shared__ u64 s_cl_r0[CL_CAP], s_cl_r1[CL_CAP];            // MULTI: reduced (edges, meet<<32 | discovered) handed from the leader warp to thread 0
     E.solo = true; E.A = &sm.acc; E.sA = &sm.acc; E.filter = false; E.s_hub = &sm.hub;
     E.s_sent = &s_sent[0][0]; E.s_rnew = &s_rnew;
+    // the pointers of the claim loop, named so that they stay in registers (E itself is a stack copy)
+    const u32* const g_col = E.col;
+    const u64* const g_row = E.row_ptr;
+    u64* const g_vis = E.vis;
+    u64* const dummy = dummy_of(K, E.me);
+    const u32 g_lo = E.lo;
     // thread 0 keeps the level state in registers across levels
     u32 nf0 = st.nf[0], nf1 = st.nf[1], d0 = st.depth[0], d1 = st.depth[1], levels = st.levels;
     u32 qlo0 = st.q_lo[0], qlo1 = st.q_lo[1], qhi0 = st.q_hi[0], qhi1 = st.q_hi[1];
@@ -1076,8 +1084,9 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
     u64 pend_edges = 0, pend_vis = 0;
     auto make_level = [&](u32 sd) {
         SoloLevel lv;
-        lv.side_flags = sd | ((sd ? val1 : val0) ? 2u : 0u) | ((sd ? cur1 : cur0) ? 4u : 0u);
         lv.total = st.local_front;
+        const bool enlist = !MULTI && sm.cl_n > 1 && lv.total > (u32)BFS_THREADS;   // bit 4: the cluster helpers take part
+        lv.side_flags = sd | ((sd ? val1 : val0) ? 2u : 0u) | ((sd ? cur1 : cur0) ? 4u : 0u) | (enlist ? 16u : 0u);
         lv.q_lo = sd ? qlo1 : qlo0;
         lv.base_tail = sd ? qhi1 : qhi0;
         lv.nq = lv.base_tail - lv.q_lo;
@@ -1086,7 +1095,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         lv.pad = 0;
         s_lv = lv;
         // a frontier larger than this CTA: the other CTAs of the cluster take the slices beyond the first
-        if (!MULTI && cl_n > 1 && lv.total > (u32)BFS_THREADS) {
+        if (enlist) {
             sm.cl_cmd = CL_HELP;
             ptx::dsmem_st_release(ptx::smem_addr(&sm.cl_seq), sm.cl_seq + 1u);
         }
@@ -1099,7 +1108,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         const uint4 raw = *reinterpret_cast<const uint4*>(&s_lv);
         const u32 side = raw.x & 1u, total = raw.y, base_tail = raw.w;
         if (raw.x & 8u) break;
-        const bool cluster_level = !MULTI && cl_n > 1 && total > (u32)BFS_THREADS;
+        const bool cluster_level = !MULTI && (raw.x & 16u);
         const u32 cur = (raw.x >> 2) & 1u;
         u32* const out = sm.q[side][cur ^ 1u];
         const u32 sh = 32u * side, osh = 32u - sh;
@@ -1114,8 +1123,8 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         if (tid < total) {
             if (!MULTI || tid < nq) u = (raw.x & 2u) ? sm.q[side][cur][tid] : __ldcg(E.q[side] + raw.z + tid);
             else u = fetch_rq(K, E, st, side, tid - nq, rq_tag);     // entry of a sender segment (tagged, polled)
-            r0 = __ldg(E.row_ptr + (u - E.lo));
-            r1 = __ldg(E.row_ptr + (u - E.lo) + 1);
+            r0 = __ldg(g_row + (u - g_lo));
+            r1 = __ldg(g_row + (u - g_lo) + 1);
         }
         u32 deg = (u32)min(r1 - r0, (u64)0xFFFFFFFFu);
         DBG_STAMP(1, deg);
@@ -1134,41 +1143,41 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             u64 old[SW];
             // branch-free issue: idle slots re-read the row's first entry and OR a zero into a private
             // scratch word, so that all SW loads and then all SW claims are in flight together
-            u64* const dummy = dummy_of(K, E.me);
 #pragma unroll
-            for (int k = 0; k < SW; ++k) v[k] = __ldg(E.col + r0 + ((e0 + k < sdeg) ? e0 + k : 0u));
+            for (int k = 0; k < SW; ++k) v[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((e0 + k < sdeg) ? e0 + k : 0u));
 #pragma unroll
             for (int k = 0; k < SW; ++k) {
                 const bool act = e0 + k < sdeg;
-                old[k] = ptx::atom_or_gpu(act ? &E.vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
+                old[k] = ptx::atom_or_gpu(act ? &g_vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
             }
 #pragma unroll
             for (int k = 0; k < SW; ++k)
                 if (!(e0 + k < sdeg)) old[k] = ~0ull;
             DBG_STAMP(3, v[0] + v[SW - 1]);
             u32 newmask = 0, meetmask = 0, remmask = 0;
+            const u32 shz = sh + ptx::zero_after(old[SW - 1]);      // == sh; pins the tests behind the whole batch
 #pragma unroll
             for (int k = 0; k < SW; ++k) {
-                const u32 isnew = ((u32)(old[k] >> ((v[k] & 31u) + sh)) & 1u) ^ 1u;
+                const u32 isnew = ((u32)(old[k] >> ((v[k] & 31u) + shz)) & 1u) ^ 1u;
                 newmask |= isnew << k;
             }
             if (MULTI && __any_sync(FULL, newmask != 0)) {
                 // vertices of other ranks: the local bit was only a "not forwarded yet" filter — claim at the
                 // owner.  Branch-free again so that the NVLink round trips (1.6 us each) overlap.
-                u64* const dummy = dummy_of(K, E.me);
                 u64 rold[SW];
 #pragma unroll
                 for (int k = 0; k < SW; ++k) {
-                    const bool rem = ((newmask >> k) & 1u) && (v[k] - E.lo) >= K.B;
+                    const bool rem = ((newmask >> k) & 1u) && (v[k] - g_lo) >= K.B;
                     remmask |= rem ? (1u << k) : 0u;
                     u64* const addr = rem ? (vis_of(K, v[k] / K.B) + (v[k] >> 5)) : dummy;
                     rold[k] = ptx::atom_or_sys(addr, rem ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
                 }
+                const u32 shr = sh + ptx::zero_after(rold[SW - 1]);
 #pragma unroll
                 for (int k = 0; k < SW; ++k) {
                     if ((remmask >> k) & 1u) {
                         old[k] = rold[k];
-                        if ((rold[k] >> ((v[k] & 31u) + sh)) & 1ull) { newmask &= ~(1u << k); remmask &= ~(1u << k); }
+                        if ((rold[k] >> ((v[k] & 31u) + shr)) & 1ull) { newmask &= ~(1u << k); remmask &= ~(1u << k); }
                     }
                 }
             }
@@ -1179,13 +1188,15 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             const u32 locmask = newmask & ~remmask;
             if (locmask) {
                 u32 slot = ptx::atoms_add(&sm.acc.q_tail[side], (u32)__popc(locmask));
+                u32* const qs = E.q[side];
+                u32* const ps = E.parent[side];
 #pragma unroll
                 for (int k = 0; k < SW; ++k) {
                     if ((locmask >> k) & 1u) {
-                        E.q[side][slot] = v[k];
-                        E.parent[side][v[k] - E.lo] = u;
+                        qs[slot] = v[k];
+                        ps[v[k] - g_lo] = u;
                         if (slot - base_tail < SOLO_CAP) out[slot - base_tail] = v[k];
-                        ptx::prefetch_l2(E.row_ptr + (v[k] - E.lo));
+                        ptx::prefetch_l2(g_row + (v[k] - g_lo));
                         ++slot;
                     }
                 }
@@ -1440,16 +1451,17 @@ __device__ __noinline__ void cluster_helper(const KParams& K, const Env& E, Smem
             u32 v[SW];
             u64 old[SW];
 #pragma unroll
-            for (int k = 0; k < SW; ++k) v[k] = __ldg(E.col + r0 + ((e0 + k < deg) ? e0 + k : 0u));
+            for (int k = 0; k < SW; ++k) v[k] = ptx::ld_relaxed_gpu(E.col + r0 + ((e0 + k < deg) ? e0 + k : 0u));
 #pragma unroll
             for (int k = 0; k < SW; ++k) {
                 const bool act = e0 + k < deg;
                 old[k] = ptx::atom_or_gpu(act ? &E.vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
             }
             u32 newmask = 0, meetmask = 0;
+            const u32 shz = sh + ptx::zero_after(old[SW - 1]);
 #pragma unroll
             for (int k = 0; k < SW; ++k) {
-                const u32 isnew = (e0 + k < deg) ? (((u32)(old[k] >> ((v[k] & 31u) + sh)) & 1u) ^ 1u) : 0u;
+                const u32 isnew = (e0 + k < deg) ? (((u32)(old[k] >> ((v[k] & 31u) + shz)) & 1u) ^ 1u) : 0u;
                 newmask |= isnew << k;
                 meetmask |= (isnew & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
             }
@@ -1524,7 +1536,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     if (tid == 0) { s_fail = 0; s_hub = 0; s_qvalid[0] = 0; s_qvalid[1] = 0; s_qcur[0] = 0; s_qcur[1] = 0; sm.pend_edges = 0; sm.pend_visited = 0; sm.stage_cnt = 0; sm.cta_new = 0; sm.cta_edges = 0; }
     if (lane == 0) { ptx::mbar_init(&sm.hub_bar[warp][0], 1); ptx::mbar_init(&sm.hub_bar[warp][1], 1); ptx::mbar_fence_init(); }
     u32 hub_parity = 0;            // phase bits of this warp's two hub barriers
-    if (tid == 0) { sm.cl_seq = 0; sm.cl_cmd = 0; }
+    if (tid == 0) { sm.cl_seq = 0; sm.cl_cmd = 0; sm.cl_n = cl_n; }
     __syncthreads();
     if (cl_n > 1) ptx::cluster_sync_all();     // the helpers may now poll the leader's command word
 
@@ -1643,7 +1655,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 continue;
             }
             {
-                solo_run<MULTI>(K, E, sm, deadline, cl_n);
+                solo_run<MULTI>(K, E, sm, deadline);
                 if (s_fail) { if (warp == 0) publish_and_wake(); __syncthreads(); alive = false; break; }
                 if (warp == 0) publish_and_wake();      // left solo mode: the grid is needed (or the query is done)
                 __syncthreads();
@@ -1850,6 +1862,17 @@ int bfs_max_ctas_clustered(u32 cluster, int* out) {
     *out = n * (int)cluster;
     return 0;
 }
+
+#ifdef BIBFS_FINE_TRACE
+extern "C" int bibfs_debug_read(uint64_t* out, uint32_t* levels) {
+    cudaMemcpyFromSymbol(out, g_dbg, sizeof(u64) * 256 * 8);
+    cudaMemcpyFromSymbol(out + 256 * 8, g_dbg2, sizeof(u64) * 256 * 8);
+    cudaMemcpyFromSymbol(levels, g_dbg_level, 4);
+    u32 z = 0;
+    cudaMemcpyToSymbol(g_dbg_level, &z, 4);
+    return 0;
+}
+#endif
 
 int path_launch(const KParams& K, cudaStream_t st) {
     k_path<<<1, 64, 0, st>>>(K);

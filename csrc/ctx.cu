@@ -8,6 +8,7 @@
 // explicitly (v4 never calls cudaSetDevice); and the per-level host calls are gone —
 // bibfs_ctx_query enqueues the whole search.
 #include "bfs.h"
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -78,7 +79,7 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     c->cpr = per_rank;
     // single rank: launch in clusters of 4 so that the leader CTA can enlist three neighbours over DSMEM
     // (frontiers up to 2048 vertices stay off the grid-wide barrier)
-    if (!c->multi && desc->vranks == 1 && per_rank >= 8) {
+    if (!c->multi && desc->vranks == 1 && per_rank >= 8 && !getenv("BIBFS_NO_CLUSTER")) {
         int fit = 0;
         if (bfs_max_ctas_clustered(4, &fit) == 0 && fit >= 8) {
             c->cluster = 4;

@@ -90,6 +90,16 @@ __device__ __forceinline__ void st_peer_v4(u32* p, u32 a, u32 b, u32 c, u32 d) {
     asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+// Scheduling fence for batches of independent atomics.  ptxas likes to consume the result of the first
+// atomic of a batch before it has issued the last one (seen in SASS: ATOMG x2, SHF on the first result,
+// ATOMG x6), which turns N overlapping 285 ns round trips into two back-to-back ones.  This returns a
+// zero that ptxas cannot prove to be zero and that depends on `last`; adding it to the operands of the
+// consumers pins them behind the whole batch.  (popc of a 64-bit word is at most 64.)
+__device__ __forceinline__ u32 zero_after(u64 last) {
+    u32 z;
+    asm volatile("{\n\t.reg .u32 t;\n\tpopc.b64 t, %1;\n\tshr.u32 %0, t, 7;\n\t}" : "=r"(z) : "l"(last));
+    return z;
+}
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void nanosleep(u32 ns) { asm volatile("nanosleep.u32 %0;" ::"r"(ns)); }
 
