@@ -2,6 +2,7 @@
 #   make            -> bidirectional_bfs_b200/_native/libbibfs_b200.so + bin/bibfs
 #   make sass       -> docs/sass/*.sass listings (cuobjdump)
 #   make clean
+#   make EXTRA=-DBIBFS_FINE_TRACE BUILD=build_ft OUTDIR=build_ft/lib   -> instrumented copy (load it with BIBFS_B200_LIB=...)
 # Counterpart of the reference's per-variant Makefiles (v1..v4/Makefile); the reference's SMS list
 # (sm_50..sm_90, v3/Makefile:16-18) is replaced by the single Blackwell target.
 NVCC      ?= /usr/local/cuda/bin/nvcc
@@ -10,8 +11,8 @@ ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVCCFLAGS := $(EXTRA) $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O3,-Wall,-Wno-unknown-pragmas \
              -Xptxas -v --expt-relaxed-constexpr -Iinclude
 CXXFLAGS  := -O3 -std=c++17 -fPIC -Wall -Wno-unknown-pragmas -ffp-contract=off -Iinclude -pthread
-BUILD     := build
-OUTDIR    := bidirectional_bfs_b200/_native
+BUILD     ?= build
+OUTDIR    ?= bidirectional_bfs_b200/_native
 LIB       := $(OUTDIR)/libbibfs_b200.so
 CLI       := bin/bibfs
 

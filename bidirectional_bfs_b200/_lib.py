@@ -15,7 +15,7 @@ from pathlib import Path
 
 _PKG = Path(__file__).resolve().parent
 _ROOT = _PKG.parent
-_SO = _PKG / "_native" / "libbibfs_b200.so"
+_SO = Path(os.environ["BIBFS_B200_LIB"]) if os.environ.get("BIBFS_B200_LIB") else _PKG / "_native" / "libbibfs_b200.so"
 _lock = threading.Lock()
 _lib = None
 

@@ -198,45 +198,67 @@ __device__ __forceinline__ bool expired(Ctrl* C, u64 deadline) {
     return ptx::globaltimer_ns() > deadline || ptx::ld_relaxed_gpu(&C->abort_flag) != 0;
 }
 
-// `parked`: the CTA may wait for many levels (solo mode) -> back off; otherwise the release is imminent -> poll hard
+// ---- polling loops are WARP-COLLECTIVE -----------------------------------------------------
+// Every lane of the calling warp runs the loop and all lanes leave it in the same iteration.
+// Measured reason (profiles/latency_microbench.md): when ONE lane spins while the other lanes of
+// its warp wait at the implicit reconvergence point, the hardware releases the waiting lanes after
+// ~4 us (forward-progress guarantee of independent thread scheduling).  From then on the warp runs
+// diverged and every later *_sync collective takes the WARPSYNC.COLLECTIVE slow path (~150 ns
+// apiece): a level that had waited 4 us for a peer paid another 2.6 us for its shuffles.
+
+__device__ __forceinline__ bool expired_warp(Ctrl* C, u64 deadline) {
+    bool ex = false;
+    if ((threadIdx.x & 31) == 0) ex = expired(C, deadline);
+    return __shfl_sync(FULL, (int)ex, 0) != 0;
+}
+
+// whole warp.  `parked`: the CTA may wait for many levels (solo mode) -> back off; otherwise the release is imminent -> poll hard
 __device__ bool wait_gen(Ctrl* C, u64 want, u64 deadline, bool parked = true) {
+    const u32 lane = threadIdx.x & 31;
     u32 spins = 0;
-    while (ptx::ld_acquire_gpu(&C->bar_gen) < want) {
+    while (true) {
+        u64 g = 0;
+        if (lane == 0) g = ptx::ld_acquire_gpu(&C->bar_gen);
+        g = __shfl_sync(FULL, g, 0);
+        if (g >= want) return true;
         if (++spins > (parked ? 64u : 4096u)) {
             ptx::nanosleep(32);
-            if ((spins & 255u) == 0 && expired(C, deadline)) return false;
+            if ((spins & 255u) == 0 && expired_warp(C, deadline)) return false;
         }
     }
-    return true;
 }
 
 // leader warp: lane w < BAR_WAYS waits until every non-leader CTA mapped to way w has arrived, then resets the way
 __device__ bool wait_count(Ctrl* C, u32 cpr, u64 deadline) {
     const u32 lane = threadIdx.x & 31;
-    bool ok = true;
-    if (lane < BAR_WAYS) {
-        // CTAs 1..cpr-1 arrive; CTA c uses way c % BAR_WAYS
-        const u32 want = lane < cpr ? (cpr - 1u - lane) / BAR_WAYS + (lane != 0 ? 1u : 0u) : 0u;
-        u32 spins = 0;
-        while (want && ptx::ld_acquire_gpu(&C->bar_way[lane].count) < want) {
-            if (++spins > 64 && (spins & 255u) == 0 && expired(C, deadline)) { ok = false; break; }
-        }
-        if (want) ptx::st_relaxed_gpu(&C->bar_way[lane].count, 0u);
-    }
-    return __all_sync(FULL, ok);
-}
-
-// poll the four tagged words a peer writes into this rank's slot until they carry `tag`
-__device__ bool wait_slot(Ctrl* C, const LSlot* sl, u32 tag, Slot& out, u64 deadline) {
+    // CTAs 1..cpr-1 arrive; CTA c uses way c % BAR_WAYS
+    const u32 want = (lane < BAR_WAYS && lane < cpr) ? (cpr - 1u - lane) / BAR_WAYS + (lane != 0 ? 1u : 0u) : 0u;
+    bool ok = true, done = want == 0;
     u32 spins = 0;
     while (true) {
-        const u64 a = ptx::ld_relaxed_sys(&sl->w[0]), b = ptx::ld_relaxed_sys(&sl->w[1]);
-        const u64 c = ptx::ld_relaxed_sys(&sl->w[2]), d = ptx::ld_relaxed_sys(&sl->w[3]);
-        if ((u32)(a >> 32) == tag && (u32)(b >> 32) == tag && (u32)(c >> 32) == tag && (u32)(d >> 32) == tag) {
-            out.count = (u32)a; out.meet = (u32)b; out.rq_tail = (u32)c; out.edges = (u32)d;
-            return true;
+        if (!done) done = ptx::ld_acquire_gpu(&C->bar_way[lane].count) >= want;
+        if (__all_sync(FULL, done)) break;
+        if (++spins > 64 && (spins & 255u) == 0 && expired_warp(C, deadline)) { ok = false; break; }
+    }
+    if (want) ptx::st_relaxed_gpu(&C->bar_way[lane].count, 0u);
+    return ok;
+}
+
+// whole warp; lanes with sl != nullptr poll the four tagged words a peer writes into this rank's slot until they carry `tag`
+__device__ bool wait_slot(Ctrl* C, const LSlot* sl, u32 tag, Slot& out, u64 deadline) {
+    bool done = sl == nullptr;
+    u32 spins = 0;
+    while (true) {
+        if (!done) {
+            const u64 a = ptx::ld_relaxed_sys(&sl->w[0]), b = ptx::ld_relaxed_sys(&sl->w[1]);
+            const u64 c = ptx::ld_relaxed_sys(&sl->w[2]), d = ptx::ld_relaxed_sys(&sl->w[3]);
+            if ((u32)(a >> 32) == tag && (u32)(b >> 32) == tag && (u32)(c >> 32) == tag && (u32)(d >> 32) == tag) {
+                out.count = (u32)a; out.meet = (u32)b; out.rq_tail = (u32)c; out.edges = (u32)d;
+                done = true;
+            }
         }
-        if (++spins > 64 && (spins & 255u) == 0 && expired(C, deadline)) return false;
+        if (__all_sync(FULL, done)) return true;
+        if (++spins > 64 && (spins & 255u) == 0 && expired_warp(C, deadline)) return false;
     }
 }
 
@@ -310,12 +332,11 @@ __device__ __noinline__ bool cross_exchange(const KParams& K, const Env& E, Leve
         ptx::st_relaxed_sys(&dst->w[1], tag | mine_for_lane.meet);
         ptx::st_relaxed_sys(&dst->w[2], tag | mine_for_lane.rq_tail);
         ptx::st_relaxed_sys(&dst->w[3], tag | mine_for_lane.edges);
-        ok = wait_slot(E.C, &E.C->slot[par][lane], (u32)epoch, got, deadline);
-        if (fenced) ptx::fence_sys();
     } else {
         got.count = 0; got.meet = NO_V; got.rq_tail = 0; got.edges = 0;
     }
-    ok = __all_sync(FULL, ok);
+    ok = wait_slot(E.C, lane < K.P ? &E.C->slot[par][lane] : nullptr, (u32)epoch, got, deadline);
+    if (fenced && lane < K.P) ptx::fence_sys();
     if (lane == 0) G.xepoch = epoch;
     __syncwarp();
     return ok;
@@ -523,23 +544,28 @@ __device__ __forceinline__ u32 fetch_frontier(const KParams& K, const Env& E, co
     return v;
 }
 
-// entry i of the concatenated sender-segment windows (i counts past the local window)
-__device__ __forceinline__ u32 fetch_rq(const KParams& K, const Env& E, const LevelState& st, u32 side, u32 i, u32 tag) {
-    u32 v = 0;
+// address of entry i of the concatenated sender-segment windows (i counts past the local window)
+__device__ __forceinline__ const u64* rq_entry(const KParams& K, const Env& E, const LevelState& st, u32 side, u32 i) {
 #pragma unroll 1
     for (u32 p = 0; p < K.P; ++p) {
         const u32 lo = st.rq_lo[side][p], c = st.rq_hi[side][p] - lo;
-        if (i < c) {
-            const u64* e = rq_of(K, E.me, side, p) + lo + i;
-            u64 w = ptx::ld_relaxed_sys(e);
-            for (u32 spins = 0; (u32)(w >> 32) != tag && spins < (1u << 24); ++spins) w = ptx::ld_relaxed_sys(e);
-            if ((u32)(w >> 32) != tag) atomicExch(&E.C->abort_flag, 1u);
-            v = (u32)w;
-            break;
-        }
+        if (i < c) return rq_of(K, E.me, side, p) + lo + i;
         i -= c;
     }
-    return v;
+    return nullptr;
+}
+// whole warp: lanes with e != nullptr read their tagged entry, polling until it carries `tag` (the sender's relaxed
+// stores may land after the exchange words that announced them); warp-collective like every polling loop
+__device__ __forceinline__ u32 fetch_rq(const Env& E, const u64* e, u32 tag) {
+    u64 w = 0;
+    bool done = e == nullptr;
+    u32 spins = 0;
+    while (true) {
+        if (!done) { w = ptx::ld_relaxed_sys(e); done = (u32)(w >> 32) == tag; }
+        if (__all_sync(FULL, done)) break;
+        if (++spins > (1u << 22)) { if (!done) atomicExch(&E.C->abort_flag, 1u); break; }
+    }
+    return (u32)w;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1120,9 +1146,13 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         }
         u32 u = 0;
         u64 r0 = 0, r1 = 0;
+        if (MULTI && (warp + 1u) * 32u > nq && warp * 32u < total) {
+            // this warp reads entries of sender segments (tagged, polled by the whole warp together)
+            const u64* e = (tid >= nq && tid < total) ? rq_entry(K, E, st, side, tid - nq) : nullptr;
+            u = fetch_rq(E, e, rq_tag);
+        }
         if (tid < total) {
             if (!MULTI || tid < nq) u = (raw.x & 2u) ? sm.q[side][cur][tid] : __ldcg(E.q[side] + raw.z + tid);
-            else u = fetch_rq(K, E, st, side, tid - nq, rq_tag);     // entry of a sender segment (tagged, polled)
             r0 = __ldg(g_row + (u - g_lo));
             r1 = __ldg(g_row + (u - g_lo) + 1);
         }
@@ -1399,21 +1429,26 @@ __device__ __noinline__ void cluster_helper(const KParams& K, const Env& E, Smem
     const u32 a_meet = ptx::dsmem_map(ptx::smem_addr(&sm.acc.meet_local), 0);
     const u32 a_edges = ptx::dsmem_map(ptx::smem_addr(&sm.acc.edges), 0);
     while (true) {
-        if (tid == 0) {
-            u32 v, spins = 0;
+        if (tid < 32) {
+            // warp-collective poll (see wait_gen): lane 0 reads the leader's sequence word, all lanes leave together
+            u32 v = seen_seq, spins = 0;
             bool dead = false;
-            while ((v = ptx::dsmem_ld(a_seq)) == seen_seq) {
+            while (true) {
+                if (lane == 0) v = ptx::dsmem_ld(a_seq);
+                v = __shfl_sync(FULL, v, 0);
+                if (v != seen_seq) break;
                 // back off: every poll is a request to the LEADER's shared-memory port, which it needs itself
                 ptx::nanosleep(96);
-                if (++spins > 4096u && (spins & 1023u) == 0 && expired(E.C, deadline)) { dead = true; break; }
+                if (++spins > 4096u && (spins & 1023u) == 0 && expired_warp(E.C, deadline)) { dead = true; break; }
             }
-            v = ptx::dsmem_ld_acquire(a_seq);
-            s_seq = v;
-            s_cmd = dead ? (u32)CL_EXIT : ptx::dsmem_ld(a_cmd);
-            if (!dead && s_cmd == CL_HELP) {
-                u32* d = reinterpret_cast<u32*>(&s_lvc);
-                for (u32 i = 0; i < sizeof(SoloLevel) / 4; ++i) d[i] = ptx::dsmem_ld(a_lv + 4 * i);
+            if (lane == 0) {
+                v = ptx::dsmem_ld_acquire(a_seq);
+                s_seq = v;
+                s_cmd = dead ? (u32)CL_EXIT : ptx::dsmem_ld(a_cmd);
             }
+            __syncwarp();
+            if (!dead && s_cmd == CL_HELP && lane < sizeof(SoloLevel) / 4)
+                reinterpret_cast<u32*>(&s_lvc)[lane] = ptx::dsmem_ld(a_lv + 4 * lane);
         }
         __syncthreads();
         seen_seq = s_seq;
@@ -1587,7 +1622,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         __syncthreads();
     } else {
         if (in_leader_cluster) cluster_helper(K, E, sm, cl_rank, cl_seen, deadline);   // may be needed before the first release
-        if (tid == 0 && !wait_gen(C, genbase | 1u, deadline)) s_fail = 1;
+        if (warp == 0 && !wait_gen(C, genbase | 1u, deadline) && lane == 0) s_fail = 1;
         __syncthreads();
         if (!s_fail) load_state();
     }
@@ -1614,11 +1649,14 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
             if (tid == 0) { sm.stage_cnt = 0; sm.cta_new = 0; sm.cta_edges = 0; }
         }
         if (!is_leader_cta) {
-            if (tid == 0) {
-                if (MULTI && mode == PH_BU) ptx::fence_sys();   // bitmap slices pushed with plain stores
-                ptx::red_release_gpu_add(&C->bar_way[E.cta % BAR_WAYS].count, 1u);
+            if (warp == 0) {
+                if (lane == 0) {
+                    if (MULTI && mode == PH_BU) ptx::fence_sys();   // bitmap slices pushed with plain stores
+                    ptx::red_release_gpu_add(&C->bar_way[E.cta % BAR_WAYS].count, 1u);
+                }
+                __syncwarp();
                 DBG_STAMP3(4, tid);      // arrived
-                if (!wait_gen(C, genbase | (u64)(st.wake + 1u), deadline, false)) s_fail = 1;
+                if (!wait_gen(C, genbase | (u64)(st.wake + 1u), deadline, false) && lane == 0) s_fail = 1;
                 DBG_STAMP3(5, tid);      // released
             }
             __syncthreads();
@@ -1648,7 +1686,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         if (phase == PH_TD_SOLO) {
             if (!is_leader_cta) {   // parked until the leader wakes the grid
                 if (in_leader_cluster) cluster_helper(K, E, sm, cl_rank, cl_seen, deadline);   // ... helping it meanwhile
-                if (tid == 0 && !wait_gen(C, genbase | (u64)(st.wake + 1u), deadline)) s_fail = 1;
+                if (warp == 0 && !wait_gen(C, genbase | (u64)(st.wake + 1u), deadline) && lane == 0) s_fail = 1;
                 __syncthreads();
                 if (s_fail) { alive = false; break; }
                 load_state();

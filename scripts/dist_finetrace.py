@@ -9,14 +9,17 @@ L = bb.lib()
 spec = bb.preset_spec("100k", seed=1)
 g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
 s = comm.DistributedSolver(g)
-for _ in range(3): s.query(0, spec.n - 1, want_path=False)
+SRC, DST = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (0, spec.n - 1)
+for _ in range(3): s.query(SRC, DST, want_path=False)
 out = np.zeros((512, 8), dtype=np.uint64); lv = C.c_uint32(0)
 L.bibfs_debug_read(out.ctypes.data, C.byref(lv))
-s.query(0, spec.n - 1, want_path=False)
+s.query(SRC, DST, want_path=False)
 L.bibfs_debug_read(out.ctypes.data, C.byref(lv))
-if rank == 0:
-    names = ["rowptr", "reduce", "col+atom", "remote", "enqueue", "syncthr", "levelend+xchg"]
+import time; time.sleep(0.5 * rank)
+if True:
+    print('--- rank', rank)
     for i in range(min(lv.value, 16)):
-        t = out[i].astype(np.int64)
-        print(i, " ".join(f"{names[k]}={t[k+1]-t[k]}" for k in range(7)), "| total", t[7]-t[0], "| gap", (out[i+1][0].astype(np.int64)-t[7]) if i+1 < lv.value else 0)
+        t = out[i].astype(np.int64); d2 = out[256 + i].astype(np.int64)
+        print("L%-2d work %5d | sync->poll %5d | poll wait %5d (first word +%d, hit %d, spins %d) | poll->allsync %5d | ->tid0 %5d | ->end %5d | total %5d" % (
+            i, t[6] - t[0], d2[0] - t[6], d2[2] - d2[0], d2[1] - d2[0], d2[4], d2[3], d2[5] - d2[2], d2[6] - d2[5], t[7] - d2[6], t[7] - t[0]))
 s.close(); dist.destroy_process_group()
