@@ -158,6 +158,7 @@ struct KParams {
     u32 seq;                       // launch sequence number (local barrier generation prefix)
     u32 watchdog_ms;
     u32 src, dst, query_in_ctrl;   // query by value, or (query_in_ctrl) read from Ctrl::q_src/q_dst
+    u64 div_B;                     // 2^64 / B rounded up: owner(v) = umulhi64(div_B, v), exact for 32-bit v
     const u32* h_query;            // pinned host memory holding {src,dst}: read by the kernel itself (zero copy), or null
     u32* h_out;                    // pinned host buffer [Result | first path entries] written by the path kernel, or null
     u32 h_out_words;               // path entries that fit in h_out

@@ -138,6 +138,9 @@ __device__ __forceinline__ u64* dummy_of(const KParams& K, u32 r) {
     return reinterpret_cast<u64*>(K.arena[r] + K.L.off_dummy) + ((blockIdx.x * BFS_THREADS + threadIdx.x) % DUMMY_WORDS);
 }
 
+// rank that owns vertex v (v / B without the 20-instruction division)
+__device__ __forceinline__ u32 owner_of(const KParams& K, u32 v) { return (u32)__umul64hi(K.div_B, (u64)v); }
+
 __device__ __forceinline__ u32 lanemask_lt() {
     u32 m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
@@ -592,7 +595,7 @@ __device__ __forceinline__ Claim claim(const KParams& K, const Env& E, u32 side,
             if (!(old & bit)) {
                 c.isnew = true;
                 if (MULTI) {
-                    c.dest = v / K.B;
+                    c.dest = owner_of(K, v);
                     if (c.dest != E.me) {
                         // first time THIS rank sees v: ask the owner.  One round trip returns both
                         // "new for this side" and "already reached by the other side".
@@ -688,7 +691,7 @@ __device__ __noinline__ u32 visit_batch(const KParams& K, const Env& E, u32 side
             u64 rold[UNR];
 #pragma unroll
             for (int k = 0; k < UNR; ++k) {
-                const u32 dest = c[k].isnew ? v[k] / K.B : E.me;
+                const u32 dest = c[k].isnew ? owner_of(K, v[k]) : E.me;
                 rem[k] = dest != E.me;
                 c[k].dest = dest;
                 rold[k] = ptx::atom_or_sys(rem[k] ? (vis_of(K, dest) + (v[k] >> 5)) : dummy, rem[k] ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
@@ -1199,7 +1202,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
                 for (int k = 0; k < SW; ++k) {
                     const bool rem = ((newmask >> k) & 1u) && (v[k] - g_lo) >= K.B;
                     remmask |= rem ? (1u << k) : 0u;
-                    u64* const addr = rem ? (vis_of(K, v[k] / K.B) + (v[k] >> 5)) : dummy;
+                    u64* const addr = rem ? (vis_of(K, owner_of(K, v[k])) + (v[k] >> 5)) : dummy;
                     rold[k] = ptx::atom_or_sys(addr, rem ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
                 }
                 const u32 shr = sh + ptx::zero_after(rold[SW - 1]);
@@ -1235,7 +1238,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
 #pragma unroll
                 for (int k = 0; k < SW; ++k) {
                     if ((remmask >> k) & 1u) {
-                        const u32 dest = v[k] / K.B;
+                        const u32 dest = owner_of(K, v[k]);
                         const u32 slot = ptx::atoms_add(&s_sent[side][dest], 1u);
                         ptx::st_relaxed_sys(rq_of(K, dest, side, E.me) + slot, (u64)v[k] | ((u64)tag << 32));
                         ptx::st_peer(parent_of(K, dest, side) + (v[k] - dest * K.B), u);

@@ -183,6 +183,7 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     K.seq = ++c->seq;
     K.watchdog_ms = c->d.watchdog_ms;
     K.src = src; K.dst = dst; K.query_in_ctrl = 0u;
+    K.div_B = ~0ull / c->B + 1ull;
     K.h_query = nullptr; K.h_out = nullptr; K.h_out_words = 0;
     K.L = c->L;
     for (u32 r = 0; r < MAXR; ++r) K.arena[r] = c->arena_all[r];

@@ -18,8 +18,8 @@ L.bibfs_debug_read(out.ctypes.data, C.byref(lv))
 import time; time.sleep(0.5 * rank)
 if True:
     print('--- rank', rank)
+    names = ["rowptr", "reduce", "col", "claims", "enqueue", "syncthr", "levelend+xchg"]
     for i in range(min(lv.value, 16)):
-        t = out[i].astype(np.int64); d2 = out[256 + i].astype(np.int64)
-        print("L%-2d work %5d | sync->poll %5d | poll wait %5d (first word +%d, hit %d, spins %d) | poll->allsync %5d | ->tid0 %5d | ->end %5d | total %5d" % (
-            i, t[6] - t[0], d2[0] - t[6], d2[2] - d2[0], d2[1] - d2[0], d2[4], d2[3], d2[5] - d2[2], d2[6] - d2[5], t[7] - d2[6], t[7] - t[0]))
+        t = out[i].astype(np.int64)
+        print("L%-2d" % i, " ".join(f"{names[k]}={t[k+1]-t[k] if abs(t[k+1]-t[k]) < 10**7 else -1}" for k in range(7)), "| total", t[7]-t[0])
 s.close(); dist.destroy_process_group()
