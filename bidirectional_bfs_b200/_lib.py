@@ -23,7 +23,7 @@ MAX_RANKS = 8
 NO_VERTEX = 0xFFFFFFFF
 
 # query flags (bibfs_b200.h)
-F_TRACE, F_FORCE_GRID, F_FORCE_TD, F_FORCE_BU, F_NO_PATH = 1, 2, 4, 8, 16
+F_TRACE, F_FORCE_GRID, F_FORCE_TD, F_FORCE_BU, F_NO_PATH, F_DEVICE_CLOCK = 1, 2, 4, 8, 16, 32
 
 
 class GenSpec(C.Structure):

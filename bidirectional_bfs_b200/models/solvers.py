@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 import torch
 
-from .._lib import F_NO_PATH, Result, check, lib
+from .._lib import F_DEVICE_CLOCK, F_NO_PATH, Result, check, lib
 from ..graph import Graph
 from ..ops.search import PathResult, SearchContext, result_from_c
 
@@ -90,9 +90,17 @@ class GpuSolver:
         self.graph = graph
         self.ctx = SearchContext(graph, 0, 1, **ctx_kw)
 
-    def query(self, src, dst, want_path=True, flags=0, pinned_query=None) -> PathResult:
+    def query(self, src, dst, want_path=True, flags=0, pinned_query=None, timing="device") -> PathResult:
+        """One launch per query.  ``timing="device"`` (default): no CUDA events around the launch, the call returns
+        as soon as the kernel has written [result | path] into pinned memory, ``search_ms`` / ``path_ms`` are measured
+        by the device's own clock inside the kernel.  ``timing="events"``: cudaEvent pair around the launch (what
+        bench.py reports as the device-timed number; includes the launch latency of the kernel)."""
         if not want_path:
             flags |= F_NO_PATH
+        if timing == "device":
+            flags |= F_DEVICE_CLOCK
+        elif timing != "events":
+            raise ValueError("timing must be 'device' or 'events'")
         return self.ctx.query(src, dst, flags, want_path, pinned_query, self.variant)
 
     def close(self):
@@ -135,7 +143,7 @@ class MultiGpuSolver:
                     a.attach_local(b.rank_lo, b)
         return self
 
-    def query(self, src, dst, want_path=True, flags=0) -> PathResult:
+    def query(self, src, dst, want_path=True, flags=0, timing=None) -> PathResult:   # timing: always CUDA events
         if not want_path:
             flags |= F_NO_PATH
         for c in self.ctxs:

@@ -63,7 +63,7 @@ class DistributedSolver:
     def fetch(self, src, dst, want_path=True) -> PathResult:
         return self.ctx.fetch(src, dst, want_path, self.variant)
 
-    def query(self, src, dst, want_path=True, flags=0, pinned_query=None) -> PathResult:
+    def query(self, src, dst, want_path=True, flags=0, pinned_query=None, timing=None) -> PathResult:   # timing: always CUDA events
         if not want_path:
             flags |= F_NO_PATH
         return self.ctx.query(src, dst, flags, want_path, pinned_query, self.variant)

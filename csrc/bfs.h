@@ -76,7 +76,8 @@ struct alignas(16) Result {   // 64 bytes (PATH_HDR_WORDS words)
     i32 status;
     u64 edges_scanned;
     u64 vertices_visited;
-    u64 t_begin_ns, t_end_ns;
+    u64 t_begin_ns;            // device clock (%globaltimer) when the search proper began
+    u32 search_ns, path_ns;    // device-measured duration of the search and of the path walk (saturating)
 };
 
 // level accumulators: one copy in Ctrl (grid mode), one in shared memory (solo mode)
@@ -157,11 +158,14 @@ struct KParams {
     u32 solo_threshold, bu_div, flags, max_path;
     u32 seq;                       // launch sequence number (local barrier generation prefix)
     u32 watchdog_ms;
+    u32 fuse_path;                 // single rank, work of the leader CTA at the end of the search kernel: 0 nothing, 1 copy the result to h_out,
+                                   // 2 walk the parent chains first (no path kernel)
     u32 src, dst, query_in_ctrl;   // query by value, or (query_in_ctrl) read from Ctrl::q_src/q_dst
     u64 div_B;                     // 2^64 / B rounded up: owner(v) = umulhi64(div_B, v), exact for 32-bit v
     const u32* h_query;            // pinned host memory holding {src,dst}: read by the kernel itself (zero copy), or null
     u32* h_out;                    // pinned host buffer [Result | first path entries] written by the path kernel, or null
     u32 h_out_words;               // path entries that fit in h_out
+    u32* h_seq;                    // pinned word that receives K.seq after h_out is complete (host polls it), or null
     Layout L;
     char* arena[MAXR];             // base of every rank's arena as seen from this device
     const u64* row_ptr[MAXR];      // CSR shards of the hosted ranks (index = rank)

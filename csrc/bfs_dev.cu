@@ -77,6 +77,9 @@ __device__ u32 g_dbg_level;
 #define DBG_STAMP2(slot, dep) do { } while (0)
 #endif
 
+__device__ __noinline__ void path_body(const KParams& K);   // defined with the path kernel below
+__device__ __noinline__ void result_to_host(const KParams& K);
+
 namespace {
 
 constexpr u32 FULL = 0xffffffffu;
@@ -308,7 +311,7 @@ __device__ __noinline__ void write_result(const KParams& K, Ctrl* C, const Level
     R.path_len = 0;
     R.edges_scanned = G.edges_total;
     R.vertices_visited = G.visited_total;
-    R.t_end_ns = ptx::globaltimer_ns();
+    { const u64 dt = ptx::globaltimer_ns() - R.t_begin_ns; R.search_ns = dt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)dt; R.path_ns = 0; }
     C->xepoch = G.xepoch;
 }
 
@@ -1781,7 +1784,17 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
             alive = sync_grid(SYNC_LEVEL, PH_BU);
         }
     }
-    if (!alive) return;   // aborted: the host must reset the context
+    if (!alive) {         // aborted: the host must reset the context (it still gets the status word)
+        if (!MULTI && K.fuse_path && is_leader_cta) { __syncthreads(); result_to_host(K); }
+        return;
+    }
+
+    // ---- single rank: the leader CTA reconstructs the path right here (one launch per query instead of two)
+    if (!MULTI && K.fuse_path && is_leader_cta) {
+        __syncthreads();
+        if (K.fuse_path == 2u) path_body(K);
+        else result_to_host(K);
+    }
 
     // ---- cleanup for the next query: clear the visited bits this query set.  Every vertex a
     // single-rank search marked sits in a queue, so a small search clears exactly those words;
@@ -1805,11 +1818,13 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
 // (reference: v1/main-v1.cpp:86-97 walks on the host; v2/v4 re-run a whole serial BFS,
 //  v2/second_try.cpp:137-162, v4/mpi_bas.cpp:141-164)
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) {
+// whole CTA (any size >= 64 threads)
+__device__ __noinline__ void path_body(const KParams& K) {
     Ctrl* C = ctrl_of(K, K.rank_lo);
     Result& R = C->res;
     u32* hdr = reinterpret_cast<u32*>(K.arena[K.rank_lo] + K.L.off_path);   // [copy of Result | path]
     u32* path = hdr + PATH_HDR_WORDS;
+    const u64 t0 = ptx::globaltimer_ns();
     const bool ok = R.status == 0 && R.length >= 0 && (u32)R.length + 1u <= K.max_path;
     const u32 L = ok ? (u32)R.length : 0u;
     const u32 ds = R.depth_s;
@@ -1818,30 +1833,50 @@ __global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) 
         for (u32 pos = ds;; --pos) {
             path[pos] = cur;
             if (pos == 0 || cur >= K.n) break;
-            const u32 o = cur / K.B;
+            const u32 o = owner_of(K, cur);
             cur = __ldcg(parent_of(K, o, 0) + (cur - o * K.B));
         }
     } else if (ok && threadIdx.x == 32) {
         u32 cur = R.meet;
         for (u32 pos = ds; pos < L && cur < K.n; ++pos) {
-            const u32 o = cur / K.B;
+            const u32 o = owner_of(K, cur);
             cur = __ldcg(parent_of(K, o, 1) + (cur - o * K.B));
             path[pos + 1] = cur;
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0) R.path_len = ok ? L + 1u : 0u;
+    if (threadIdx.x == 0) {
+        R.path_len = ok ? L + 1u : 0u;
+        const u64 dt = ptx::globaltimer_ns() - t0;
+        R.path_ns = dt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)dt;
+    }
     __syncthreads();
     static_assert(sizeof(Result) == PATH_HDR_WORDS * 4, "result header size");
     if (threadIdx.x < PATH_HDR_WORDS) hdr[threadIdx.x] = reinterpret_cast<const u32*>(&R)[threadIdx.x];
     // short answers go straight to the caller's pinned buffer (posted PCIe writes): the host only waits for the stream
     if (K.h_out) {
+        __syncthreads();
         const u32 plen = ok ? L + 1u : 0u;
         const u32 words = PATH_HDR_WORDS + (plen <= K.h_out_words ? plen : 0u);
         for (u32 i = threadIdx.x; i < words; i += blockDim.x) K.h_out[i] = hdr[i];
         __threadfence_system();
+        if (K.h_seq) {               // completion word: the host may be polling it instead of waiting for the stream
+            __syncthreads();
+            if (threadIdx.x == 0) { *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq; __threadfence_system(); }
+        }
     }
 }
+
+// no path wanted: only the 64-byte result goes to the host (whole CTA)
+__device__ __noinline__ void result_to_host(const KParams& K) {
+    const Result& R = ctrl_of(K, K.rank_lo)->res;
+    if (!K.h_out) return;
+    if (threadIdx.x < PATH_HDR_WORDS) { K.h_out[threadIdx.x] = reinterpret_cast<const u32*>(&R)[threadIdx.x]; __threadfence_system(); }
+    __syncthreads();
+    if (threadIdx.x == 0 && K.h_seq) { *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq; __threadfence_system(); }
+}
+
+__global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) { path_body(K); }
 
 // ------------------------------------------------------------------------------------------
 // launch helpers used by ctx.cu

@@ -8,6 +8,7 @@
 // explicitly (v4 never calls cudaSetDevice); and the per-level host calls are gone —
 // bibfs_ctx_query enqueues the whole search.
 #include "bfs.h"
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -25,6 +26,9 @@ struct bibfs_ctx {
     u32 seq = 0;
     u32 cpr = 0;
     u32 cluster = 1;
+    bool last_fused = false;     // the last query wrote its result (and path) to h_stage from inside the search kernel
+    bool last_lean = false;      // ... and was launched without events (BIBFS_F_DEVICE_CLOCK)
+    u32* h_seq = nullptr;        // completion word inside h_stage
     bool multi = false;
     cudaEvent_t ev[3] = {};
     char* h_stage = nullptr;        // pinned: Result + path
@@ -105,6 +109,8 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
         bibfs_ctx_destroy(c);
         return fail("pinned staging allocation failed");
     }
+    memset(c->h_stage, 0, c->h_stage_bytes);
+    c->h_seq = reinterpret_cast<u32*>(c->h_stage + sizeof(Result) + (size_t)c->d.max_path * 4);   // in the 256-byte tail
     BIBFS_CUDA_TRY(cudaDeviceSynchronize());
     *out = c;
     return 0;
@@ -203,14 +209,24 @@ extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const u
     KParams K;
     fill_params(c, K, src, dst, false, flags);
     K.h_query = h_query_pinned;          // read by the kernel itself: pinned memory is device-visible under UVA
-    if (!(flags & BIBFS_F_NO_PATH)) { K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = HOST_PATH_WORDS; }
+    const bool want_path = !(flags & BIBFS_F_NO_PATH);
+    const bool single = !c->multi && c->d.vranks == 1;
+    if (want_path || single) { K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = HOST_PATH_WORDS; }
+    // one rank: the search kernel's leader CTA walks the parent chains itself and writes [result | path] into the
+    // pinned staging buffer, followed by a completion word: a query is ONE launch and the host need not wait for
+    // the stream to drain
+    c->last_lean = single && (flags & BIBFS_F_DEVICE_CLOCK);
+    c->last_fused = single && (want_path || c->last_lean);      // event-timed searches without a path: plain D2H copy of the result
+    K.fuse_path = c->last_fused ? (want_path ? 2u : 1u) : 0u;
+    K.h_seq = c->last_fused ? c->h_seq : nullptr;
     c->last_flags = flags;
-    BIBFS_CUDA_TRY(cudaEventRecord(c->ev[0], st));
+    if (!c->last_lean) BIBFS_CUDA_TRY(cudaEventRecord(c->ev[0], st));
     if (bfs_launch(K, c->multi, st)) return 1;
-    BIBFS_CUDA_TRY(cudaEventRecord(c->ev[1], st));
-    if (!(flags & BIBFS_F_NO_PATH))
+    if (!c->last_lean) BIBFS_CUDA_TRY(cudaEventRecord(c->ev[1], st));
+    if (want_path && !c->last_fused) {
         if (path_launch(K, st)) return 1;
-    BIBFS_CUDA_TRY(cudaEventRecord(c->ev[2], st));
+        BIBFS_CUDA_TRY(cudaEventRecord(c->ev[2], st));
+    }
     return 0;
 }
 
@@ -223,9 +239,30 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     const bool has_path = !(c->last_flags & BIBFS_F_NO_PATH);
     // with a path kernel the answer ([Result | first path entries]) was written into h_stage by the device itself
     const u32 first = has_path ? HOST_PATH_WORDS : 0u;
-    if (!has_path)
-        BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, st));
-    BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
+    if (c->last_fused) {
+        // the kernel itself wrote h_stage and then the completion word: poll that word (posted PCIe writes arrive in
+        // order) instead of waiting for the kernel to retire; look at the stream now and then in case it failed
+        volatile u32* seq = c->h_seq;
+        bool done = false;
+        if (c->last_lean) {
+            for (u32 spins = 0;; ++spins) {
+                if (*seq == c->seq) { done = true; break; }
+#if defined(__x86_64__) || defined(__i386__)
+                __builtin_ia32_pause();
+#endif
+                if ((spins & 4095u) == 4095u && cudaStreamQuery(st) != cudaErrorNotReady) break;
+            }
+            std::atomic_thread_fence(std::memory_order_acquire);
+        }
+        if (!done) {
+            BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
+            if (*seq != c->seq) return fail("the search kernel finished without delivering a result (aborted launch?)");
+        }
+    } else {
+        if (!has_path)
+            BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, st));
+        BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
+    }
     *res = bibfs_result();
     res->length = hr->length;
     res->meet = hr->meet;
@@ -238,8 +275,18 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     res->vertices_visited = hr->vertices_visited;
     res->path_len = 0;
     float a = 0, b = 0;
-    if (cudaEventElapsedTime(&a, c->ev[0], c->ev[1]) == cudaSuccess) res->search_ms = a;
-    if (cudaEventElapsedTime(&b, c->ev[1], c->ev[2]) == cudaSuccess) res->path_ms = b;
+    if (c->last_lean) {
+        res->search_ms = hr->search_ns * 1e-6;        // the device's own clock, launch latency not included
+        res->path_ms = hr->path_ns * 1e-6;
+    } else if (cudaEventElapsedTime(&a, c->ev[0], c->ev[1]) == cudaSuccess) res->search_ms = a;
+    if (c->last_lean) {
+    } else if (c->last_fused) {
+        // the path walk ran inside the search kernel: split the event time with the device's own clock
+        res->path_ms = hr->path_ns * 1e-6;
+        res->search_ms = a > res->path_ms ? a - res->path_ms : a;
+    } else if (has_path) {
+        if (cudaEventElapsedTime(&b, c->ev[1], c->ev[2]) == cudaSuccess) res->path_ms = b;
+    }
     cudaGetLastError();
     if (hr->status == 1) return fail("search aborted by the device watchdog (a rank did not arrive); reset the context");
     if (hr->status == 2) return fail("src/dst out of range (n=%u)", c->d.n);
@@ -265,8 +312,22 @@ extern "C" int bibfs_ctx_query_result(bibfs_ctx* c, uint32_t src, uint32_t dst, 
 extern "C" int bibfs_ctx_timing(bibfs_ctx* c, float* search_ms, float* path_ms) {
     if (!c) return fail("NULL ctx");
     DeviceGuard g(c->device);
-    if (search_ms) BIBFS_CUDA_TRY(cudaEventElapsedTime(search_ms, c->ev[0], c->ev[1]));
-    if (path_ms) BIBFS_CUDA_TRY(cudaEventElapsedTime(path_ms, c->ev[1], c->ev[2]));
+    float a = 0, b = 0;
+    if (c->last_lean) {
+        const Result* hr = reinterpret_cast<const Result*>(c->h_stage);
+        if (search_ms) *search_ms = hr->search_ns * 1e-6f;
+        if (path_ms) *path_ms = hr->path_ns * 1e-6f;
+        return 0;
+    }
+    BIBFS_CUDA_TRY(cudaEventElapsedTime(&a, c->ev[0], c->ev[1]));
+    if (c->last_fused) {
+        b = reinterpret_cast<const Result*>(c->h_stage)->path_ns * 1e-6f;
+        a = a > b ? a - b : a;
+    } else if (!(c->last_flags & BIBFS_F_NO_PATH)) {
+        BIBFS_CUDA_TRY(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
+    }
+    if (search_ms) *search_ms = a;
+    if (path_ms) *path_ms = b;
     return 0;
 }
 

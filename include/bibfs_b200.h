@@ -202,6 +202,8 @@ int bibfs_ctx_reset(bibfs_ctx* ctx, void* stream);
 #define BIBFS_F_FORCE_TD     4u   /* never go bottom-up                                     */
 #define BIBFS_F_FORCE_BU     8u   /* always go bottom-up                                    */
 #define BIBFS_F_NO_PATH     16u   /* skip the path kernel                                   */
+#define BIBFS_F_DEVICE_CLOCK 32u  /* one rank: no CUDA events around the launch; search_ms / path_ms come from the
+                                     device's own clock and completion is detected by polling the pinned result    */
 #define BIBFS_F_POLICY_V1   32u   /* reserved: side choice by vertex count (the default)    */
 
 /* Enqueue one query: (optional) H2D of the query from pinned host memory, the persistent

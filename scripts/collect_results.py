@@ -22,7 +22,7 @@ for cfg in configs:
         best = None
         for _ in range(3):
             flush.fill_(1)
-            r = solver.query(s, t)
+            r = solver.query(s, t, timing="events")
             assert r.length == L
             best = r if best is None or r.search_ms < best.search_ms else best
         ms.append(best.search_ms); pms.append(best.path_ms); lev.append(best.levels); edges.append(best.edges_scanned)
