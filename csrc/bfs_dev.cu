@@ -39,6 +39,7 @@
 // With P "virtual ranks" hosted by one launch (blockIdx.x / cpr = rank) the very same protocol
 // runs on a single GPU, which is how the multi-rank path is tested without 8 GPUs.
 #include "bfs.h"
+#include <type_traits>
 #include "ptx.cuh"
 
 namespace bibfs {
@@ -86,7 +87,7 @@ constexpr u32 FULL = 0xffffffffu;
 constexpr u32 BIG_ROW = 64;          // rows at least this long are strip-mined by the whole warp
 constexpr int UNR = 4;               // independent edges in flight per lane
 constexpr u32 WPC = BFS_THREADS / 32;
-constexpr u32 SOLO_CAP = 2048;       // entries of the shared-memory queue mirror per side
+constexpr u32 SOLO_CAP = 4096;       // entries of the shared-memory queue mirror per side (a cluster of 8 x 512 threads)
 constexpr u32 FILTER_MIN = 4096;
 constexpr u32 STAGE_CAP = 4096;      // grid mode: discoveries a CTA stages in shared memory before one queue reservation     // frontiers at least this large pre-check the visited word
 
@@ -139,6 +140,24 @@ __device__ __forceinline__ HubEntry* hub_of(const KParams& K, u32 r) {
 // private scratch word of the calling thread: where the branch-free claim code sends its no-op atomics
 __device__ __forceinline__ u64* dummy_of(const KParams& K, u32 r) {
     return reinterpret_cast<u64*>(K.arena[r] + K.L.off_dummy) + ((blockIdx.x * BFS_THREADS + threadIdx.x) % DUMMY_WORDS);
+}
+
+// Warp-aggregated reservation: every lane wants `c` consecutive slots; one atomic per warp on the cursor (returns the
+// lane's first slot).  ADD is called by the last lane with the warp total.  Used when a level is wide enough for the
+// 512 per-lane atomics on ONE shared-memory word to queue up.
+template <typename AddFn>
+__device__ __forceinline__ u32 warp_reserve(u32 c, AddFn add) {
+    const u32 lane = threadIdx.x & 31;
+    u32 incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 t = __shfl_up_sync(FULL, incl, d);
+        if (lane >= (u32)d) incl += t;
+    }
+    u32 base = 0;
+    if (lane == 31 && incl) base = add(incl);
+    base = __shfl_sync(FULL, base, 31);
+    return base + incl - c;
 }
 
 // rank that owns vertex v (v / B without the 20-instruction division)
@@ -1034,7 +1053,7 @@ struct SoloLevel {          // written by thread 0 at the end of a level, read b
     u32 nq;                 // size of the local window
     u32 tag;                // epoch tag for entries sent to other ranks in this level
     u32 rq_tag;             // tag carried by the entries of the sender-segment windows
-    u32 pad;
+    u32 slice;              // cluster tier: frontier vertices per CTA of the cluster (0: the leader CTA takes them all)
 };
 static_assert(sizeof(SoloLevel) == 32, "two LDS.128");
 
@@ -1087,6 +1106,7 @@ __device__ __noinline__ void solo_push_hub(const KParams& K, const Env& E, Smem&
 // 16-byte descriptor.  Nothing is published to the grid until it is needed.
 constexpr int SW = 8;       // adjacency entries per lane per round
 constexpr u32 SOLO_HUB_ROW = 128;   // solo mode packs the frontier into few warps: longer rows are shared by the CTA or the grid
+constexpr u32 CL_ENLIST_MIN = 192;   // cluster tier: smallest frontier that is dealt over the cluster
 constexpr u32 CL_CAP = 64;          // rows the CTA keeps for itself per level ...
 constexpr u32 CL_MAX_EDGES = 16384; // ... as long as they add up to no more than this many entries
 
@@ -1117,20 +1137,20 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
     auto make_level = [&](u32 sd) {
         SoloLevel lv;
         lv.total = st.local_front;
-        const bool enlist = !MULTI && sm.cl_n > 1 && lv.total > (u32)BFS_THREADS;   // bit 4: the cluster helpers take part
+        // bit 4: the other CTAs of the cluster take part.  One SM's load/store path is the limit of a wide level
+        // (measured: 2.6 us for <= 32 vertices, 3.7 us for 256, 5.5 us for 512 in ONE CTA), so the frontier is dealt
+        // evenly over the cluster as soon as that beats the ~1 us a cluster round costs
+        const bool enlist = !MULTI && sm.cl_n > 1 && lv.total > CL_ENLIST_MIN;
         lv.side_flags = sd | ((sd ? val1 : val0) ? 2u : 0u) | ((sd ? cur1 : cur0) ? 4u : 0u) | (enlist ? 16u : 0u);
         lv.q_lo = sd ? qlo1 : qlo0;
         lv.base_tail = sd ? qhi1 : qhi0;
         lv.nq = lv.base_tail - lv.q_lo;
         lv.tag = (u32)(st.xepoch + 1);
         lv.rq_tag = st.rq_tag[sd];
-        lv.pad = 0;
+        lv.slice = enlist ? min((u32)BFS_THREADS, max(64u, ((lv.total + sm.cl_n - 1u) / sm.cl_n + 31u) & ~31u)) : 0u;
         s_lv = lv;
         // a frontier larger than this CTA: the other CTAs of the cluster take the slices beyond the first
-        if (enlist) {
-            sm.cl_cmd = CL_HELP;
-            ptx::dsmem_st_release(ptx::smem_addr(&sm.cl_seq), sm.cl_seq + 1u);
-        }
+        if (enlist) { sm.cl_cmd = CL_HELP; ptx::dsmem_st_release(ptx::smem_addr(&sm.cl_seq), sm.cl_seq + 1u); }
     };
     if (MULTI && tid < 2 * MAXR) s_sent[tid / MAXR][tid % MAXR] = ptx::ld_relaxed_gpu(&E.C->sent[tid / MAXR][tid % MAXR]);
     if (tid == 0) { make_level(st.side); s_rnew = 0; s_cl_n = 0; s_cl_edges = 0; }
@@ -1145,11 +1165,15 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         u32* const out = sm.q[side][cur ^ 1u];
         const u32 sh = 32u * side, osh = 32u - sh;
         u32 nq = total, tag = 0, rq_tag = 0;
+        u32 mine = total;                       // frontier vertices of THIS CTA (the first slice in a cluster level)
         if (MULTI) {
             const uint4 raw2 = *(reinterpret_cast<const uint4*>(&s_lv) + 1);
             nq = raw2.x; tag = raw2.y; rq_tag = raw2.z;
             E.tag = tag;
+        } else if (cluster_level) {
+            mine = min(total, s_lv.slice);
         }
+        const bool wide = !MULTI && total > 64u;  // aggregate the cursor reservations per warp
         u32 u = 0;
         u64 r0 = 0, r1 = 0;
         if (MULTI && (warp + 1u) * 32u > nq && warp * 32u < total) {
@@ -1157,7 +1181,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             const u64* e = (tid >= nq && tid < total) ? rq_entry(K, E, st, side, tid - nq) : nullptr;
             u = fetch_rq(E, e, rq_tag);
         }
-        if (tid < total) {
+        if (tid < mine) {
             if (!MULTI || tid < nq) u = (raw.x & 2u) ? sm.q[side][cur][tid] : __ldcg(E.q[side] + raw.z + tid);
             r0 = __ldg(g_row + (u - g_lo));
             r1 = __ldg(g_row + (u - g_lo) + 1);
@@ -1174,43 +1198,47 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         u32 sdeg = deg < 32u ? deg : 0u;
         DBG_STAMP(2, sdeg);
         // rows shorter than a warp: each lane walks its own row, SW entries per round
-        for (u32 e0 = 0; __any_sync(FULL, e0 < sdeg); e0 += SW) {
-            u32 v[SW];
-            u64 old[SW];
+        // one round = W adjacency entries per lane; W = 4 when no row of the warp has more than 4 entries left (grids,
+        // most Erdos-Renyi rows): half the loads and claims of the 8-wide round, and one SM's load/store path is what
+        // limits a wide level
+        auto round = [&](auto Wc, const u32 e0) {
+            constexpr int W = decltype(Wc)::value;
+            u32 v[W];
+            u64 old[W];
             // branch-free issue: idle slots re-read the row's first entry and OR a zero into a private
-            // scratch word, so that all SW loads and then all SW claims are in flight together
+            // scratch word, so that all W loads and then all W claims are in flight together
 #pragma unroll
-            for (int k = 0; k < SW; ++k) v[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((e0 + k < sdeg) ? e0 + k : 0u));
+            for (int k = 0; k < W; ++k) v[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((e0 + k < sdeg) ? e0 + k : 0u));
 #pragma unroll
-            for (int k = 0; k < SW; ++k) {
+            for (int k = 0; k < W; ++k) {
                 const bool act = e0 + k < sdeg;
                 old[k] = ptx::atom_or_gpu(act ? &g_vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
             }
 #pragma unroll
-            for (int k = 0; k < SW; ++k)
+            for (int k = 0; k < W; ++k)
                 if (!(e0 + k < sdeg)) old[k] = ~0ull;
-            DBG_STAMP(3, v[0] + v[SW - 1]);
+            DBG_STAMP(3, v[0] + v[W - 1]);
             u32 newmask = 0, meetmask = 0, remmask = 0;
-            const u32 shz = sh + ptx::zero_after(old[SW - 1]);      // == sh; pins the tests behind the whole batch
+            const u32 shz = sh + ptx::zero_after(old[W - 1]);      // == sh; pins the tests behind the whole batch
 #pragma unroll
-            for (int k = 0; k < SW; ++k) {
+            for (int k = 0; k < W; ++k) {
                 const u32 isnew = ((u32)(old[k] >> ((v[k] & 31u) + shz)) & 1u) ^ 1u;
                 newmask |= isnew << k;
             }
             if (MULTI && __any_sync(FULL, newmask != 0)) {
                 // vertices of other ranks: the local bit was only a "not forwarded yet" filter — claim at the
                 // owner.  Branch-free again so that the NVLink round trips (1.6 us each) overlap.
-                u64 rold[SW];
+                u64 rold[W];
 #pragma unroll
-                for (int k = 0; k < SW; ++k) {
+                for (int k = 0; k < W; ++k) {
                     const bool rem = ((newmask >> k) & 1u) && (v[k] - g_lo) >= K.B;
                     remmask |= rem ? (1u << k) : 0u;
                     u64* const addr = rem ? (vis_of(K, owner_of(K, v[k])) + (v[k] >> 5)) : dummy;
                     rold[k] = ptx::atom_or_sys(addr, rem ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
                 }
-                const u32 shr = sh + ptx::zero_after(rold[SW - 1]);
+                const u32 shr = sh + ptx::zero_after(rold[W - 1]);
 #pragma unroll
-                for (int k = 0; k < SW; ++k) {
+                for (int k = 0; k < W; ++k) {
                     if ((remmask >> k) & 1u) {
                         old[k] = rold[k];
                         if ((rold[k] >> ((v[k] & 31u) + shr)) & 1ull) { newmask &= ~(1u << k); remmask &= ~(1u << k); }
@@ -1218,16 +1246,18 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
                 }
             }
 #pragma unroll
-            for (int k = 0; k < SW; ++k)
+            for (int k = 0; k < W; ++k)
                 meetmask |= (((newmask >> k) & 1u) & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
             DBG_STAMP(4, newmask);
             const u32 locmask = newmask & ~remmask;
+            u32 wslot = 0;
+            if (wide) wslot = warp_reserve((u32)__popc(locmask), [&](u32 n) { return ptx::atoms_add(&sm.acc.q_tail[side], n); });
             if (locmask) {
-                u32 slot = ptx::atoms_add(&sm.acc.q_tail[side], (u32)__popc(locmask));
+                u32 slot = wide ? wslot : ptx::atoms_add(&sm.acc.q_tail[side], (u32)__popc(locmask));
                 u32* const qs = E.q[side];
                 u32* const ps = E.parent[side];
 #pragma unroll
-                for (int k = 0; k < SW; ++k) {
+                for (int k = 0; k < W; ++k) {
                     if ((locmask >> k) & 1u) {
                         qs[slot] = v[k];
                         ps[v[k] - g_lo] = u;
@@ -1239,7 +1269,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             }
             if (MULTI && remmask) {
 #pragma unroll
-                for (int k = 0; k < SW; ++k) {
+                for (int k = 0; k < W; ++k) {
                     if ((remmask >> k) & 1u) {
                         const u32 dest = owner_of(K, v[k]);
                         const u32 slot = ptx::atoms_add(&s_sent[side][dest], 1u);
@@ -1251,9 +1281,15 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
             }
             if (meetmask) {
 #pragma unroll
-                for (int k = 0; k < SW; ++k)
+                for (int k = 0; k < W; ++k)
                     if ((meetmask >> k) & 1u) ptx::reds_min(&sm.acc.meet_local, v[k]);
             }
+                };
+        for (u32 e0 = 0;;) {
+            const u32 left = __reduce_max_sync(FULL, sdeg > e0 ? sdeg - e0 : 0u);
+            if (left == 0) break;
+            if (left <= 4u) { round(std::integral_constant<int, 4>{}, e0); e0 += 4; }
+            else { round(std::integral_constant<int, SW>{}, e0); e0 += SW; }
         }
         DBG_STAMP(5, sdeg);
         // rows of a warp's length or more (below the hub threshold): the warp walks them together
@@ -1429,32 +1465,29 @@ __device__ __noinline__ void cluster_helper(const KParams& K, const Env& E, Smem
     __shared__ u32 s_cmd, s_seq;
     __shared__ __align__(16) SoloLevel s_lvc;
     // leader-side addresses (same layout in every CTA of the kernel)
-    const u32 a_seq = ptx::dsmem_map(ptx::smem_addr(&sm.cl_seq), 0), a_cmd = ptx::dsmem_map(ptx::smem_addr(&sm.cl_cmd), 0);
-    const u32 a_lv = ptx::dsmem_map(ptx::smem_addr(&sm.lv), 0);
     const u32 a_hub = ptx::dsmem_map(ptx::smem_addr(&sm.hub), 0);
     const u32 a_meet = ptx::dsmem_map(ptx::smem_addr(&sm.acc.meet_local), 0);
     const u32 a_edges = ptx::dsmem_map(ptx::smem_addr(&sm.acc.edges), 0);
     while (true) {
         if (tid < 32) {
-            // warp-collective poll (see wait_gen): lane 0 reads the leader's sequence word, all lanes leave together
+            // warp-collective poll (see wait_gen): lane 0 reads the leader's sequence word over DSMEM, all lanes leave together.
+            // (Measured alternative: the leader PUSHING descriptor + command into an inbox in each helper's own shared memory,
+            //  polled locally - 9 % slower on the 4096 grid and 5 % on er100k; the helpers' tight local polling and the extra
+            //  stores in the leader's loop cost more than the three DSMEM round trips they save.)
             u32 v = seen_seq, spins = 0;
             bool dead = false;
+            const u32 a_seq = ptx::dsmem_map(ptx::smem_addr(&sm.cl_seq), 0), a_cmd = ptx::dsmem_map(ptx::smem_addr(&sm.cl_cmd), 0);
+            const u32 a_lv = ptx::dsmem_map(ptx::smem_addr(&sm.lv), 0);
             while (true) {
                 if (lane == 0) v = ptx::dsmem_ld(a_seq);
                 v = __shfl_sync(FULL, v, 0);
                 if (v != seen_seq) break;
-                // back off: every poll is a request to the LEADER's shared-memory port, which it needs itself
                 ptx::nanosleep(96);
                 if (++spins > 4096u && (spins & 1023u) == 0 && expired_warp(E.C, deadline)) { dead = true; break; }
             }
-            if (lane == 0) {
-                v = ptx::dsmem_ld_acquire(a_seq);
-                s_seq = v;
-                s_cmd = dead ? (u32)CL_EXIT : ptx::dsmem_ld(a_cmd);
-            }
+            if (lane == 0) { v = ptx::dsmem_ld_acquire(a_seq); s_seq = v; s_cmd = dead ? (u32)CL_EXIT : ptx::dsmem_ld(a_cmd); }
             __syncwarp();
-            if (!dead && s_cmd == CL_HELP && lane < sizeof(SoloLevel) / 4)
-                reinterpret_cast<u32*>(&s_lvc)[lane] = ptx::dsmem_ld(a_lv + 4 * lane);
+            if (!dead && s_cmd == CL_HELP && lane < sizeof(SoloLevel) / 4) reinterpret_cast<u32*>(&s_lvc)[lane] = ptx::dsmem_ld(a_lv + 4 * lane);
         }
         __syncthreads();
         seen_seq = s_seq;
@@ -1462,7 +1495,8 @@ __device__ __noinline__ void cluster_helper(const KParams& K, const Env& E, Smem
         const u32 side = s_lvc.side_flags & 1u, cur = (s_lvc.side_flags >> 2) & 1u;
         const u32 total = s_lvc.total, base_tail = s_lvc.base_tail;
         const u32 sh = 32u * side, osh = 32u - sh;
-        const u32 i = cl_rank * (u32)BFS_THREADS + tid;
+        const u32 slice = s_lvc.slice;
+        const u32 i = tid < slice ? cl_rank * slice + tid : 0xFFFFFFFFu;
         const u32 a_tail = ptx::dsmem_map(ptx::smem_addr(&sm.acc.q_tail[side]), 0);
         const u32 a_out = ptx::dsmem_map(ptx::smem_addr(&sm.q[side][cur ^ 1u][0]), 0);
         u32 u = 0;
@@ -1488,28 +1522,30 @@ __device__ __noinline__ void cluster_helper(const KParams& K, const Env& E, Smem
             deg = 0;
         }
         u64* const dummy = dummy_of(K, E.me);
-        for (u32 e0 = 0; __any_sync(FULL, e0 < deg); e0 += SW) {
-            u32 v[SW];
-            u64 old[SW];
+        auto round = [&](auto Wc, const u32 e0) {
+            constexpr int W = decltype(Wc)::value;
+            u32 v[W];
+            u64 old[W];
 #pragma unroll
-            for (int k = 0; k < SW; ++k) v[k] = ptx::ld_relaxed_gpu(E.col + r0 + ((e0 + k < deg) ? e0 + k : 0u));
+            for (int k = 0; k < W; ++k) v[k] = ptx::ld_relaxed_gpu(E.col + r0 + ((e0 + k < deg) ? e0 + k : 0u));
 #pragma unroll
-            for (int k = 0; k < SW; ++k) {
+            for (int k = 0; k < W; ++k) {
                 const bool act = e0 + k < deg;
                 old[k] = ptx::atom_or_gpu(act ? &E.vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
             }
             u32 newmask = 0, meetmask = 0;
-            const u32 shz = sh + ptx::zero_after(old[SW - 1]);
+            const u32 shz = sh + ptx::zero_after(old[W - 1]);
 #pragma unroll
-            for (int k = 0; k < SW; ++k) {
+            for (int k = 0; k < W; ++k) {
                 const u32 isnew = (e0 + k < deg) ? (((u32)(old[k] >> ((v[k] & 31u) + shz)) & 1u) ^ 1u) : 0u;
                 newmask |= isnew << k;
                 meetmask |= (isnew & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
             }
+            // the leader's queue cursor: one DSMEM atomic per warp
+            u32 slot = warp_reserve((u32)__popc(newmask), [&](u32 n) { return ptx::dsmem_atom_add(a_tail, n); });
             if (newmask) {
-                u32 slot = ptx::dsmem_atom_add(a_tail, (u32)__popc(newmask));     // the leader's queue cursor
 #pragma unroll
-                for (int k = 0; k < SW; ++k) {
+                for (int k = 0; k < W; ++k) {
                     if ((newmask >> k) & 1u) {
                         E.q[side][slot] = v[k];
                         E.parent[side][v[k] - E.lo] = u;
@@ -1520,10 +1556,16 @@ __device__ __noinline__ void cluster_helper(const KParams& K, const Env& E, Smem
                 }
                 if (meetmask) {
 #pragma unroll
-                    for (int k = 0; k < SW; ++k)
+                    for (int k = 0; k < W; ++k)
                         if ((meetmask >> k) & 1u) ptx::dsmem_red_min(a_meet, v[k]);
                 }
             }
+                };
+        for (u32 e0 = 0;;) {
+            const u32 left = __reduce_max_sync(FULL, deg > e0 ? deg - e0 : 0u);
+            if (left == 0) break;
+            if (left <= 4u) { round(std::integral_constant<int, 4>{}, e0); e0 += 4; }
+            else { round(std::integral_constant<int, SW>{}, e0); e0 += SW; }
         }
         {
             const u32 wsum = __reduce_add_sync(FULL, nedges);

@@ -81,14 +81,21 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     if (desc->max_ctas && desc->max_ctas < per_rank) per_rank = desc->max_ctas;
     if (per_rank < 1) { delete c; return fail("not enough SMs for %u hosted ranks", desc->vranks); }
     c->cpr = per_rank;
-    // single rank: launch in clusters of 4 so that the leader CTA can enlist three neighbours over DSMEM
-    // (frontiers up to 2048 vertices stay off the grid-wide barrier)
+    // single rank: launch in thread-block clusters (8, else 4) so that the leader CTA can enlist its neighbours over
+    // DSMEM: frontiers up to cluster x 512 vertices stay off the grid-wide barrier.  BIBFS_CLUSTER=n overrides.
     if (!c->multi && desc->vranks == 1 && per_rank >= 8 && !getenv("BIBFS_NO_CLUSTER")) {
-        int fit = 0;
-        if (bfs_max_ctas_clustered(4, &fit) == 0 && fit >= 8) {
-            c->cluster = 4;
-            c->cpr = (per_rank < (u32)fit ? per_rank : (u32)fit) / 4 * 4;
-            if (c->d.solo_threshold == (u32)BFS_THREADS) c->d.solo_threshold = 4 * BFS_THREADS;
+        const char* want = getenv("BIBFS_CLUSTER");
+        const u32 first = want ? (u32)atoi(want) : 8u;
+        for (u32 cl = first; cl >= 2; cl /= 2) {
+            if (cl > 8 || (cl & (cl - 1))) continue;
+            int fit = 0;
+            if (bfs_max_ctas_clustered(cl, &fit) == 0 && fit >= (int)(2 * cl)) {
+                c->cluster = cl;
+                c->cpr = (per_rank < (u32)fit ? per_rank : (u32)fit) / cl * cl;
+                if (c->d.solo_threshold == (u32)BFS_THREADS) c->d.solo_threshold = cl * BFS_THREADS;
+                break;
+            }
+            cudaGetLastError();
         }
         cudaGetLastError();
     }

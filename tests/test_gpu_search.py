@@ -128,6 +128,34 @@ def test_pinned_query_input(bb):
     solver.close()
 
 
+def test_timing_modes_agree(bb):
+    """timing="device" (no events, pinned completion word) and timing="events" return the same answer; both report
+    a positive search time; long paths (beyond the pinned staging window) are fetched from the device buffer."""
+    spec = bb.grid_spec(40, 40)          # corner to corner: 78 hops
+    g = bb.Graph.generate(spec, device="cuda:0")
+    g_cpu = g.to("cpu")
+    solver = bb.GpuSolver(g)
+    for s, t in [(0, spec.n - 1), (5, 5), (3, 777), (spec.n - 1, 0)]:
+        a = solver.query(s, t, timing="device")
+        b = solver.query(s, t, timing="events")
+        c = solver.query(s, t, want_path=False, timing="device")
+        d = solver.query(s, t, want_path=False, timing="events")
+        assert a.length == b.length == c.length == d.length
+        assert a.path == b.path and c.path is None and d.path is None
+        bb.validate_path(g_cpu, s, t, a.path, a.length)
+        if s != t:
+            assert a.search_ms > 0 and b.search_ms > 0 and c.search_ms > 0 and d.search_ms > 0
+            assert a.edges_scanned == b.edges_scanned > 0
+    solver.close()
+    big = bb.grid_spec(400, 2)           # 401-hop path: longer than the 240-entry pinned window
+    gb = bb.Graph.generate(big, device="cuda:0")
+    sb = bb.GpuSolver(gb)
+    r = sb.query(0, big.n - 1)
+    assert r.length is not None and len(r.path) == r.length + 1
+    bb.validate_path(gb.to("cpu"), 0, big.n - 1, r.path, r.length)
+    sb.close()
+
+
 def test_out_of_range_query_is_an_error(bb):
     solver = bb.GpuSolver(bb.Graph.generate(bb.grid_spec(8, 8), device="cuda:0"))
     with pytest.raises(bb.BibfsError):
