@@ -881,19 +881,31 @@ struct HubChunk {
     bool valid;
 };
 
+// whole warp, same c in every lane.  The entries are ordered by chunk_base (slot and base come from one atomic): a
+// 32-ary search, one load per step (18 entries: ONE step where a binary search takes five dependent L2 round trips),
+// then the 32-byte entry is fetched by eight lanes at once.
 __device__ __forceinline__ HubChunk hub_lookup(const HubEntry* H, u32 ne, const u32* col, u32 c) {
+    const u32 lane = threadIdx.x & 31;
     HubChunk h;
-    // entries are ordered by chunk_base (slot and base come from one atomic): binary search
-    u32 lo = 0, hi = ne;
-    while (hi - lo > 1) {
-        const u32 mid = (lo + hi) >> 1;
-        if (__ldcg(&H[mid].chunk_base) <= c) lo = mid; else hi = mid;
+    u32 lo = 0, n = ne;
+    while (n > 1) {
+        const u32 step = (n + 31u) / 32u;
+        const u32 idx = lo + lane * step;
+        const u64 b = (lane * step < n) ? __ldcg(&H[idx].chunk_base) : ~0ull;
+        const u32 m = __ballot_sync(FULL, b <= (u64)c) | 1u;
+        const u32 k = 31u - (u32)__clz(m);
+        const u32 rest = n - k * step;
+        lo += k * step;
+        n = rest < step ? rest : step;
     }
-    const u64 base = __ldcg(&H[lo].chunk_base);
-    const u32 nch = __ldcg(&H[lo].nchunks);
+    static_assert(sizeof(HubEntry) == 32, "eight words");
+    const u32 w = (lane < 8 && ne) ? __ldcg(reinterpret_cast<const u32*>(&H[lo]) + lane) : 0u;
+    h.uu = __shfl_sync(FULL, w, 0);
+    const u32 nch = __shfl_sync(FULL, w, 1);
+    const u64 r0 = (u64)__shfl_sync(FULL, w, 2) | ((u64)__shfl_sync(FULL, w, 3) << 32);
+    const u64 r1 = (u64)__shfl_sync(FULL, w, 4) | ((u64)__shfl_sync(FULL, w, 5) << 32);
+    const u64 base = (u64)__shfl_sync(FULL, w, 6) | ((u64)__shfl_sync(FULL, w, 7) << 32);
     h.valid = ne != 0 && (c - base) < nch;          // false: chunk of an entry that did not fit in the list
-    const u64 r0 = __ldcg(&H[lo].r0), r1 = __ldcg(&H[lo].r1);
-    h.uu = __ldcg(&H[lo].u);
     const u64 A = (r0 & ~3ull) + (u64)(c - base) * HUB_CHUNK;     // 16-byte aligned
     const u64 Aend = min(A + HUB_CHUNK, r1);
     h.lo = (u32)(max(A, r0) - A);
@@ -914,8 +926,9 @@ __device__ __noinline__ void expand_hubs(const KParams& K, const Env& E0, const 
     E.smem_src = true;
     u32 cnt = 0;
     u32 c = warp_gid;
-    HubChunk cur = hub_lookup(H, ne, E.col, c < st.hub_chunks ? c : 0);
-    cur.valid = cur.valid && c < st.hub_chunks;
+    HubChunk cur;
+    cur.valid = false;
+    if (c < st.hub_chunks) cur = hub_lookup(H, ne, E.col, c);
     if (lane == 0 && cur.valid) { ptx::mbar_expect_tx(&bars[0], cur.bytes); ptx::bulk_g2s(stage, cur.src, cur.bytes, &bars[0]); }
     for (u32 i = 0; c < st.hub_chunks; c += nwarps, ++i) {
         const u32 buf = i & 1u;
@@ -926,8 +939,9 @@ __device__ __noinline__ void expand_hubs(const KParams& K, const Env& E0, const 
         }
         // start the copy of this warp's next chunk into the other buffer
         const u32 cn = c + nwarps;
-        HubChunk nxt = hub_lookup(H, ne, E.col, cn < st.hub_chunks ? cn : 0);
-        nxt.valid = nxt.valid && cn < st.hub_chunks;
+        HubChunk nxt;
+        nxt.valid = false;
+        if (cn < st.hub_chunks) nxt = hub_lookup(H, ne, E.col, cn);
         if (lane == 0 && nxt.valid) {
             ptx::fence_proxy_async();       // this buffer was read through the generic proxy two iterations ago
             ptx::mbar_expect_tx(&bars[buf ^ 1u], nxt.bytes);
@@ -1976,6 +1990,8 @@ int bfs_max_ctas_clustered(u32 cluster, int* out) {
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
     int n = 0;
+    if (cluster > 8)      // beyond the portable limit: opt in (B200 schedules 16-CTA clusters inside one GPC)
+        BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     BIBFS_CUDA_TRY(cudaOccupancyMaxActiveClusters(&n, k_bibfs<false>, &cfg));
     *out = n * (int)cluster;
     return 0;

@@ -81,13 +81,13 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     if (desc->max_ctas && desc->max_ctas < per_rank) per_rank = desc->max_ctas;
     if (per_rank < 1) { delete c; return fail("not enough SMs for %u hosted ranks", desc->vranks); }
     c->cpr = per_rank;
-    // single rank: launch in thread-block clusters (8, else 4) so that the leader CTA can enlist its neighbours over
+    // single rank: launch in thread-block clusters (16 - beyond the portable 8, B200 takes it - else 8, 4, 2) so that the leader CTA can enlist its neighbours over
     // DSMEM: frontiers up to cluster x 512 vertices stay off the grid-wide barrier.  BIBFS_CLUSTER=n overrides.
     if (!c->multi && desc->vranks == 1 && per_rank >= 8 && !getenv("BIBFS_NO_CLUSTER")) {
         const char* want = getenv("BIBFS_CLUSTER");
-        const u32 first = want ? (u32)atoi(want) : 8u;
+        const u32 first = want ? (u32)atoi(want) : 16u;
         for (u32 cl = first; cl >= 2; cl /= 2) {
-            if (cl > 8 || (cl & (cl - 1))) continue;
+            if (cl > 16 || (cl & (cl - 1))) continue;
             int fit = 0;
             if (bfs_max_ctas_clustered(cl, &fit) == 0 && fit >= (int)(2 * cl)) {
                 c->cluster = cl;
