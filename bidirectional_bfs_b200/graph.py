@@ -85,6 +85,37 @@ class Graph:
         return Graph._build(int(spec.n), None, spec, device, nranks, ranks, sort_rows, name)
 
     # ---- views ---------------------------------------------------------------------------
+    # ---- cached partitioned CSR (the nearest thing to a checkpoint - big graphs need not be rebuilt) ----
+    def save_csr(self, path) -> None:
+        """Write the hosted shards to ``path`` (one uncompressed .npz: n, nranks, ranks and row_ptr / col per shard).
+        In the one-process-per-GPU mode every rank saves its own file (e.g. ``f"graph.{rank}.npz"``)."""
+        arrs = {"n": np.int64(self.n), "nranks": np.int64(self.nranks), "m_records": np.int64(self.m_records),
+                "ranks": np.array(sorted(self.shards), dtype=np.int64)}
+        for r, sh in self.shards.items():
+            arrs[f"row_ptr_{r}"] = sh.row_ptr.cpu().numpy()
+            arrs[f"col_{r}"] = sh.col.cpu().numpy()                               # (the device-side padding is not part of the view)
+        with open(path, "wb") as f:
+            np.savez(f, **arrs)
+
+    @staticmethod
+    def load_csr(path, device="cpu", ranks=None) -> "Graph":
+        """Read a file written by :meth:`save_csr`; ``ranks`` selects a subset of the stored shards."""
+        dev = torch.device(device)
+        with np.load(path) as z:
+            n, nranks = int(z["n"]), int(z["nranks"])
+            part = Partition(n, nranks)
+            g = Graph(n=n, nranks=nranks, device=dev, m_records=int(z["m_records"]), name=str(path))
+            for r in (int(x) for x in z["ranks"]):
+                if ranks is not None and r not in ranks:
+                    continue
+                lo, hi = part.range(r)
+                rp = torch.from_numpy(z[f"row_ptr_{r}"]).to(dev)
+                col = torch.from_numpy(z[f"col_{r}"])
+                g.shards[r] = Shard(r, lo, hi, rp, padded_col(col, dev) if dev.type == "cuda" else col.to(dev))
+        if not g.shards:
+            raise ValueError(f"{path}: none of the requested ranks {ranks} is stored in the file")
+        return g
+
     @property
     def partition(self) -> Partition:
         return Partition(self.n, self.nranks)

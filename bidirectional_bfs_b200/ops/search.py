@@ -7,6 +7,7 @@ v4 C API (v4/comp.h:8-36), minus the per-level host calls.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 
 import numpy as np
@@ -46,6 +47,9 @@ def result_from_c(src, dst, r: Result, path_buf, variant) -> PathResult:
                       int(r.meet) if found else None, int(r.levels), int(r.levels_bottom_up),
                       int(r.depth_s), int(r.depth_t), int(r.edges_scanned), int(r.vertices_visited),
                       float(r.search_ms), float(r.path_ms), variant)
+
+
+_NVTX = bool(os.environ.get("BIBFS_NVTX"))
 
 
 class SearchContext:
@@ -108,6 +112,12 @@ class SearchContext:
         return result_from_c(src, dst, r, self._path, variant)
 
     def query(self, src, dst, flags=0, want_path=True, pinned_query=None, variant="gpu") -> PathResult:
+        if _NVTX:       # BIBFS_NVTX=1: NVTX range per query for nsys timelines
+            with torch.cuda.nvtx.range(f"bibfs.query {src}->{dst}"):
+                return self._query(src, dst, flags, want_path, pinned_query, variant)
+        return self._query(src, dst, flags, want_path, pinned_query, variant)
+
+    def _query(self, src, dst, flags, want_path, pinned_query, variant) -> PathResult:
         r = Result()
         q = pinned_query.data_ptr() if pinned_query is not None else None
         check(lib().bibfs_ctx_query_result(self._h, int(src), int(dst), q, flags, C.byref(r),

@@ -75,3 +75,21 @@ def test_dense_legacy(bb, tmp_path):
     assert np.array_equal(bb.io.read_dense(p), a)
     with pytest.raises(bb.BibfsError):
         bb.io.read_dense(tmp_path / "nope.bin")
+
+
+def test_csr_cache_roundtrip(bb, tmp_path):
+    """Graph.save_csr / load_csr: the cached partitioned CSR gives back the same shards."""
+    import numpy as np
+    spec = bb.er_spec(3000, 3.0 / 3000, seed=5)
+    g = bb.Graph.generate(spec, nranks=4)
+    p = tmp_path / "g.npz"
+    g.save_csr(p)
+    h = bb.Graph.load_csr(p)
+    assert (h.n, h.nranks, sorted(h.shards)) == (g.n, 4, [0, 1, 2, 3])
+    for r in range(4):
+        assert np.array_equal(h.shards[r].row_ptr.numpy(), g.shards[r].row_ptr.numpy())
+        assert np.array_equal(h.shards[r].col.numpy(), g.shards[r].col.numpy())
+    one = bb.Graph.load_csr(p, ranks=[2])
+    assert list(one.shards) == [2]
+    s, t = 0, spec.n - 1
+    assert bb.bibfs(h, s, t, variant="cpu-ranks").length == bb.bibfs(g, s, t, variant="serial").length
