@@ -1203,7 +1203,9 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         u32 deg = (u32)min(r1 - r0, (u64)0xFFFFFFFFu);
         DBG_STAMP(1, deg);
         const u32 nedges = deg;                      // statistics: hub rows count as inspected here
-        if (deg >= SOLO_HUB_ROW) {
+        // a small frontier sits in a warp or two: there even a 32-entry row is better dealt over all 16 warps (CTA list)
+        // than walked by its warp, row after row at ~0.6 us each
+        if (deg >= (total <= 64u ? 32u : SOLO_HUB_ROW)) {
             const u32 slot = deg < HUB_ROW * 8u ? ptx::atoms_add(&s_cl_n, 1u) : CL_CAP;
             if (slot < CL_CAP) { s_cl_u[slot] = u; s_cl_r0[slot] = r0; s_cl_r1[slot] = r1; ptx::reds_add(&s_cl_edges, deg); }
             else solo_push_hub(K, E, sm, u, r0, r1);          // very long row, or the CTA list is full: whole grid
