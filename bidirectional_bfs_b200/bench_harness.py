@@ -56,7 +56,8 @@ def run(graph_paths, variants, repeats=5, ranks=4, outdir=".", device="cuda:0", 
                 solver = bb.make_solver(g, variant)
                 ngpu = 1
             build_ms = (time.perf_counter() - t0) * 1e3
-            res = [solver.query(0, n - 1) for _ in range(repeats)]
+            kw = {"timing": "events"} if variant in ("gpu", "multi-gpu") else {}       # cudaEvent-timed like the reference's v3
+            res = [solver.query(0, n - 1, **kw) for _ in range(repeats)]
             r = res[-1]
             sm = statistics.median(x.search_ms for x in res)
             pm = statistics.median(x.path_ms for x in res)
