@@ -972,6 +972,7 @@ __device__ __noinline__ void expand_hubs(const KParams& K, const Env& E0, const 
 // bottom-up level: every unvisited owned vertex looks for a parent in the frontier bitmap.
 // Short rows are scanned by their lane, long rows by the whole warp (ballot = early exit).
 // ------------------------------------------------------------------------------------------
+constexpr int BU_W = 8;      // adjacency entries a lane has in flight in the bottom-up scans
 template <bool MULTI>
 __device__ __noinline__ void expand_bu(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps) {
     const u32 lane = threadIdx.x & 31;
@@ -993,10 +994,21 @@ __device__ __noinline__ void expand_bu(const KParams& K, const Env& E, const Lev
         if (unvis) { r0 = __ldg(E.row_ptr + (v - E.lo)); r1 = __ldg(E.row_ptr + (v - E.lo) + 1); }
         const u64 deg = r1 - r0;
         if (unvis && deg < BIG_ROW) {
-            for (u64 e = r0; e < r1; ++e) {
-                const u32 u = __ldg(E.col + e);
-                ++edges;
-                if ((fcur[u >> 5] >> (u & 31u)) & 1u) { found = true; par = u; break; }
+            // BU_W entries per step: the column loads and then the bitmap loads of a step are independent, so BU_W
+            // L2 / DRAM round trips overlap where the one-entry loop had them back to back (the first hit still wins)
+            for (u64 e = r0; e < r1 && !found; e += BU_W) {
+                u32 u[BU_W], w[BU_W];
+#pragma unroll
+                for (int k = 0; k < BU_W; ++k) u[k] = __ldg(E.col + (e + k < r1 ? e + k : r0));
+#pragma unroll
+                for (int k = 0; k < BU_W; ++k) w[k] = fcur[u[k] >> 5];
+#pragma unroll
+                for (int k = 0; k < BU_W; ++k) {
+                    if (!found && e + k < r1) {
+                        ++edges;
+                        if ((w[k] >> (u[k] & 31u)) & 1u) { found = true; par = u[k]; }
+                    }
+                }
             }
         }
         u32 big = __ballot_sync(FULL, unvis && deg >= BIG_ROW);
@@ -1005,13 +1017,20 @@ __device__ __noinline__ void expand_bu(const KParams& K, const Env& E, const Lev
             big &= big - 1;
             const u64 b = __shfl_sync(FULL, r0, sl), e = __shfl_sync(FULL, r1, sl);
             u32 hitpar = NO_V;
-            for (u64 p = b; p < e; p += 32) {
-                const u64 idx = p + lane;
-                u32 u = 0;
-                bool hit = false;
-                if (idx < e) { u = __ldg(E.col + idx); ++edges; hit = (fcur[u >> 5] >> (u & 31u)) & 1u; }
-                const u32 hm = __ballot_sync(FULL, hit);
-                if (hm) { hitpar = __shfl_sync(FULL, u, __ffs(hm) - 1); break; }
+            // 32 x BU_W entries per step (BU_W per lane, loads of a step independent of one another)
+            for (u64 p = b; p < e && hitpar == NO_V; p += 32u * BU_W) {
+                u32 u[BU_W], w[BU_W];
+#pragma unroll
+                for (int k = 0; k < BU_W; ++k) { const u64 idx = p + 32u * k + lane; u[k] = __ldg(E.col + (idx < e ? idx : b)); }
+#pragma unroll
+                for (int k = 0; k < BU_W; ++k) w[k] = fcur[u[k] >> 5];
+#pragma unroll
+                for (int k = 0; k < BU_W; ++k) {
+                    const bool in = p + 32u * k + lane < e;
+                    if (in && hitpar == NO_V) ++edges;
+                    const u32 hm = __ballot_sync(FULL, in && ((w[k] >> (u[k] & 31u)) & 1u));
+                    if (hm && hitpar == NO_V) hitpar = __shfl_sync(FULL, u[k], __ffs(hm) - 1);
+                }
             }
             if (lane == sl && hitpar != NO_V) { found = true; par = hitpar; }
         }
