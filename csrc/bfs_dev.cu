@@ -1185,6 +1185,18 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
         // a frontier larger than this CTA: the other CTAs of the cluster take the slices beyond the first
         if (enlist) { sm.cl_cmd = CL_HELP; ptx::dsmem_st_release(ptx::smem_addr(&sm.cl_seq), sm.cl_seq + 1u); }
     };
+    // MULTI: per-peer base pointers, looked up with one shared-memory load per remote claim / entry (computing them from
+    // the kernel parameters costs ~25 instructions per remote discovery)
+    __shared__ u64* s_pvis[MAXR];            // peer's visited words
+    __shared__ u64* s_prq[2][MAXR];          // this rank's segment in the peer's arena, per side
+    __shared__ u32* s_ppar[2][MAXR];         // peer's parent array per side, biased so that it is indexed by the global vertex id
+    if (MULTI && tid < K.P) {
+        s_pvis[tid] = vis_of(K, tid);
+        for (u32 sd = 0; sd < 2; ++sd) {
+            s_prq[sd][tid] = rq_of(K, tid, sd, E.me);
+            s_ppar[sd][tid] = parent_of(K, tid, sd) - (size_t)tid * K.B;
+        }
+    }
     if (MULTI && tid < 2 * MAXR) s_sent[tid / MAXR][tid % MAXR] = ptx::ld_relaxed_gpu(&E.C->sent[tid / MAXR][tid % MAXR]);
     if (tid == 0) { make_level(st.side); s_rnew = 0; s_cl_n = 0; s_cl_edges = 0; }
     __syncthreads();
@@ -1268,7 +1280,7 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
                 for (int k = 0; k < W; ++k) {
                     const bool rem = ((newmask >> k) & 1u) && (v[k] - g_lo) >= K.B;
                     remmask |= rem ? (1u << k) : 0u;
-                    u64* const addr = rem ? (vis_of(K, owner_of(K, v[k])) + (v[k] >> 5)) : dummy;
+                    u64* const addr = rem ? (s_pvis[owner_of(K, v[k])] + (v[k] >> 5)) : dummy;
                     rold[k] = ptx::atom_or_sys(addr, rem ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
                 }
                 const u32 shr = sh + ptx::zero_after(rold[W - 1]);
@@ -1308,8 +1320,8 @@ __device__ __noinline__ void solo_run(const KParams& K, Env E, Smem& sm, u64 dea
                     if ((remmask >> k) & 1u) {
                         const u32 dest = owner_of(K, v[k]);
                         const u32 slot = ptx::atoms_add(&s_sent[side][dest], 1u);
-                        ptx::st_relaxed_sys(rq_of(K, dest, side, E.me) + slot, (u64)v[k] | ((u64)tag << 32));
-                        ptx::st_peer(parent_of(K, dest, side) + (v[k] - dest * K.B), u);
+                        ptx::st_relaxed_sys(s_prq[side][dest] + slot, (u64)v[k] | ((u64)tag << 32));
+                        ptx::st_peer(s_ppar[side][dest] + v[k], u);
                     }
                 }
                 ptx::reds_add(&s_rnew, (u32)__popc(remmask));
