@@ -101,8 +101,8 @@ constexpr u32 HUB_CHUNK = 256;    // adjacency entries per hub work item (1 KB: 
 BIBFS_HD u32 hub_nchunks(u64 r0, u64 r1) { return (u32)((r1 - (r0 & ~3ull) + HUB_CHUNK - 1) / HUB_CHUNK); }
 constexpr u32 BAR_WAYS = 16;
 constexpr u32 PATH_HDR_WORDS = 16;   // sizeof(Result) / 4
-constexpr u32 HUB_CAP = 16384;
-constexpr u32 DUMMY_WORDS = 512 * 512;   // one private scratch word per thread of up to 512 CTAs: target of no-op atomics    // hub entries per level per rank (overflow: expanded in place)
+constexpr u32 HUB_CAP = 16384;          // hub entries per level per rank (overflow: expanded in place)
+constexpr u32 DUMMY_WORDS = 512 * 512;   // one private scratch word per thread of up to 512 CTAs: target of no-op atomics
 
 struct Ctrl {
     // written by the host (H2D copy from pinned memory) before the launch

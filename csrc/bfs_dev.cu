@@ -87,7 +87,7 @@ constexpr u32 FULL = 0xffffffffu;
 constexpr u32 BIG_ROW = 64;          // rows at least this long are strip-mined by the whole warp
 constexpr int UNR = 4;               // independent edges in flight per lane
 constexpr u32 WPC = BFS_THREADS / 32;
-constexpr u32 SOLO_CAP = 4096;       // entries of the shared-memory queue mirror per side (a cluster of 8 x 512 threads)
+constexpr u32 SOLO_CAP = 4096;       // entries of the shared-memory queue mirror per side (larger cluster levels read the queue itself)
 constexpr u32 FILTER_MIN = 4096;
 constexpr u32 STAGE_CAP = 4096;      // grid mode: discoveries a CTA stages in shared memory before one queue reservation     // frontiers at least this large pre-check the visited word
 
