@@ -59,3 +59,17 @@ def test_to_scipy_and_neighbors(bb):
     A = g.to_scipy()
     assert A.shape == (5, 5) and A.nnz == 6
     assert g.neighbors(1).tolist() == [0, 2, 4] and g.degree(3) == 0
+
+
+def test_owner_reciprocal_is_exact():
+    """owner_of() in csrc/bfs_dev.cu replaces v / B by umulhi64(2^64 / B rounded up, v): exact for every 32-bit v."""
+    import random
+    rnd = random.Random(5)
+    M64 = (1 << 64) - 1
+    for _ in range(300):
+        B = rnd.choice([64, 128, 192, 1 << 20, 64 * rnd.randrange(1, 1 << 20), 64 * rnd.randrange(1, 1 << 26)])
+        div = (M64 // B + 1) & M64
+        vs = [0, 1, B - 1, B, B + 1, 2 * B - 1, 7 * B, 8 * B - 1, (1 << 32) - 1] + [rnd.randrange(1 << 32) for _ in range(200)]
+        for v in vs:
+            v &= (1 << 32) - 1
+            assert (div * v) >> 64 == v // B, (B, v)
