@@ -1,6 +1,7 @@
 # Build libbibfs_b200.so (sm_100a only) and the native `bibfs` CLI, in-tree.
 #   make            -> bidirectional_bfs_b200/_native/libbibfs_b200.so + bin/bibfs
 #   make sass       -> docs/sass/*.sass listings (cuobjdump)
+#   make run / make test -> smoke queries on the 1k preset / the CPU test-suite
 #   make clean
 #   make EXTRA=-DBIBFS_FINE_TRACE BUILD=build_ft OUTDIR=build_ft/lib   -> instrumented copy (load it with BIBFS_B200_LIB=...)
 # Counterpart of the reference's per-variant Makefiles (v1..v4/Makefile); the reference's SMS list
@@ -44,7 +45,19 @@ sass: $(LIB)
 	@mkdir -p docs/sass
 	/usr/local/cuda/bin/cuobjdump -sass $(LIB) > docs/sass/libbibfs_b200.sass
 
+# smoke targets like the reference's `make run` (v2/Makefile:31-32, v3/Makefile:46-47, v4/Makefile:63-64): the 1k preset, query 0 -> 999
+graphs/1k.bin:
+	python -m bidirectional_bfs_b200 make-graphs --dir graphs
+
+run: all graphs/1k.bin
+	$(CLI) graphs/1k.bin 0 999 --variant serial
+	$(CLI) graphs/1k.bin 0 999 --variant cpu-ranks --ranks 4
+	@if nvidia-smi -L > /dev/null 2>&1; then $(CLI) graphs/1k.bin 0 999 --variant gpu; else echo "(no GPU: gpu variant skipped)"; fi
+
+test: all
+	python -m pytest tests -q -m "not gpu"
+
 clean:
 	rm -rf $(BUILD) $(LIB) $(CLI)
 
-.PHONY: all clean sass
+.PHONY: all clean sass run test
