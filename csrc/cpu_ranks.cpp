@@ -8,10 +8,12 @@
 // Differences on purpose: the smaller side is expanded (one side per level, like v1/v4) so the
 // reported length is the true hop count (v2 prints ceil(d/2)); parents are recorded so
 // the path comes from the search itself instead of a second serial BFS (second_try.cpp:137-162);
-// the search stops as soon as the side to expand is empty (Q9).
+// the search stops as soon as the side to expand is empty (Q9); small frontiers are expanded by rank 0 alone from
+// vertex lists (solo_phase below), the bitset levels of all ranks take over when a frontier outgrows 2,048 vertices.
 #include "common.h"
 #include <atomic>
 #include <chrono>
+#include <cstdlib>
 #include <thread>
 #include <vector>
 
@@ -71,11 +73,63 @@ struct Shared {
     }
 };
 
-void worker(Shared& S, SpinBarrier& bar, u32 rank, std::chrono::steady_clock::time_point* t_start) {
+// Solo phase (rank 0 alone, the other ranks wait at one barrier): as long as the frontier of the side to expand is
+// small, a level is a walk over a vertex LIST - no bitset sweep, no barrier, no atomics contention.  Same idea as the
+// solo mode of the GPU kernel, and the "queue mode" of the reference's v2 prototype (v2/main-v2.cpp:57-69, frontier
+// queues exchanged with Allgatherv).  The bitset frontiers are kept in step, so the parallel levels can take over at
+// any level boundary.  Reference-sized graphs (average degree 2.2) finish here.
+// (BIBFS_CPU_SOLO_MAX overrides the 2,048 of the hand-over: the tests force the parallel levels with a small value)
+static size_t solo_max_frontier() {
+    const char* e = getenv("BIBFS_CPU_SOLO_MAX");
+    return e ? (size_t)strtoull(e, nullptr, 10) : 2048;
+}
+
+void solo_phase(Shared& S, u32 src, u32 dst) {
+    std::vector<u32> fl[2] = {{src}, {dst}}, nxt;
+    const size_t solo_max = solo_max_frontier();
+    while (!S.done) {
+        const int s = S.side, o = 1 - s;
+        if (fl[s].size() > solo_max) return;                       // hand over to all ranks
+        u32 meet = BIBFS_NO_VERTEX;
+        u64 scanned = 0;
+        nxt.clear();
+        for (u32 u : fl[s]) {
+            for (u64 e = S.row_ptr[u]; e < S.row_ptr[u + 1]; ++e) {
+                const u32 v = S.col[e];
+                ++scanned;
+                const u64 mv = 1ull << (v & 63);
+                const u64 w = S.vis[s][v >> 6].load(std::memory_order_relaxed);
+                if (w & mv) continue;
+                S.vis[s][v >> 6].store(w | mv, std::memory_order_relaxed);
+                S.par[s][v] = u;
+                nxt.push_back(v);
+                if ((S.vis[o][v >> 6].load(std::memory_order_relaxed) & mv) && v < meet) meet = v;
+            }
+        }
+        // keep the bitset frontier of this side in step with the list
+        for (u32 u : fl[s]) S.front[s][u >> 6].store(0, std::memory_order_relaxed);
+        for (u32 v : nxt) S.front[s][v >> 6].fetch_or(1ull << (v & 63), std::memory_order_relaxed);
+        fl[s].swap(nxt);
+        S.nf[s] = fl[s].size();
+        S.visited += fl[s].size();
+        S.scanned += scanned;
+        ++S.depth[s];
+        ++S.levels;
+        if (meet != BIBFS_NO_VERTEX) { S.meet = meet; S.done = true; }
+        else {
+            S.side = S.nf[0] <= S.nf[1] ? 0 : 1;
+            if (S.nf[S.side] == 0) S.done = true;
+        }
+    }
+}
+
+void worker(Shared& S, SpinBarrier& bar, u32 rank, std::chrono::steady_clock::time_point* t_start, u32 src, u32 dst) {
     // start line: the timed region begins when every rank is up (v2 starts MPI_Wtime after MPI_Init
     // and the graph broadcast, second_try.cpp:66)
     bar.wait();
     if (t_start) *t_start = std::chrono::steady_clock::now();
+    if (rank == 0) solo_phase(S, src, dst);
+    bar.wait();
     while (true) {
         const int s = S.side, o = 1 - s;
         if (S.done) return;
@@ -160,8 +214,8 @@ extern "C" int bibfs_cpu_ranks(uint32_t n, const uint64_t* row_ptr, const uint32
 
     std::chrono::steady_clock::time_point t0;
     std::vector<std::thread> th;
-    for (int r = 1; r < ranks; ++r) th.emplace_back(worker, std::ref(S), std::ref(bar), (u32)r, nullptr);
-    worker(S, bar, 0, &t0);
+    for (int r = 1; r < ranks; ++r) th.emplace_back(worker, std::ref(S), std::ref(bar), (u32)r, nullptr, src, dst);
+    worker(S, bar, 0, &t0, src, dst);
     auto t1 = std::chrono::steady_clock::now();
     for (auto& t : th) t.join();
 

@@ -104,3 +104,22 @@ def test_bit_exact_length_vs_reference_v1(bb, ref_v1, tmp_path):
                 assert ours.length == ref_len
                 assert ours.path == ref_path      # same edge order + same schedule => same tie-breaks
                 assert bb.bibfs(g, s, t, variant="cpu-ranks").length == ref_len
+
+
+def test_cpu_ranks_hands_over_to_parallel_levels(bb, monkeypatch):
+    """The solo phase (rank 0, vertex lists) hands over to the bitset levels of all ranks at any level boundary:
+    BIBFS_CPU_SOLO_MAX = 0 / 3 / 40 moves the hand-over through the search, the answers stay those of the serial variant."""
+    from conftest import query_pairs
+    spec = bb.er_spec(20000, 6.0 / 20000, seed=21)
+    g = bb.Graph.generate(spec)
+    ser = bb.SerialSolver(g, policy=0)
+    pairs = query_pairs(spec.n, 10, 9) + [(5, 5)]
+    want = [ser.query(s, t, want_path=False).length for s, t in pairs]
+    for solo_max in ("0", "3", "40", "100000"):
+        monkeypatch.setenv("BIBFS_CPU_SOLO_MAX", solo_max)
+        par = bb.CpuRanksSolver(g, ranks=4)
+        for (s, t), w in zip(pairs, want):
+            r = par.query(s, t)
+            assert r.length == w, (solo_max, s, t)
+            if r.length:
+                bb.validate_path(g, s, t, r.path, r.length)
