@@ -8,14 +8,19 @@
 A step is ONE s-t query (the reference answers one query per process, benchmark_test.sh:47-54).
 Default config: the reference's largest published graph — Erdos-Renyi G(100000, 2.2/n), first
 query 0 -> n-1 (graphs/make_graphs:8-13, benchmark_test.sh:7-8,43) — BASELINE.json config 2.
-The other BASELINE.json shapes are available with --config (rmat10m, grid16m, kron26).
+The other BASELINE.json shapes are measured too (`other_configs` in the JSON line, --others) or
+alone with --config (rmat10m, grid16m, kron26).
 
-Timing: W warm-up queries, then K queries, each device-timed with CUDA events around the search
-and path kernels of that rank, max over ranks per step; L2 is flushed between steps when the
-graph fits in L2.  GTEPS uses the COMMON numerator of BASELINE.md: directed adjacency entries the
-v1 schedule inspects for that query (replayed by the serial variant, policy 0), so more work is
-never rewarded.  "e2e" repeats the K queries through the public API with the query read from
-pinned host memory and the result + path copied back, wall clock.
+Both arms get the graph, the query list and the GTEPS numerator from the SAME stand-alone helper
+(baseline/tools/bench_prep.cpp, no CUDA and no libbibfs_b200.so): the counter-based generator of
+csrc/gen.h, seeded; queries = 0 -> n-1, then seeded random connected pairs; numerator = directed
+adjacency entries the reference's v1 schedule inspects for that query, so more
+work is never rewarded and the GTEPS ratio of two implementations equals their time ratio.
+
+Timing (ours): W warm-up queries, then K queries, each device-timed with CUDA events around the
+search on the launching stream, max over ranks per step; L2 is flushed (256 MB write) between
+steps when the graph fits in L2.  "e2e" repeats the K queries through the public API with the
+query read from pinned host memory and the result + path copied back, wall clock.
 """
 from __future__ import annotations
 
@@ -33,51 +38,109 @@ import numpy as np
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
-PUBLISHED_V4_MS = {"er1k": 35.9098, "er10k": 99.5562, "er50k": 62.6357, "er100k": 108.312}   # benchmark_results.csv:14-17
+# published by the reference (other hardware): benchmark_results.csv:14-17, v4 MPI+CUDA on Quadro M1200 laptops + 1 GbE
+PUBLISHED_V4_MS = {"er1k": 35.9098, "er10k": 99.5562, "er50k": 62.6357, "er100k": 108.312}
+# the same reference binaries measured on the B200 box by the driver in round 1
+# (BENCH_r01 / SCALE_r01 `reference` arm, er100k, 20 queries): v4 ms per query by rank count, v1 on the host CPU
+SAME_BOX_V4_MS = {"er100k": {1: 29.66, 2: 35.78, 4: 46.05, 8: 54.56}}
+SAME_BOX_V1_MS = {"er100k": {"v1_O3": 0.0155, "v1_as_shipped": 0.0364}}
 L2_BYTES = 126 << 20
+UNIT = "GTEPS"
+UNIT_NOTE = "directed adjacency entries inspected by the reference's v1 schedule for the query / search time (the region the reference's own timers cover)"
+
+
+# --------------------------------------------------------------------------------------------
+# graph spec, query list and numerator: shared by both arms, computed without this repo's .so
+# --------------------------------------------------------------------------------------------
+def spec_string(config: str, seed: int) -> tuple[str, str]:
+    """-> (bench_prep spec, description)."""
+    presets = {"er1k": 1000, "er10k": 10000, "er50k": 50000, "er100k": 100000, "er1m": 1000000}
+    if config in presets:
+        n = presets[config]
+        return f"er:{n}:{2.2000000001 / n!r}:{seed}", "ER G(n, 2.2/n) (graphs/make_graphs)"
+    if config == "rmat10m":
+        return f"rmat:24:8:10000000:{seed}", "R-MAT A=.57 B=.19 C=.19, 10M vertices, 80M edges"
+    if config.startswith("rmat"):
+        sc = int(config[4:])
+        return f"rmat:{sc}:16:{1 << sc}:{seed}", f"R-MAT scale {sc} edgefactor 16"
+    if config == "grid16m":
+        return "grid:4096:4096", "2-D grid 4096x4096"
+    if config.startswith("grid"):
+        k = int(config[4:])
+        return f"grid:{k}:{k}", f"2-D grid {k}x{k}"
+    if config == "kron26":
+        return f"rmat:26:16:{1 << 26}:{seed}", "Graph500 Kronecker scale 26 edgefactor 16"
+    raise SystemExit(f"unknown config {config}")
 
 
 def make_spec(bb, config: str, seed: int):
-    if config in ("er1k", "er10k", "er50k", "er100k", "er1m"):
-        return bb.preset_spec(config[2:], seed=seed), "ER G(n, 2.2/n) (graphs/make_graphs)"
-    if config == "rmat10m":
-        return bb.rmat_spec(24, edgefactor=8, n=10_000_000, seed=seed), "R-MAT A=.57 B=.19 C=.19, 10M vertices, 80M edges"
-    if config.startswith("rmat"):
-        sc = int(config[4:])
-        return bb.rmat_spec(sc, edgefactor=16, seed=seed), f"R-MAT scale {sc} edgefactor 16"
-    if config == "grid16m":
-        return bb.grid_spec(4096, 4096), "2-D grid 4096x4096"
-    if config.startswith("grid"):
-        k = int(config[4:])
-        return bb.grid_spec(k, k), f"2-D grid {k}x{k}"
-    if config == "kron26":
-        return bb.rmat_spec(26, edgefactor=16, seed=seed), "Graph500 Kronecker scale 26 edgefactor 16"
-    raise SystemExit(f"unknown config {config}")
+    """The same graph as spec_string(), as a generator spec of the library (our arm only)."""
+    kind, *f = spec_string(config, seed)[0].split(":")
+    if kind == "er":
+        return bb.er_spec(int(f[0]), float(f[1]), seed=int(f[2]))
+    if kind == "rmat":
+        return bb.rmat_spec(int(f[0]), edgefactor=int(f[1]), n=int(f[2]), seed=int(f[3]))
+    return bb.grid_spec(int(f[0]), int(f[1]))
+
+
+def prep_tool() -> Path:
+    exe = ROOT / "bin" / "bench_prep"
+    src = ROOT / "baseline" / "tools" / "bench_prep.cpp"
+    if not exe.exists() or exe.stat().st_mtime < src.stat().st_mtime:
+        exe.parent.mkdir(exist_ok=True)
+        subprocess.run(["g++", "-O3", "-std=c++17", "-pthread", f"-I{ROOT / 'include'}", str(src), "-o", str(exe)], check=True)
+    return exe
 
 
 def candidate_pairs(n: int, count: int, seed: int):
     rng = np.random.default_rng(seed)
-    yield 0, n - 1                       # the reference's query (benchmark_test.sh:8,43)
+    out = [(0, n - 1)]                   # the reference's query (benchmark_test.sh:8,43)
     for _ in range(count):
-        yield int(rng.integers(n)), int(rng.integers(n))
-
-
-def pick_queries(query_fn, n, need, seed):
-    """First `need` candidate pairs that are connected by a path of >= 2 hops (same on every rank)."""
-    out = []
-    for s, t in candidate_pairs(n, 50 * need + 100, seed):
-        if s == t:
-            continue
-        length = query_fn(s, t)
-        if length is not None and (length >= 2 or (s, t) == (0, n - 1)):
-            out.append((s, t, length))
-            if len(out) == need:
-                break
-    if not out:
-        raise SystemExit("no connected query pairs found")
-    while len(out) < need:
-        out.append(out[len(out) % max(1, len(out))])
+        out.append((int(rng.integers(n)), int(rng.integers(n))))
     return out
+
+
+def prepare(config: str, seed: int, need: int, bin_path: Path | None = None, host_limit: int = 40_000_000):
+    """-> dict(n, records, nnz, queries=[(s, t, length, v1_edges, v1_levels)]) from the stand-alone helper.
+    Graphs beyond `host_limit` vertices are not replayed on the host (queries = None)."""
+    spec, desc = spec_string(config, seed)
+    f = spec.split(":")
+    n = {"er": lambda: int(f[1]), "rmat": lambda: int(f[3]), "grid": lambda: int(f[1]) * int(f[2])}[f[0]]()
+    if n > host_limit:
+        return {"n": n, "desc": desc, "queries": None}
+    # the answer is a pure function of (spec, need): keep it for the other runs on this box (N = 1, 2, 4, 8 back to back)
+    shm = Path("/dev/shm") if Path("/dev/shm").is_dir() else Path("/tmp")
+    cache = shm / f"bibfs_prep_{spec.replace(':', '_')}_{need}.json"
+    if cache.exists() and (bin_path is None or bin_path.exists()):
+        try:
+            got = json.loads(cache.read_text())
+            got["queries"] = [tuple(q) for q in got["queries"]]
+            return got
+        except (OSError, ValueError, KeyError):
+            pass
+    cand = candidate_pairs(n, 50 * need + 100, seed)
+    cmd = [str(prep_tool()), spec] + (["--bin", str(bin_path)] if bin_path else [])
+    out = subprocess.run(cmd, input="".join(f"{s} {t}\n" for s, t in cand), capture_output=True, text=True, check=True).stdout.splitlines()
+    _, n_s, rec, nnz = out[0].split()
+    picked = []
+    for line in out[1:]:
+        s, t, length, edges, levels = (int(x) for x in line.split())
+        if s != t and length >= 0 and (length >= 2 or (s, t) == (0, n - 1)):
+            picked.append((s, t, length, edges, levels))
+            if len(picked) == need:
+                break
+    if not picked:
+        raise SystemExit("no connected query pairs found")
+    while len(picked) < need:
+        picked.append(picked[len(picked) % len(picked)])
+    got = {"n": int(n_s), "desc": desc, "records": int(rec), "nnz": int(nnz), "queries": picked}
+    try:
+        tmp = cache.with_suffix(f".{os.getpid()}.tmp")
+        tmp.write_text(json.dumps(got))
+        tmp.replace(cache)
+    except OSError:
+        pass
+    return got
 
 
 def emit(obj):
@@ -87,23 +150,15 @@ def emit(obj):
 # --------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------
-def run_ours(args):
-    import torch
-    import bidirectional_bfs_b200 as bb
-    from bidirectional_bfs_b200.parallel import comm
-    from bidirectional_bfs_b200.utils.clocks import ClockSampler
-
-    rank, world, local = comm.init_distributed()
-    if args.gpus != world:
-        if rank == 0:
-            print(f"note: --gpus {args.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a GPU (use the serial variant via the CLI for CPU numbers)")
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    import torch.distributed as dist
-
-    spec, desc = make_spec(bb, args.config, args.seed)
+def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do_e2e=True):
+    """Build `config` on the GPUs, run W + K queries, return the measurement dict (rank 0) or None."""
+    info = [None]
+    if rank == 0:
+        info[0] = prepare(config, seed, K + W)
+    if world > 1:
+        dist.broadcast_object_list(info, src=0)
+    info = info[0]
+    spec = make_spec(bb, config, seed)
     n = int(spec.n)
     t0 = time.time()
     if world == 1:
@@ -114,28 +169,29 @@ def run_ours(args):
         solver = comm.DistributedSolver(g)
     torch.cuda.synchronize()
     build_s = time.time() - t0
-    nnz_local = g.nnz
-    nnz = nnz_local
+    nnz = g.nnz
     if world > 1:
-        t = torch.tensor([nnz_local], dtype=torch.int64, device=dev)
+        t = torch.tensor([nnz], dtype=torch.int64, device=dev)
         dist.all_reduce(t)
         nnz = int(t.item())
     graph_bytes = nnz * 4 + (n + 1) * 8
 
-    K, W = args.steps, args.warmup
-    queries = pick_queries(lambda s, t: solver.query(s, t, want_path=False).length, n, K + W, args.seed)
-
-    # common GTEPS numerator: the v1 schedule's inspected adjacency entries (serial replay on the CPU)
-    numerator = "v1-schedule edges (serial replay)"
-    v1_edges = None
-    if rank == 0 and n <= 2_500_000:
-        g_cpu = g.to("cpu") if world == 1 else bb.Graph.generate(spec)
-        ser = bb.SerialSolver(g_cpu, policy=0)
-        v1_edges = []
-        for s, t, length in queries:
-            r = ser.query(s, t, want_path=False)
-            assert r.length == length, f"length mismatch vs serial oracle on {s}->{t}: {length} vs {r.length}"
-            v1_edges.append(r.edges_scanned)
+    numerator = "v1-schedule edges (host replay by baseline/tools/bench_prep)"
+    if info["queries"] is None:
+        # too large for the host replay: connected pairs found by the GPUs themselves, own inspected edges as numerator
+        numerator = "edges inspected by this implementation (graph too large for the host replay of the v1 schedule)"
+        queries = []
+        for s, t in candidate_pairs(n, 50 * (K + W) + 100, seed):
+            if s == t:
+                continue
+            r = solver.query(s, t, want_path=False)
+            if r.length is not None and r.length >= 2:
+                queries.append((s, t, r.length, None, r.levels))
+                if len(queries) == K + W:
+                    break
+    else:
+        assert info["nnz"] == nnz, f"device graph has {nnz} stored entries, the helper's {info['nnz']}"
+        queries = info["queries"]
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if graph_bytes < 2 * L2_BYTES else None
 
@@ -144,20 +200,17 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-timed K steps -------------------------------------------------------------
-    sampler = ClockSampler(local, period_ms=20).start()      # clocks / throttle reasons during warm-up + timed regions
-    for s, t, _ in queries[:W]:
+    for s, t, length, _, _ in queries[:W]:
         if flush is not None:
             flush.fill_(1)
-        solver.query(s, t, want_path=True, timing="events")
+        r = solver.query(s, t, want_path=True, timing="events")
+        if r.length != length:
+            raise SystemExit(f"{config}: wrong length on {s}->{t}: {r.length}, the v1 schedule gives {length}")
     barrier()
     launches0 = bb.lib().bibfs_launch_count()
     wall0 = time.perf_counter()
-    ms = np.zeros(K)
-    ms_path = np.zeros(K)
-    own_edges = np.zeros(K)
-    lengths = []
-    for i, (s, t, length) in enumerate(queries[W:W + K]):
+    ms, ms_path, own_edges, lengths = np.zeros(K), np.zeros(K), np.zeros(K), []
+    for i, (s, t, length, _, _) in enumerate(queries[W:W + K]):
         if flush is not None:
             flush.fill_(i & 0xFF)                      # evict the graph from L2 between steps
         r = solver.query(s, t, want_path=True, timing="events")      # CUDA events on the launching stream
@@ -166,7 +219,7 @@ def run_ours(args):
         own_edges[i] = r.edges_scanned
         lengths.append(r.length)
         if r.length != length:
-            raise SystemExit(f"non-deterministic answer on {s}->{t}: {r.length} vs {length}")
+            raise SystemExit(f"{config}: wrong length on {s}->{t}: {r.length}, the v1 schedule gives {length}")
     barrier()
     wall_dev_loop = time.perf_counter() - wall0
     launches = bb.lib().bibfs_launch_count() - launches0
@@ -175,92 +228,125 @@ def run_ours(args):
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)     # max over ranks, per step
         ms = tms.cpu().numpy()
 
-    # ---- end to end through the public API -----------------------------------------------
-    pinned = torch.empty(2, dtype=torch.int32).pin_memory()
-    pinned_np = pinned.numpy()            # same memory; numpy item stores cost ~0.1 us, torch ones ~10 us
-    barrier()
-    e0 = time.perf_counter()
-    d2h = 0
-    for i, (s, t, length) in enumerate(queries[W:W + K]):
-        pinned_np[0], pinned_np[1] = s, t
-        r = solver.query(-1 & 0x7FFFFFFF, -1 & 0x7FFFFFFF, want_path=True, pinned_query=pinned)
-        assert r.length == length
-        d2h += 64 + 4 * (length + 1)
-    barrier()
-    e2e_s = time.perf_counter() - e0
-    if e2e_s < 0.3:                       # keep the GPU in the same state long enough for nvidia-smi to sample it
-        t_end = time.perf_counter() + 0.3
+    e2e_s, d2h = None, 0
+    if do_e2e:
+        pinned = torch.empty(2, dtype=torch.int32).pin_memory()
+        pinned_np = pinned.numpy()            # same memory; numpy item stores cost ~0.1 us, torch ones ~10 us
+        barrier()
+        e0 = time.perf_counter()
+        for s, t, length, _, _ in queries[W:W + K]:
+            pinned_np[0], pinned_np[1] = s, t
+            r = solver.query(-1 & 0x7FFFFFFF, -1 & 0x7FFFFFFF, want_path=True, pinned_query=pinned)
+            assert r.length == length
+            d2h += 64 + 4 * (length + 1)
+        barrier()
+        e2e_s = time.perf_counter() - e0
+        t_end = time.perf_counter() + 0.3     # keep the GPU in the same state long enough for nvidia-smi to sample it under load
         while time.perf_counter() < t_end:
-            s, t, _ = queries[W]
-            solver.query(s, t, want_path=False)
-    clocks = sampler.stop()
-    if world > 1:
-        te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e_s = float(te.item())
+            solver.query(queries[W][0], queries[W][1], want_path=False)
+        if world > 1:
+            te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+            e2e_s = float(te.item())
+    solver.close()
+    del solver, g
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    num = own_edges if queries[0][3] is None else np.array([q[3] for q in queries[W:W + K]], dtype=np.float64)
+    total_ms = float(ms.sum())
+    return {
+        "config": config, "desc": info["desc"], "n": n, "nnz": nnz, "numerator": numerator,
+        "gteps": float(num.sum() / (total_ms * 1e-3) / 1e9) if total_ms > 0 else 0.0,
+        "ms_per_step": total_ms / K, "ms": ms, "ms_path": ms_path, "lengths": lengths,
+        "own_gteps": float(own_edges.sum() / (total_ms * 1e-3) / 1e9) if total_ms > 0 else 0.0,
+        "num_sum": float(num.sum()), "e2e_s": e2e_s, "d2h": d2h, "launches": int(launches), "build_s": build_s,
+        "wall_dev_loop": wall_dev_loop, "l2": "256 MB write between steps" if flush is not None else "inputs larger than L2",
+        "levels_mean": float(np.mean([q[4] for q in queries[W:W + K]])),
+    }
 
-    # ---- extra (N > 1, graph fits one GPU): the same K queries dealt over N REPLICAS of the graph, one per GPU.
-    # Not the headline (that is one query answered by all ranks on the partitioned graph, the reference's
-    # multi-rank semantics); reported so that the capacity and the throughput use of N GPUs can be told apart.
-    replicated = None
-    if world > 1 and graph_bytes < (8 << 30):
-        g_full = bb.Graph.generate(spec, device=dev)
-        rsolver = bb.GpuSolver(g_full)
-        mine = queries[W:W + K][rank::world]
-        for s, t, _ in mine[:2]:
-            rsolver.query(s, t, want_path=True)
-        barrier()
-        r0 = time.perf_counter()
-        for s, t, length in mine:
-            assert rsolver.query(s, t, want_path=True).length == length
-        barrier()
-        rep_s = time.perf_counter() - r0
-        tr = torch.tensor([rep_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(tr, op=dist.ReduceOp.MAX)
-        replicated = {"queries_per_s": K / float(tr.item()), "ms_per_query_wall": float(tr.item()) * 1e3 / K,
-                      "what": f"the K timed queries dealt round-robin over {world} GPUs, each holding the whole graph; wall clock incl. path, max over ranks"}
-        rsolver.close()
+
+def run_ours(args):
+    import torch
+    import bidirectional_bfs_b200 as bb
+    from bidirectional_bfs_b200.parallel import comm
+    from bidirectional_bfs_b200.utils.clocks import ClockSampler
+
+    rank, world, local = comm.init_distributed()
+    if args.gpus != world and rank == 0:
+        print(f"note: --gpus {args.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU (use the serial variant via the CLI for CPU numbers)")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    import torch.distributed as dist
+
+    K, W = args.steps, args.warmup
+    sampler = ClockSampler(local, period_ms=20).start()      # clocks / throttle reasons during warm-up + timed regions
+    m = measure_ours(bb, comm, dist, torch, dev, rank, world, args.config, args.seed, K, W)
+    clocks = sampler.stop()
+
+    # ---- the other BASELINE.json shapes, a few queries each (same method; not the headline value)
+    others = {}
+    for cfg in [c for c in args.others.split(",") if c and c != args.config]:
+        t0 = time.time()
+        try:
+            o = measure_ours(bb, comm, dist, torch, dev, rank, world, cfg, args.seed, args.other_steps, 3, do_e2e=False)
+        except Exception as e:  # noqa: BLE001
+            o = None
+            if rank == 0:
+                others[cfg] = {"error": str(e)[:200]}
+        if o is not None:
+            others[cfg] = {"model": o["desc"], "n": o["n"], "directed_edges": o["nnz"], "steps": args.other_steps, "warmup": 3,
+                           "ms_per_step": o["ms_per_step"], "value": o["gteps"], "unit": UNIT, "numerator": o["numerator"],
+                           "own_edges_gteps": o["own_gteps"], "levels_mean": o["levels_mean"],
+                           "path_length": {"min": int(min(o["lengths"])), "max": int(max(o["lengths"]))},
+                           "us_per_level": 1e3 * o["ms_per_step"] / max(1.0, o["levels_mean"]), "l2": o["l2"],
+                           "graph_build_s": o["build_s"], "wall_s": time.time() - t0}
 
     if rank == 0:
-        if v1_edges is None:
-            numerator = "edges inspected by this implementation (graph too large for the CPU replay)"
-            num = own_edges
-        else:
-            num = np.array(v1_edges[W:W + K], dtype=np.float64)
-        total_ms = float(ms.sum())
-        gteps = float(num.sum() / (total_ms * 1e-3) / 1e9) if total_ms > 0 else 0.0
-        e2e_gteps = float(num.sum() / e2e_s / 1e9)
-        ms_per_step = total_ms / K
-        vsb = PUBLISHED_V4_MS[args.config] / ms_per_step if args.config in PUBLISHED_V4_MS else None
+        ms_per_step = m["ms_per_step"]
+        v4 = SAME_BOX_V4_MS.get(args.config, {}).get(world)
+        v1 = SAME_BOX_V1_MS.get(args.config)
+        e2e_gteps = m["num_sum"] / m["e2e_s"] / 1e9
         emit({
-            "metric": "GTEPS", "value": gteps, "unit": "GTEPS (v1-schedule directed edges / CUDA-event-timed search time, the region the reference's timers cover)",
+            "metric": "GTEPS", "value": m["gteps"], "unit": UNIT, "unit_note": UNIT_NOTE,
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_per_step,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": vsb,
-            "vs_baseline_note": "published v4 MPI+CUDA time on this graph size (benchmark_results.csv:14-17, Quadro M1200 laptops) divided by ms_per_step; GTEPS was not published, same numerator on both sides makes the GTEPS ratio equal the time ratio",
+            "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": (v4 / ms_per_step) if v4 else None,
+            "vs_baseline_note": "BASELINE.md §4: the reference's v4 MPI+CUDA binary (sm_100 build) on the same B200 box with the same number of ranks, "
+                                "ms per query / ours (same numerator on both sides: the GTEPS ratio is the time ratio). The driver's own ratio comes from --impl reference.",
+            "vs_published_v4_laptop": (PUBLISHED_V4_MS[args.config] / ms_per_step) if args.config in PUBLISHED_V4_MS else None,
+            "vs_reference_v1_serial_cpu": None if not v1 else {
+                "v1_O3_ms": v1["v1_O3"], "v1_as_shipped_ms": v1["v1_as_shipped"], "ours_ms": ms_per_step,
+                "ratio_vs_v1_O3": v1["v1_O3"] / ms_per_step, "ratio_vs_v1_as_shipped": v1["v1_as_shipped"] / ms_per_step,
+                "note": "the reference's serial v1 on the host CPU (same box, BASELINE.md §4); a ratio below 1 means the CPU variant is faster on this latency-bound graph"},
             "dtype": "uint32 vertex ids / bitmaps (integer traversal, no floating point)", "data": "synthetic",
             "impl": "ours",
-            "config": {"model": f"bidirectional BFS on {desc}", "name": args.config, "n": n, "directed_edges": nnz,
+            "config": {"model": f"bidirectional BFS on {m['desc']}", "name": args.config, "n": m["n"], "directed_edges": m["nnz"],
                        "global_batch": 1, "seq_len": None, "queries": "0->n-1 first, then seeded random connected pairs",
                        "parallelism": f"1-D vertex partition over {world} GPU(s), one process per GPU",
-                       "l2": "256 MB write between steps" if flush is not None else "inputs larger than L2",
-                       "numerator": numerator, "seed": args.seed},
-            "search_ms": {"mean": ms_per_step, "median": float(np.median(ms)), "min": float(ms.min()), "max": float(ms.max())},
-            "path_kernel_ms_mean": float(ms_path.mean()),
-            "path_length": {"min": int(min(lengths)), "max": int(max(lengths))},
-            "own_edges_gteps": float(own_edges.sum() / (total_ms * 1e-3) / 1e9) if total_ms > 0 else 0.0,
+                       "l2": m["l2"], "numerator": m["numerator"], "seed": args.seed},
+            "search_ms": {"mean": ms_per_step, "median": float(np.median(m["ms"])), "min": float(m["ms"].min()), "max": float(m["ms"].max())},
+            "path_ms_mean": float(m["ms_path"].mean()),
+            "path_length": {"min": int(min(m["lengths"])), "max": int(max(m["lengths"]))},
+            "own_edges_gteps": m["own_gteps"],
             "clocks": {"sm_mhz": clocks["sm_mhz"], "sm_max_mhz": clocks["sm_max_mhz"], "reasons": clocks["reasons"], "samples": clocks["samples"]},
-            "e2e": {"value": e2e_gteps, "unit": "GTEPS", "ms_per_step": e2e_s * 1e3 / K, "h2d_bytes_per_step": 8,
-                    "d2h_bytes_per_step": d2h / K, "what": "solver.query(): (src,dst) in pinned host memory read by the kernel -> search + path walk in one launch -> [result | path] written to pinned host memory and read by the caller, wall clock"},
-            "gpu_launches": int(launches), "launches_per_step": launches / K, "replicated_graph_throughput": replicated,
-            "graph_build_s": build_s, "wall_s_device_loop": wall_dev_loop,
+            "e2e": {"value": e2e_gteps, "unit": UNIT, "ms_per_step": m["e2e_s"] * 1e3 / K, "h2d_bytes_per_step": 8,
+                    "d2h_bytes_per_step": m["d2h"] / K,
+                    "what": "solver.query(): (src,dst) in pinned host memory read by the kernel -> search + path walk in one launch -> [result | path] written to pinned host memory and read by the caller, wall clock"},
+            "gpu_launches": m["launches"], "launches_per_step": m["launches"] / K,
+            "graph_build_s": m["build_s"], "wall_s_device_loop": m["wall_dev_loop"],
+            "other_configs": others,
         })
-    solver.close()
     if world > 1:
         dist.destroy_process_group()
 
 
 # --------------------------------------------------------------------------------------------
-# reference arm: the unmodified reference binaries, one process launch per query (their API)
+# reference arm: the unmodified reference binaries, one process launch per query (their API).
+# Nothing of this repository's library is imported here: graph file, queries and numerator come
+# from the stand-alone helper, the measured region is baseline/_ref/bin/v4 under the MPI stand-in.
 # --------------------------------------------------------------------------------------------
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
@@ -274,23 +360,15 @@ def run_reference(args):
     if not exe.exists():
         emit({"impl": "reference", "unavailable": "baseline/_ref/bin/v4 missing and baseline/build_ref.sh could not build it (see baseline/_ref/build.log)"})
         return
-    import bidirectional_bfs_b200 as bb
-    import torch
-    spec, desc = make_spec(bb, args.config, args.seed)
-    n = int(spec.n)
-    if n > 2_500_000 and not args.force:
-        emit({"impl": "reference", "unavailable": f"config {args.config}: the reference reloads and rebuilds the whole graph in every process (one query per process); not run by default (--force to try)"})
-        return
-    # the same graph as our arm: same generator, same seed (host generator == device generator bit for bit)
-    edges = bb.graph.edge_list(spec, "cuda:0" if torch.cuda.is_available() else "cpu")
+    spec, desc = spec_string(args.config, args.seed)
+    K, W = args.steps, args.warmup
     shm = Path("/dev/shm") if Path("/dev/shm").is_dir() else Path("/tmp")
     path = shm / f"bibfs_bench_{args.config}_{args.seed}.bin"
-    bb.io.write_bin(path, n, edges)
-    g_cpu = bb.Graph.from_edges(n, edges)
-    ser = bb.SerialSolver(g_cpu, policy=0)
-    K, W = args.steps, args.warmup
-    queries = pick_queries(lambda s, t: ser.query(s, t, want_path=False).length, n, K + W, args.seed)
-    v1_edges = [ser.query(s, t, want_path=False).edges_scanned for s, t, _ in queries]
+    info = prepare(args.config, args.seed, K + W, bin_path=path, host_limit=40_000_000 if args.force else 2_500_000)
+    if info["queries"] is None:
+        emit({"impl": "reference", "unavailable": f"config {args.config}: the reference reloads and rebuilds the whole graph in every process (one query per process); not run by default (--force to try)"})
+        return
+    n, queries = info["n"], info["queries"]
     env = dict(os.environ, MPISHIM_GPU_PER_RANK="1", MPISHIM_SLOT_BYTES=str(max(64 << 20, 4 * n + 4096)))
     for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
         env.pop(k, None)
@@ -310,10 +388,10 @@ def run_reference(args):
         return float(m.group(1)) * 1e3
 
     try:
-        for s, t, length in queries[:W]:
+        for s, t, length, _, _ in queries[:W]:
             one(s, t, length)
         t0 = time.perf_counter()
-        for s, t, length in queries[W:W + K]:
+        for s, t, length, _, _ in queries[W:W + K]:
             ms.append(one(s, t, length))
         wall = time.perf_counter() - t0
     except Exception as e:  # noqa: BLE001
@@ -325,7 +403,7 @@ def run_reference(args):
         if not Path(cmd[0]).exists():
             continue
         vals = []
-        for s, t, _ in queries[W:W + min(K, 5)]:
+        for s, t, _, _, _ in queries[W:W + K]:
             o = subprocess.run(cmd + [str(path), str(s), str(t)], capture_output=True, text=True, timeout=600).stdout
             m = re.search(r"took ([0-9.eE+-]+) seconds", o)
             if m:
@@ -335,20 +413,30 @@ def run_reference(args):
                 vals.append(float(m.group(1)))
         if vals:
             extra[name + "_ms_mean"] = float(np.mean(vals))
-    num = np.array(v1_edges[W:W + K], dtype=np.float64)
+    num = np.array([q[3] for q in queries[W:W + K]], dtype=np.float64)
+    levels = float(np.mean([q[4] for q in queries[W:W + K]]))
     total_ms = float(np.sum(ms))
+    # bytes the reference moves per query and rank, from its source: CSR upload once (v4/comp.cu:49-65), then per level
+    # H2D frontier 4N (comp.cu:94) and D2H next + visited 8N (comp.cu:104-105)
+    h2d = (n + 1) * 4 + info["nnz"] * 4 + levels * 4 * n
+    d2h = levels * 8 * n
     emit({
-        "metric": "GTEPS", "value": float(num.sum() / (total_ms * 1e-3) / 1e9), "unit": "GTEPS (v1-schedule directed edges / time printed by the reference)",
+        "metric": "GTEPS", "value": float(num.sum() / (total_ms * 1e-3) / 1e9), "unit": UNIT,
+        "unit_note": UNIT_NOTE + "; here: the time the reference prints ([Time] MPI+CUDA BI-BFS, MPI_Wtime around its level loop, rank 0)",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": (PUBLISHED_V4_MS[args.config] / (total_ms / K)) if args.config in PUBLISHED_V4_MS else None,
         "dtype": "int32 flags per vertex (reference)", "data": "synthetic", "impl": "reference",
         "config": {"model": f"reference v4 MPI+CUDA (mpi_bibfs, sm_100 build) on {desc}", "name": args.config, "n": n,
-                   "ranks": world, "launcher": "baseline/mpi_shim/mpirun (shared-memory MPI stand-in, one GPU per rank)",
-                   "timer": "the reference's own '[Time] MPI+CUDA BI-BFS' line (MPI_Wtime around its level loop, rank 0)",
-                   "numerator": "v1-schedule edges (serial replay)", "seed": args.seed},
+                   "directed_edges": info["nnz"], "global_batch": 1, "seq_len": None,
+                   "queries": "0->n-1 first, then seeded random connected pairs",
+                   "parallelism": f"{world} MPI rank(s), one GPU per rank, graph replicated (baseline/mpi_shim/mpirun: shared-memory MPI stand-in)",
+                   "l2": "one process per query: every query starts with a cold GPU", "numerator": "v1-schedule edges (host replay by baseline/tools/bench_prep)",
+                   "seed": args.seed},
         "wrong_lengths": wrong, "wall_s": wall, "other_reference_variants": extra,
-        "e2e": {"value": float(num.sum() / wall / 1e9), "unit": "GTEPS", "what": "wall clock of the K process launches (graph load + build + search + exit)"},
-        "gpu_launches": None,
+        "e2e": {"value": float(num.sum() / wall / 1e9), "unit": UNIT, "ms_per_step": wall * 1e3 / K,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "what": "wall clock of the K process launches of the reference's public interface (graph load + build + upload + search + exit); bytes per rank computed from v4/comp.cu:49-106"},
+        "gpu_launches": int(K * levels), "gpu_launches_note": "one expand_frontier_kernel per level and rank (v4/comp.cu:99), levels from the v1 schedule",
     })
 
 
@@ -359,6 +447,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--config", default="er100k")
+    ap.add_argument("--others", default="rmat10m,grid16m", help="further BASELINE.json shapes reported as other_configs ('' = none)")
+    ap.add_argument("--other-steps", type=int, default=6)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--force", action="store_true")
     args = ap.parse_args()

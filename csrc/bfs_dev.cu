@@ -11,7 +11,7 @@
 //   expand_frontier(_kernel)  (v3:13-43, comp.cu:20-38; one thread per vertex over all N)
 //        -> expand_td: frontier-proportional work, warp-cooperative neighbour gathering with
 //           batched independent loads/atomics; rows >= HUB_ROW are deferred to a hub phase in
-//           which the whole grid splits them into 2 KB chunks;
+//           which the whole grid splits them into 1 KB chunks (HUB_CHUNK entries);
 //           expand_bu: bottom-up sweep over unvisited owned vertices against a frontier bitmap
 //   check_intersect(_kernel) + host O(N) scan  (v3:45-62, comp.cu:40-47, mpi_bas.cpp:81-87)
 //        -> fused: the visited bitmap word carries both sides' bits, so the atomic OR that claims
@@ -20,11 +20,12 @@
 //        -> a remote atom.or on the OWNER's bitmap word + remote stores of the parent and of the
 //           vertex into the owner's per-sender queue segment, straight over NVLink (peer pointers)
 //   MPI_Allreduce(LOR/SUM) for found / changed / frontier sizes  (mpi_bas.cpp:85,124; second_try:115-124)
-//        -> one 16-byte slot store per peer + a release flag; every rank sums the slots itself
+//        -> four tagged 8-byte words per peer (value | epoch tag << 32, st.relaxed.sys); every rank
+//           polls its own slots until all tags match and sums them itself (cross_exchange)
 //   the blocking collectives' implicit barrier
-//        -> device-side barrier: local arrive counter + generation word, cross-rank epoch flags
-//           written with st.release.sys and polled with ld.acquire.sys.  A watchdog turns a lost
-//           rank into an error instead of a hang.
+//        -> device-side barrier: 16 local arrive counters + a generation word; across ranks the
+//           tagged words ARE the barrier (no fence.sys, no release/acquire pair on the level
+//           path).  A watchdog turns a lost rank into an error instead of a hang.
 //
 // Scheduling: the side with the smaller (global) frontier is expanded, ties to the source side
 // (v1/main-v1.cpp:51, mpi_bas.cpp:90-92).  Small local frontiers are expanded by CTA 0 alone
@@ -1787,46 +1788,10 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 load_state();
                 continue;
             }
-            {
-                solo_run<MULTI>(K, E, sm, deadline);
-                if (s_fail) { if (warp == 0) publish_and_wake(); __syncthreads(); alive = false; break; }
-                if (warp == 0) publish_and_wake();      // left solo mode: the grid is needed (or the query is done)
-                __syncthreads();
-                continue;
-            }
-            {
-                const u32 side = st.side;
-                const u32 nq = st.q_hi[side] - st.q_lo[side];
-                // read the frontier from the shared mirror when the previous level of this side left
-                // one; this level's discoveries go to the side's other buffer
-                const u32 cur = s_qcur[side];
-                const u32* front = (s_qvalid[side] && nq <= SOLO_CAP) ? s_q[side][cur] : nullptr;
-                E.A = &s_acc; E.solo = true;
-                E.tag = (u32)(st.xepoch + 1);
-                E.sq = s_q[side][cur ^ 1u];
-                E.sq_base = st.q_hi[side];           // == current tail of this side's queue
-                E.s_hub = &s_hub;
-                E.filter = st.local_front >= FILTER_MIN;
-                expand_td<MULTI>(K, E, st, warp, WPC, front);
-            }
+            solo_run<MULTI>(K, E, sm, deadline);
+            if (s_fail) { if (warp == 0) publish_and_wake(); __syncthreads(); alive = false; break; }
+            if (warp == 0) publish_and_wake();      // left solo mode: the grid is needed (or the query is done)
             __syncthreads();
-            if (warp == 0) {
-                const bool hubs = s_hub != 0;
-                const u32 side_done = st.side;
-                if (!leader_sync<MULTI>(K, E, st, s_acc, SYNC_LEVEL, PH_TD_SOLO, deadline, hubs) && lane == 0) s_fail = 1;
-                if (lane == 0) {
-                    // (a hub phase appends to the global queue only: the mirror is then incomplete)
-                    s_qcur[side_done] ^= 1u;
-                    s_qvalid[side_done] = (!hubs && s_acc.q_tail[side_done] - E.sq_base <= SOLO_CAP) ? 1u : 0u;
-                    s_hub = 0;
-                }
-                __syncwarp();
-                if (st.phase != PH_TD_SOLO) publish_and_wake();
-            }
-            __syncthreads();
-            DBG_STAMP2(3, st.phase);
-            E.sq = nullptr; E.s_hub = nullptr; E.filter = true; E.solo = false; E.A = &C->acc;
-            if (s_fail) { alive = false; break; }
         } else if (phase == PH_TD_GRID) {
             E.A = &C->acc;
             E.tag = (u32)(st.xepoch + 1);

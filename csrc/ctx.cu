@@ -58,6 +58,9 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     if (desc->vranks < 1 || desc->rank_lo + desc->vranks > desc->nranks) return fail("bad hosted rank range");
     for (u32 i = 0; i < desc->vranks; ++i)
         if (!desc->d_row_ptr[i]) return fail("hosted rank %u has no CSR", desc->rank_lo + i);
+    for (u32 i = 0; i < desc->vranks; ++i)
+        if (reinterpret_cast<uintptr_t>(desc->d_col[i]) & 15u)
+            return fail("d_col of hosted rank %u is not 16-byte aligned (hub rows are fetched with cp.async.bulk)", desc->rank_lo + i);
     int coop = 0, dev = 0;
     BIBFS_CUDA_TRY(cudaGetDevice(&dev));
     BIBFS_CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
@@ -209,6 +212,7 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
 extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const uint32_t* h_query_pinned,
                                uint32_t flags, void* stream) {
     if (!c) return fail("NULL ctx");
+    if (flags & ~BIBFS_F_ALL) return fail("unknown query flag bits 0x%x", flags & ~BIBFS_F_ALL);
     for (u32 r = 0; r < c->d.nranks; ++r)
         if (!c->arena_all[r]) return fail("rank %u is not attached", r);
     DeviceGuard g(c->device);
@@ -297,6 +301,8 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     cudaGetLastError();
     if (hr->status == 1) return fail("search aborted by the device watchdog (a rank did not arrive); reset the context");
     if (hr->status == 2) return fail("src/dst out of range (n=%u)", c->d.n);
+    if (has_path && hr->status == 0 && hr->length >= 0 && path && (hr->path_len == 0 || hr->path_len > path_cap))
+        res->status = 3;     // a path exists but did not fit the device buffer (max_path) or the caller's (path_cap)
     if (path && has_path && hr->path_len && hr->path_len <= path_cap) {
         if (hr->path_len > first) {      // long path: fetch all of it from the device buffer
             BIBFS_CUDA_TRY(cudaMemcpyAsync(hp, c->arena_local[0] + c->L.off_path + sizeof(Result), (size_t)hr->path_len * 4,

@@ -133,7 +133,8 @@ typedef struct {
     uint32_t levels;         /* single-side expansions performed                            */
     uint32_t levels_bottom_up;
     uint32_t path_len;       /* vertices written to the path buffer (length+1), 0 if none   */
-    int32_t  status;         /* 0 ok; 1 watchdog abort; 2 bad arguments                     */
+    int32_t  status;         /* 0 ok; 1 watchdog abort; 2 bad arguments; 3 path found but longer than the
+                                path buffer (length is valid, path_len = 0: retry with a larger max_path / path_cap) */
     uint64_t edges_scanned;  /* directed adjacency entries inspected                        */
     uint64_t vertices_visited;
     double   search_ms;      /* host variants: wall; device variants: cudaEvent search kernel */
@@ -176,7 +177,8 @@ typedef struct {
     uint32_t rank_lo;           /* first rank hosted here                                  */
     uint32_t vranks;            /* ranks hosted here                                       */
     const uint64_t* d_row_ptr[BIBFS_MAX_RANKS]; /* per hosted rank i: rows of rank rank_lo+i */
-    const uint32_t* d_col[BIBFS_MAX_RANKS];
+    const uint32_t* d_col[BIBFS_MAX_RANKS];     /* 16-byte aligned, and readable for 12 bytes past the last entry: rows of
+                                                   >= 1024 entries are fetched with 16-byte-granular bulk copies (TMA)    */
     uint32_t max_path;          /* capacity of the device path buffer (0 -> default)       */
     uint32_t solo_threshold;    /* frontier <= this is expanded by one CTA (0 -> default)  */
     uint32_t bottom_up_div;     /* go bottom-up when frontier > n/div (0 -> default, ~0u never) */
@@ -204,7 +206,7 @@ int bibfs_ctx_reset(bibfs_ctx* ctx, void* stream);
 #define BIBFS_F_NO_PATH     16u   /* skip the path kernel                                   */
 #define BIBFS_F_DEVICE_CLOCK 32u  /* one rank: no CUDA events around the launch; search_ms / path_ms come from the
                                      device's own clock and completion is detected by polling the pinned result    */
-#define BIBFS_F_POLICY_V1   32u   /* reserved: side choice by vertex count (the default)    */
+#define BIBFS_F_ALL         63u   /* every defined flag bit; bibfs_ctx_query rejects any other bit */
 
 /* Enqueue one query: (optional) H2D of the query from pinned host memory, the persistent
  * search kernel, and the path kernel.  h_query_pinned = {src,dst} in pinned memory, or NULL
