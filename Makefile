@@ -17,13 +17,20 @@ OUTDIR    ?= bidirectional_bfs_b200/_native
 LIB       := $(OUTDIR)/libbibfs_b200.so
 CLI       := bin/bibfs
 
-CU_SRCS   := csrc/gen_dev.cu csrc/csr_dev.cu csrc/bfs_dev.cu csrc/ctx.cu csrc/naive_dev.cu csrc/msbfs_dev.cu csrc/scan_noalloc.cu
+CU_SRCS   := csrc/gen_dev.cu csrc/csr_dev.cu csrc/bfs_dev.cu csrc/ctx.cu csrc/naive_dev.cu csrc/msbfs_dev.cu csrc/scan_noalloc.cu csrc/vrec_dev.cu
 CPP_SRCS  := csrc/error.cpp csrc/host_io.cpp csrc/host_graph.cpp csrc/cpu_serial.cpp csrc/cpu_ranks.cpp
 CU_OBJS   := $(patsubst csrc/%.cu,$(BUILD)/%.o,$(CU_SRCS))
 CPP_OBJS  := $(patsubst csrc/%.cpp,$(BUILD)/%.o,$(CPP_SRCS))
 HDRS      := $(wildcard csrc/*.h csrc/*.cuh include/*.h)
 
-all: $(LIB) $(CLI)
+PREP      := bin/bench_prep
+
+all: $(LIB) $(CLI) $(PREP)
+
+# stand-alone helper of bench.py (graph file, query list, v1-schedule numerator) — links nothing of the library
+$(PREP): baseline/tools/bench_prep.cpp csrc/gen.h csrc/rng.h
+	@mkdir -p bin
+	$(CXX) -O3 -std=c++17 -pthread -Iinclude $< -o $@
 
 $(BUILD)/%.o: csrc/%.cu $(HDRS)
 	@mkdir -p $(BUILD)

@@ -219,6 +219,8 @@ class BatchSolver:
                 d.n, d.nranks, d.rank_lo, d.vranks = graph.n, 1, 0, 1
                 d.d_row_ptr[0] = s.row_ptr.data_ptr()
                 d.d_col[0] = s.col.data_ptr() if s.col.numel() else s.row_ptr.data_ptr()
+                vr = s.vertex_records()
+                d.d_vrec[0] = vr.data_ptr() if vr is not None else None
                 free, _ = torch.cuda.mem_get_info(graph.device)
                 per_lane = 20 * graph.n + (1 << 22)            # parents + queues + bitmaps, roughly
                 lanes = max(1, min(lanes, int(free * 0.6 // per_lane)))

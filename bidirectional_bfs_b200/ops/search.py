@@ -32,6 +32,8 @@ class PathResult:
     search_ms: float = 0.0       # device-timed for GPU variants, wall for CPU variants
     path_ms: float = 0.0
     variant: str = ""
+    levels_grid: int = 0         # levels that needed the whole grid
+    levels_paired: int = 0       # levels run by the pair tier (both directions per round)
 
     @property
     def found(self) -> bool:
@@ -46,7 +48,7 @@ def result_from_c(src, dst, r: Result, path_buf, variant) -> PathResult:
     return PathResult(src, dst, int(r.length) if found else None, path,
                       int(r.meet) if found else None, int(r.levels), int(r.levels_bottom_up),
                       int(r.depth_s), int(r.depth_t), int(r.edges_scanned), int(r.vertices_visited),
-                      float(r.search_ms), float(r.path_ms), variant)
+                      float(r.search_ms), float(r.path_ms), variant, int(r.levels_grid), int(r.levels_paired))
 
 
 _NVTX = bool(os.environ.get("BIBFS_NVTX"))
@@ -54,7 +56,7 @@ _NVTX = bool(os.environ.get("BIBFS_NVTX"))
 
 class SearchContext:
     def __init__(self, graph, rank_lo=0, vranks=None, max_path=0, solo_threshold=0, bottom_up_div=0,
-                 max_ctas=0, watchdog_ms=0):
+                 max_ctas=0, watchdog_ms=0, pair_tier=True):
         if graph.device.type != "cuda":
             raise ValueError("SearchContext needs a CUDA graph")
         self.graph = graph
@@ -68,6 +70,9 @@ class SearchContext:
             s = graph.shards[rank_lo + i]
             d.d_row_ptr[i] = s.row_ptr.data_ptr()
             d.d_col[i] = s.col.data_ptr() if s.col.numel() else s.row_ptr.data_ptr()
+            if pair_tier:
+                vr = s.vertex_records()
+                d.d_vrec[i] = vr.data_ptr() if vr is not None else None
         d.max_path = max_path or min(graph.n + 1, 1 << 24)
         d.solo_threshold, d.bottom_up_div, d.max_ctas, d.watchdog_ms = solo_threshold, bottom_up_div, max_ctas, watchdog_ms
         self.max_path = d.max_path

@@ -61,7 +61,8 @@ struct LevelState {
     u32 meet;
     u32 status;
     u32 wake;                  // number of local wake-ups issued so far (gen low word)
-    u32 pad;
+    u32 rounds_paired;         // levels run by the pair tier (pair_tier.cuh)
+    u32 levels_grid, pad;      // levels that needed the whole grid (grid top-down, hub phase, bottom-up)
     u64 xepoch;                // cross-rank barrier epoch
     u64 edges_total;           // adjacency entries inspected so far (all ranks)
     u64 visited_total;         // vertices reached so far (all ranks, both sides)
@@ -76,7 +77,8 @@ struct alignas(16) Result {   // 64 bytes (PATH_HDR_WORDS words)
     i32 status;
     u64 edges_scanned;
     u64 vertices_visited;
-    u64 t_begin_ns;            // device clock (%globaltimer) when the search proper began
+    u32 levels_grid;           // levels that ran on the whole grid: feeds the launch-geometry policy of ctx.cu
+    u32 rounds_paired;         // levels run by the pair tier
     u32 search_ns, path_ns;    // device-measured duration of the search and of the path walk (saturating)
 };
 
@@ -124,6 +126,7 @@ struct Ctrl {
     alignas(128) u64 xepoch;
     u32 abort_flag;
     u32 trace_count;
+    u64 t_begin_ns;            // device clock (%globaltimer) when the search proper began
     alignas(128) LevelState st;
     alignas(128) Result res;
 };
@@ -170,6 +173,8 @@ struct KParams {
     char* arena[MAXR];             // base of every rank's arena as seen from this device
     const u64* row_ptr[MAXR];      // CSR shards of the hosted ranks (index = rank)
     const u32* col[MAXR];
+    const uint4* vrec[MAXR];       // vertex records of the shards (pair tier), or null
+    u32 warm_lines;                // > 0: the graph is small enough for L2 — idle CTAs prefetch this many 128-byte lines of vrec at query start
 };
 
 // implemented in bfs_dev.cu

@@ -331,7 +331,9 @@ __device__ __noinline__ void write_result(const KParams& K, Ctrl* C, const Level
     R.path_len = 0;
     R.edges_scanned = G.edges_total;
     R.vertices_visited = G.visited_total;
-    { const u64 dt = ptx::globaltimer_ns() - R.t_begin_ns; R.search_ns = dt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)dt; R.path_ns = 0; }
+    R.levels_grid = G.levels_grid;
+    R.rounds_paired = G.rounds_paired;
+    { const u64 dt = ptx::globaltimer_ns() - C->t_begin_ns; R.search_ns = dt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)dt; R.path_ns = 0; }
     C->xepoch = G.xepoch;
 }
 
@@ -440,6 +442,7 @@ __device__ __noinline__ bool leader_sync(const KParams& K, const Env& E, LevelSt
         G.nf[side] = total;
         G.depth[side] += 1;
         G.levels += 1;
+        if (mode != PH_TD_SOLO || level_mode == PH_TD_HUB) G.levels_grid += 1;
         if (mode == PH_BU) { G.levels_bu += 1; G.fbm_cur[side] ^= 1u; G.fbm_valid[side] = 1; }
         else G.fbm_valid[side] = 0;
         G.q_lo[side] = G.q_hi[side];
@@ -494,7 +497,7 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
         for (u32 p = 0; p < MAXR; ++p) { C->sent[0][p] = 0; C->sent[1][p] = 0; }
         C->trace_count = 0;
         G.edges_total = 0; G.visited_total = 2;
-        C->res.t_begin_ns = ptx::globaltimer_ns();
+        C->t_begin_ns = ptx::globaltimer_ns();
         G.phase = PH_TD_SOLO; G.side = 0; G.levels = 0; G.levels_bu = 0;
         G.depth[0] = G.depth[1] = 0;
         G.nf[0] = G.nf[1] = 1;
@@ -503,7 +506,7 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
             G.fbm_cur[s] = 0; G.fbm_valid[s] = 0;
             for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
         }
-        G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 0; G.pad = 0;
+        G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 0; G.pad = 0; G.rounds_paired = 0; G.levels_grid = 0;
         G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
         G.rq_tag[0] = G.rq_tag[1] = 0;
         G.xepoch = C->xepoch;
@@ -1623,6 +1626,12 @@ __device__ __noinline__ void cluster_helper(const KParams& K, const Env& E, Smem
     }
 }
 
+#include "pair_tier.cuh"
+
+constexpr size_t SMEM_BYTES = sizeof(Smem) + sizeof(PairSmem);
+static_assert(sizeof(Smem) % 16 == 0, "PairSmem follows Smem in dynamic shared memory");
+static_assert(SMEM_BYTES <= 227 * 1024, "shared memory of the search kernel");
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------
@@ -1632,6 +1641,7 @@ template <bool MULTI>
 __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant__ KParams K) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+    PairSmem& ps = *reinterpret_cast<PairSmem*>(smem_raw + sizeof(Smem));
     LevelState& st = sm.st;        // this CTA's copy of the level state (the leader CTA's is authoritative)
     Acc& s_acc = sm.acc;           // leader CTA: accumulators of solo levels / staging at sync points
     u32& s_fail = sm.fail;
@@ -1717,12 +1727,25 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         }
         __syncthreads();
     } else {
+        if (K.warm_lines && E.cpr > 1) {
+            // the graph fits L2 with room to spare: the CTAs that would only wait stream the vertex records and the
+            // visited words into L2 while the leader runs the first rounds (they were evicted since the last query
+            // whenever anything else used the GPU; a cold record costs ~700 ns on the leader's chain, a hit 154 ns)
+            const char* rec = reinterpret_cast<const char*>(K.vrec[E.me]);
+            const char* vw = reinterpret_cast<const char*>(E.vis);
+            const u32 vis_lines = (E.nw * 8u + 127u) / 128u;
+            const u32 stride = (E.cpr - 1u) * BFS_THREADS;
+            for (u32 i = (E.cta - 1u) * BFS_THREADS + tid; i < K.warm_lines + vis_lines; i += stride)
+                ptx::prefetch_l2(i < K.warm_lines ? rec + 128ull * i : vw + 128ull * (i - K.warm_lines));
+        }
         if (in_leader_cluster) cluster_helper(K, E, sm, cl_rank, cl_seen, deadline);   // may be needed before the first release
         if (warp == 0 && !wait_gen(C, genbase | 1u, deadline) && lane == 0) s_fail = 1;
         __syncthreads();
         if (!s_fail) load_state();
     }
     bool alive = (s_fail == 0);
+    // latency tier first (leader CTA): paired rounds on vertex records, while both frontiers are small
+    bool pair_first = !MULTI && K.vrec[E.me] != nullptr && !(K.flags & (BIBFS_F_FORCE_GRID | BIBFS_F_FORCE_BU));
 
     // Synchronisation point of grid-mode phases.  Returns false if the query was aborted.
     auto sync_grid = [&](int kind, u32 mode) -> bool {
@@ -1787,6 +1810,11 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 if (s_fail) { alive = false; break; }
                 load_state();
                 continue;
+            }
+            if (pair_first) {
+                pair_first = false;
+                pair_run(K, E, sm, ps);
+                if (st.phase != PH_TD_SOLO) { if (warp == 0) publish_and_wake(); __syncthreads(); continue; }
             }
             solo_run<MULTI>(K, E, sm, deadline);
             if (s_fail) { if (warp == 0) publish_and_wake(); __syncthreads(); alive = false; break; }
@@ -1937,8 +1965,8 @@ __global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) 
 // ------------------------------------------------------------------------------------------
 // opt in to the kernel's dynamic shared memory; the attribute is per device, so contexts call this at creation
 static int bfs_prepare(bool multi) {
-    if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-    else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_bibfs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     return 0;
 }
 
@@ -1947,8 +1975,8 @@ int bfs_max_ctas_per_device(bool multi, int* out) {
     BIBFS_CUDA_TRY(cudaGetDevice(&dev));
     BIBFS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (bfs_prepare(multi)) return 1;
-    if (multi) BIBFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_bibfs<true>, BFS_THREADS, sizeof(Smem)));
-    else BIBFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_bibfs<false>, BFS_THREADS, sizeof(Smem)));
+    if (multi) BIBFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_bibfs<true>, BFS_THREADS, SMEM_BYTES));
+    else BIBFS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_bibfs<false>, BFS_THREADS, SMEM_BYTES));
     if (per < 1) return fail("search kernel does not fit on an SM");
     *out = sms * per;
     return 0;
@@ -1958,7 +1986,7 @@ int bfs_launch(const KParams& K, bool multi, cudaStream_t st) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(K.cpr * K.vranks);
     cfg.blockDim = dim3(BFS_THREADS);
-    cfg.dynamicSmemBytes = sizeof(Smem);
+    cfg.dynamicSmemBytes = SMEM_BYTES;
     cfg.stream = st;
     cudaLaunchAttribute attrs[2];
     attrs[0].id = cudaLaunchAttributeCooperative;
@@ -1981,7 +2009,7 @@ int bfs_max_ctas_clustered(u32 cluster, int* out) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(cluster * 64);
     cfg.blockDim = dim3(BFS_THREADS);
-    cfg.dynamicSmemBytes = sizeof(Smem);
+    cfg.dynamicSmemBytes = SMEM_BYTES;
     cudaLaunchAttribute attr;
     attr.id = cudaLaunchAttributeClusterDimension;
     attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;

@@ -26,6 +26,14 @@ struct bibfs_ctx {
     u32 seq = 0;
     u32 cpr = 0;
     u32 cluster = 1;
+    // launch geometry (single rank, clustered): a query that never needs the grid is launched as ONE cluster (its
+    // launch + teardown costs less than half of the 148-CTA cooperative launch); `grid_score` follows the recent
+    // queries' levels_grid and moves the context to the full grid when the graph keeps asking for it
+    u32 cpr_small = 0;
+    int grid_score = 0;
+    int geometry = 0;            // 0 auto, 1 always small, 2 always full (BIBFS_GEOMETRY)
+    bool last_small = false;
+    bool has_vrec = false;
     bool last_fused = false;     // the last query wrote its result (and path) to h_stage from inside the search kernel
     bool last_lean = false;      // ... and was launched without events (BIBFS_F_DEVICE_CLOCK)
     u32* h_seq = nullptr;        // completion word inside h_stage
@@ -95,6 +103,7 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
             if (bfs_max_ctas_clustered(cl, &fit) == 0 && fit >= (int)(2 * cl)) {
                 c->cluster = cl;
                 c->cpr = (per_rank < (u32)fit ? per_rank : (u32)fit) / cl * cl;
+                c->cpr_small = cl;
                 if (c->d.solo_threshold == (u32)BFS_THREADS) c->d.solo_threshold = cl * BFS_THREADS;
                 break;
             }
@@ -103,6 +112,10 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
         cudaGetLastError();
     }
 
+    if (const char* g = getenv("BIBFS_GEOMETRY")) c->geometry = !strcmp(g, "small") ? 1 : !strcmp(g, "full") ? 2 : 0;
+    c->has_vrec = desc->d_vrec[0] != nullptr;
+    for (u32 i = 0; i < desc->vranks; ++i)
+        if (reinterpret_cast<uintptr_t>(desc->d_vrec[i]) & 31u) { delete c; return fail("d_vrec of hosted rank %u is not 32-byte aligned", desc->rank_lo + i); }
     for (u32 i = 0; i < desc->vranks; ++i) {
         cudaError_t e = cudaMalloc((void**)&c->arena_local[i], c->L.total);
         if (e == cudaSuccess) e = cudaMemset(c->arena_local[i], 0, zero_prefix(c->L));
@@ -192,6 +205,11 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     K.n = c->d.n; K.B = c->B; K.P = c->d.nranks;
     K.rank_lo = c->d.rank_lo; K.vranks = c->d.vranks; K.cpr = c->cpr;
     K.cluster = c->cluster;
+    c->last_small = false;
+    if (c->cpr_small && c->cpr_small < c->cpr && c->geometry != 2 && (c->geometry == 1 || c->grid_score < 4)) {
+        K.cpr = c->cpr_small;
+        c->last_small = true;
+    }
     K.solo_threshold = c->d.solo_threshold;
     K.bu_div = c->d.bottom_up_div;
     K.flags = flags;
@@ -206,7 +224,10 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     for (u32 i = 0; i < c->d.vranks; ++i) {
         K.row_ptr[c->d.rank_lo + i] = c->d.d_row_ptr[i];
         K.col[c->d.rank_lo + i] = c->d.d_col[i];
+        K.vrec[c->d.rank_lo + i] = reinterpret_cast<const uint4*>(c->d.d_vrec[i]);
     }
+    // records + visited words of a small graph are streamed into L2 by the idle CTAs at query start (<= 24 MB: a fifth of L2)
+    if (c->has_vrec && !c->multi && c->d.vranks == 1 && (u64)c->B * 32ull <= (24ull << 20)) K.warm_lines = (u32)(((u64)c->d.n * 32ull + 127ull) / 128ull);
 }
 
 extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const uint32_t* h_query_pinned,
@@ -284,7 +305,12 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     res->status = hr->status;
     res->edges_scanned = hr->edges_scanned;
     res->vertices_visited = hr->vertices_visited;
+    res->levels_grid = hr->levels_grid;
+    res->levels_paired = hr->rounds_paired;
     res->path_len = 0;
+    // launch-geometry policy: queries that needed the grid pull the context towards the full launch, the others back
+    if (hr->levels_grid) c->grid_score = c->grid_score + 2 > 8 ? 8 : c->grid_score + 2;
+    else if (c->grid_score > 0) c->grid_score -= 1;
     float a = 0, b = 0;
     if (c->last_lean) {
         res->search_ms = hr->search_ns * 1e-6;        // the device's own clock, launch latency not included

@@ -1,0 +1,251 @@
+// pair_tier.cuh — the latency tier of the search kernel: PAIRED rounds on inline-adjacency records.
+// (included by bfs_dev.cu inside its anonymous namespace, after Env / Smem)
+//
+// A reference-sized query (ER 100k: ~3,000 vertices touched in 14 levels) is a chain of dependent
+// memory round trips; the work is nothing.  The plain solo level has three on its chain
+// (row offsets -> adjacency entries -> visited word) and runs one side per level.  This tier cuts
+// the chain to ONE round trip per round, and halves the number of rounds:
+//
+//   * vertex records ("vrec", built once per shard by k_vrec_build): 32 bytes per vertex =
+//     {degree, row start, first six neighbours}.  When v is a CANDIDATE (read from its parent's
+//     record) its own record is fetched in the same instruction slot as the atomic that claims it:
+//     the claim (285 ns) and the fetch (154 ns, L2) overlap, and a newly discovered vertex enters
+//     the next frontier WITH its neighbours already in shared memory.  A round is
+//         shared memory -> { claim || record fetch } -> shared memory -> one __syncthreads.
+//     Rows longer than six entries read the rest from col[] (a second trip, for those rows only).
+//   * both directions expand in the SAME round on disjoint warps (the reference's v2/v3 expand S
+//     and T in one iteration too, v2/second_try.cpp:70-105 — and print ceil(d/2)).
+//     Exact length rule used here: balls are disjoint when a round starts, so every vertex that
+//     ends the round with both marks was marked by at least one side in this round.  If it sits in
+//     one of the two frontiers that were expanded (its mark is OLD, depth d_x) the path through it
+//     has d_s + d_t + 1 hops; if both marks are new, d_s + d_t + 2.  After a round that saw a hit,
+//     every frontier thread re-reads the visited word of ITS OWN frontier vertex: any other-side
+//     mark there is an old hit.  Cost: one extra load, in the last round only.
+//   * level state lives in registers of EVERY thread (each derives the next round from two
+//     counters and a flag word in shared memory), so a round has one barrier, not two, and no
+//     thread-0 bookkeeping between them (that was 40 % of a solo level).  The counters rotate
+//     through three sets so that nobody resets a word somebody else may still read.
+//
+// The tier runs at the start of a query while both frontiers fit one CTA (<= 512 entries per side)
+// and no row of >= PT_MAXDEG entries has been discovered; then it hands the search to the general
+// machinery (solo / cluster / grid / hub / bottom-up) through the same LevelState those use.
+
+constexpr u32 PT_CAP = 512;          // frontier entries per side
+constexpr u32 PT_MAXDEG = 32;        // a discovered row at least this long ends the tier
+constexpr int PT_NB = 6;             // neighbours inlined in a vertex record
+constexpr int PT_W = 4;              // adjacency entries per lane per batch beyond the inlined ones
+enum : u32 { PT_HIT = 1u, PT_BIG = 2u, PT_OVF = 4u };
+
+struct PairSmem {
+    u32 cnt[3][2];                   // vertices discovered in the round, per side (three rotating sets)
+    u32 flag[3];
+    u32 meet_new[3];                 // smallest vertex a claim of the round found marked by the other side
+    u32 tr_edges[3][2];              // (tracing only) adjacency entries per side
+    u32 meet_old[2];                 // old-hit test: smallest frontier vertex of side x that carries the other side's mark
+    unsigned long long edges, visited;
+    alignas(16) u32 fv[2][2][PT_CAP];            // frontier vertices [side][buffer]
+    alignas(16) uint4 fr[2][2][PT_CAP][2];       // ... and their records
+};
+
+__device__ __forceinline__ uint4 ld_rec(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void reds_or(u32* p, u32 v) {
+    asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(ptx::smem_addr(p)), "r"(v) : "memory");
+}
+
+// Returns with st.phase == PH_DONE (result written) or with the level state handed over (decide_next done).
+__device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSmem& ps) {
+    const u32 tid = threadIdx.x, lane = tid & 31;
+    LevelState& st = sm.st;
+    Ctrl* const C = E.C;
+    const uint4* const vrec = K.vrec[E.me];
+    const u32* const g_col = E.col;
+    u64* const g_vis = E.vis;
+    u64* const dummy = dummy_of(K, E.me);
+    const u32 g_lo = E.lo;
+    const bool tracing = (K.flags & BIBFS_F_TRACE) != 0;
+    // level state, identical in every thread
+    u32 n0 = 1, n1 = 1, base0 = 1, base1 = 1, d0 = 0, d1 = 0, levels = 0, buf0 = 0, buf1 = 0, par = 0;
+    u64 my_edges = 0;
+    if (tid < 2) {
+        const u32 v = tid ? C->q_dst : C->q_src;
+        const uint4 a = ld_rec(vrec + 2 * (size_t)(v - g_lo)), b = ld_rec(vrec + 2 * (size_t)(v - g_lo) + 1);
+        ps.fv[tid][0][0] = v;
+        ps.fr[tid][0][0][0] = a;
+        ps.fr[tid][0][0][1] = b;
+        ps.meet_old[tid] = a.x >= PT_MAXDEG ? 0u : NO_V;       // (borrowed until the first barrier: "seed row too long")
+    }
+    if (tid < 3) { ps.cnt[tid][0] = 0; ps.cnt[tid][1] = 0; ps.flag[tid] = 0; ps.meet_new[tid] = NO_V; ps.tr_edges[tid][0] = 0; ps.tr_edges[tid][1] = 0; }
+    if (tid == 32) { ps.edges = 0; ps.visited = 0; }
+    __syncthreads();
+    bool leave = (ps.meet_old[0] & ps.meet_old[1]) != NO_V;
+    __syncthreads();
+    if (tid < 2) ps.meet_old[tid] = NO_V;
+    i32 length = -2;                 // -2: still searching
+    u32 meet = NO_V, depth_s = 0, depth_t = 0;
+    u32 visited = 0;
+
+    while (!leave) {
+        // ---- which sides expand: both, unless one frontier dwarfs the other (then the smaller, ties -> source, like v1)
+        const u32 mx = max(n0, n1), mn = min(n0, n1);
+        if (mn > PT_CAP) break;
+        const u32 pad0 = (n0 + 31u) & ~31u;
+        const bool both = (mx <= 4u * mn || mx <= 32u) && pad0 + n1 <= (u32)BFS_THREADS && mx <= PT_CAP;
+        const bool e0 = both || n0 <= n1, e1 = both || n1 < n0;
+        const u32 off1 = e0 ? pad0 : 0u;                        // the target side starts on a warp boundary
+        const u32 side = (e0 && (!e1 || tid < off1)) ? 0u : 1u;      // warp-uniform
+        const u32 idx = side ? tid - off1 : tid;
+        const bool have = side ? (e1 && tid >= off1 && idx < n1) : (e0 && tid < n0);
+        const u32 sh = 32u * side, osh = 32u - sh;
+        const u32 buf = side ? buf1 : buf0;
+        const u32 base = side ? base1 : base0;
+        const bool wide = (e0 ? n0 : 0u) + (e1 ? n1 : 0u) > 64u;  // aggregate the cursor reservations per warp
+        u32 u = 0, deg = 0, r0 = 0, fl = 0;
+        uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
+        if (have) {
+            u = ps.fv[side][buf][idx];
+            ra = ps.fr[side][buf][idx][0];
+            rb = ps.fr[side][buf][idx][1];
+            deg = ra.x; r0 = ra.y;
+        }
+        my_edges += deg;
+        if (tracing && deg) ptx::reds_add(&ps.tr_edges[par][side], deg);
+        u32* const out_v = ps.fv[side][buf ^ 1u];
+        uint4(*const out_r)[2] = ps.fr[side][buf ^ 1u];
+        u32* const cursor = &ps.cnt[par][side];
+        u32* const qs = E.q[side];
+        u32* const pp = E.parent[side];
+
+        // one batch of W candidates: claims and record fetches in flight together (branch-free: idle slots OR a zero
+        // into the thread's scratch word and re-read the thread's own record)
+        auto batch = [&](auto Wc, const u32* v, const u32 nact) {
+            constexpr int W = decltype(Wc)::value;
+            uint4 qa[W], qb[W];
+            u64 old[W];
+#pragma unroll
+            for (int k = 0; k < W; ++k) {
+                const uint4* p = vrec + 2 * (size_t)(((u32)k < nact ? v[k] : u) - g_lo);
+                qa[k] = ld_rec(p);
+                qb[k] = ld_rec(p + 1);
+            }
+#pragma unroll
+            for (int k = 0; k < W; ++k) {
+                const bool act = (u32)k < nact;
+                old[k] = ptx::atom_or_gpu(act ? &g_vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
+            }
+            const u32 shz = sh + ptx::zero_after(old[W - 1]);      // == sh; pins the tests behind the whole batch
+            u32 newmask = 0, meetmask = 0;
+#pragma unroll
+            for (int k = 0; k < W; ++k) {
+                const u32 isnew = (u32)k < nact ? (((u32)(old[k] >> ((v[k] & 31u) + shz)) & 1u) ^ 1u) : 0u;
+                newmask |= isnew << k;
+                meetmask |= (isnew & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
+            }
+            const u32 nnew = (u32)__popc(newmask);
+            u32 slot = 0;
+            if (wide) slot = warp_reserve(nnew, [&](u32 n) { return ptx::atoms_add(cursor, n); });
+            else if (nnew) slot = ptx::atoms_add(cursor, nnew);
+            if (newmask) {
+#pragma unroll
+                for (int k = 0; k < W; ++k) {
+                    if ((newmask >> k) & 1u) {
+                        qs[base + slot] = v[k];
+                        pp[v[k] - g_lo] = u;
+                        if (slot < PT_CAP) { out_v[slot] = v[k]; out_r[slot][0] = qa[k]; out_r[slot][1] = qb[k]; }
+                        else fl |= PT_OVF;
+                        if (qa[k].x >= PT_MAXDEG) fl |= PT_BIG;
+                        ++slot;
+                    }
+                }
+                if (meetmask) {
+                    fl |= PT_HIT;
+#pragma unroll
+                    for (int k = 0; k < W; ++k)
+                        if ((meetmask >> k) & 1u) ptx::reds_min(&ps.meet_new[par], v[k]);
+                }
+            }
+        };
+        if (__any_sync(FULL, have)) {
+            {
+                const u32 c[PT_NB] = {ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
+                batch(std::integral_constant<int, PT_NB>{}, c, min(deg, (u32)PT_NB));
+            }
+            for (u32 e = PT_NB; __any_sync(FULL, e < deg); e += PT_W) {
+                u32 c[PT_W];
+                const u32 left = deg > e ? deg - e : 0u;
+#pragma unroll
+                for (int k = 0; k < PT_W; ++k) c[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((u32)k < left ? e + k : 0u));
+                batch(std::integral_constant<int, PT_W>{}, c, min(left, (u32)PT_W));
+            }
+            if (fl) reds_or(&ps.flag[par], fl);
+        }
+        __syncthreads();
+        // ---- round end: every thread derives the next state from the round's counters
+        const u32 c0 = ps.cnt[par][0], c1 = ps.cnt[par][1], f = ps.flag[par], mnew = ps.meet_new[par];
+        if (tid == 0) {
+            const u32 z = (par + 2u) % 3u;       // last read before this barrier, next used after the next one
+            ps.cnt[z][0] = 0; ps.cnt[z][1] = 0; ps.flag[z] = 0; ps.meet_new[z] = NO_V;
+            if (tracing) {
+                const u64 now = ptx::globaltimer_ns();
+                if (e0) trace_level(K, E, 0, PH_TD_SOLO | 16u, n0, c0, ps.tr_edges[par][0], now);
+                if (e1) trace_level(K, E, 1, PH_TD_SOLO | 16u, n1, c1, ps.tr_edges[par][1], now);
+                ps.tr_edges[z][0] = 0; ps.tr_edges[z][1] = 0;
+            }
+        }
+        if (e0) { d0 += 1; levels += 1; base0 += c0; n0 = c0; buf0 ^= 1u; visited += c0; }
+        if (e1) { d1 += 1; levels += 1; base1 += c1; n1 = c1; buf1 ^= 1u; visited += c1; }
+        par = (par + 1u) % 3u;
+        if (f & PT_HIT) {
+            length = (i32)(d0 + d1); meet = mnew; depth_s = d0;
+            if (e0 && e1) {
+                // old-hit test (see the header): is a vertex of an expanded frontier marked by the other side now?
+                if (have) {
+                    const u64 w = ptx::ld_relaxed_gpu(&g_vis[u >> 5]);
+                    if ((w >> ((u & 31u) + osh)) & 1ull) ptx::reds_min(&ps.meet_old[side], u);
+                }
+                __syncthreads();
+                const u32 m0 = ps.meet_old[0], m1 = ps.meet_old[1];
+                if (m0 != NO_V) { length = (i32)(d0 + d1 - 1u); meet = m0; depth_s = d0 - 1u; }        // in the source frontier, reached by the target side
+                else if (m1 != NO_V) { length = (i32)(d0 + d1 - 1u); meet = m1; depth_s = d0; }
+            }
+            depth_t = (u32)length - depth_s;
+            break;
+        }
+        if (n0 == 0 || n1 == 0) { length = -1; depth_s = d0; depth_t = d1; break; }      // a side is exhausted: no path
+        if (f & (PT_BIG | PT_OVF)) break;
+    }
+    // ---- leave the tier: totals, then either the verdict or the hand-over to the general machinery
+    {
+        u64 e = my_edges;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) e += __shfl_xor_sync(FULL, e, d);
+        if (lane == 0 && e) ptx::reds_add64(&ps.edges, e);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        st.nf[0] = n0; st.nf[1] = n1;
+        st.depth[0] = d0; st.depth[1] = d1;
+        st.levels = levels;
+        st.q_lo[0] = base0 - n0; st.q_hi[0] = base0;
+        st.q_lo[1] = base1 - n1; st.q_hi[1] = base1;
+        sm.acc.q_tail[0] = base0; sm.acc.q_tail[1] = base1;
+        sm.acc.new_count = 0; sm.acc.meet_local = NO_V; sm.acc.edges = 0;
+        sm.qvalid[0] = 0; sm.qvalid[1] = 0;             // the general tiers read the frontier from the queue
+        st.edges_total += ps.edges;
+        st.visited_total += visited;
+        st.rounds_paired = levels;
+        if (length != -2) {
+            st.length = length; st.meet = length >= 0 ? meet : NO_V;
+            st.depth[0] = depth_s; st.depth[1] = depth_t;
+            st.phase = PH_DONE;
+            write_result(K, C, st);
+        } else {
+            decide_next(K, st);
+            if (st.phase == PH_DONE) write_result(K, C, st);
+        }
+    }
+    __syncthreads();
+}

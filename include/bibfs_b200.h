@@ -139,6 +139,8 @@ typedef struct {
     uint64_t vertices_visited;
     double   search_ms;      /* host variants: wall; device variants: cudaEvent search kernel */
     double   path_ms;
+    uint32_t levels_grid;    /* levels that needed the whole grid (grid top-down, hub phase, bottom-up) */
+    uint32_t levels_paired;  /* levels run by the pair tier (both directions per round)      */
 } bibfs_result;
 
 /* ------------------------------------------------------------------------------------------
@@ -184,9 +186,19 @@ typedef struct {
     uint32_t bottom_up_div;     /* go bottom-up when frontier > n/div (0 -> default, ~0u never) */
     uint32_t max_ctas;          /* cap on CTAs per rank (0 -> all SMs)                     */
     uint32_t watchdog_ms;       /* spin-loop timeout (0 -> default 4000)                   */
+    const void* d_vrec[BIBFS_MAX_RANKS];        /* per hosted rank: vertex records (bibfs_vrec_build_device) or NULL.
+                                                   With records, small searches run on the pair tier: both directions
+                                                   per round, one memory round trip per round                            */
 } bibfs_ctx_desc;
 
 uint32_t bibfs_block_size(uint32_t n, uint32_t nranks);
+
+/* Vertex records of a CSR shard: 32 bytes per row = {degree, row start (32 bits), first six neighbours}.
+ * d_vrec: bibfs_vrec_bytes(rows) bytes, 32-byte aligned; nnz = stored entries of the shard (< 2^32).
+ * No counterpart in the reference. */
+size_t bibfs_vrec_bytes(uint32_t rows);
+int bibfs_vrec_build_device(const uint64_t* d_row_ptr, const uint32_t* d_col, uint32_t rows, uint64_t nnz,
+                            void* d_vrec, void* stream);
 
 int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc);
 int bibfs_ctx_destroy(bibfs_ctx* ctx);
@@ -226,7 +238,7 @@ int bibfs_ctx_timing(bibfs_ctx* ctx, float* search_ms, float* path_ms);
 
 typedef struct {
     uint32_t side;       /* 0 = source side, 1 = target side                               */
-    uint32_t mode;       /* 0 solo top-down, 1 grid top-down, 2 bottom-up                   */
+    uint32_t mode;       /* 0 solo top-down, 1 grid top-down, 2 bottom-up; +8 hub phase; +16 paired round */
     uint32_t frontier;   /* global frontier vertices expanded at this level                 */
     uint32_t discovered; /* global vertices discovered                                      */
     uint64_t t_ns;       /* %globaltimer at the end of the level (rank-local)               */
