@@ -49,6 +49,15 @@ namespace bibfs {
 __device__ u64 g_dbg[256][8];
 __device__ u64 g_dbg2[256][8];
 __device__ u32 g_dbg_level;
+__device__ u64 g_kt[32];      // kernel-level stamps of the leader thread: entry, init done, tier entry / exit, path walk, end
+#define KT_STAMP(i)                                                                              \
+    do {                                                                                         \
+        if (blockIdx.x == 0 && threadIdx.x == 0) {                                               \
+            u64 _t;                                                                              \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t)::"memory");                     \
+            g_kt[i] = _t;                                                                        \
+        }                                                                                        \
+    } while (0)
 #define DBG_STAMP(slot, dep)                                                                     \
     do {                                                                                         \
         if (blockIdx.x == 0 && threadIdx.x == 0 && g_dbg_level < 256) {                          \
@@ -74,6 +83,7 @@ __device__ u32 g_dbg_level;
         }                                                                                        \
     } while (0)
 #else
+#define KT_STAMP(i) do { } while (0)
 #define DBG_STAMP3(slot, dep) do { } while (0)
 #define DBG_STAMP(slot, dep) do { } while (0)
 #define DBG_STAMP2(slot, dep) do { } while (0)
@@ -1642,6 +1652,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
     PairSmem& ps = *reinterpret_cast<PairSmem*>(smem_raw + sizeof(Smem));
+    KT_STAMP(0);
     LevelState& st = sm.st;        // this CTA's copy of the level state (the leader CTA's is authoritative)
     Acc& s_acc = sm.acc;           // leader CTA: accumulators of solo levels / staging at sync points
     u32& s_fail = sm.fail;
@@ -1715,7 +1726,9 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     // whenever the next phase needs the other CTAs.
     if (is_leader_cta) {
         if (warp == 0) {
+            KT_STAMP(1);
             const bool ok = leader_init<MULTI>(K, E, st, s_acc, deadline);
+            KT_STAMP(2);
             if (!ok && lane == 0) s_fail = 1;
             if (lane == 0) {   // the seeds are the first mirrored entries
                 const u32 src = C->q_src, dst = C->q_dst;     // as resolved by leader_init
@@ -1813,7 +1826,9 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
             }
             if (pair_first) {
                 pair_first = false;
+                KT_STAMP(3);
                 pair_run(K, E, sm, ps);
+                KT_STAMP(4);
                 if (st.phase != PH_TD_SOLO) { if (warp == 0) publish_and_wake(); __syncthreads(); continue; }
             }
             solo_run<MULTI>(K, E, sm, deadline);
@@ -1872,11 +1887,13 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     }
 
     // ---- single rank: the leader CTA reconstructs the path right here (one launch per query instead of two)
+    KT_STAMP(5);
     if (!MULTI && K.fuse_path && is_leader_cta) {
         __syncthreads();
         if (K.fuse_path == 2u) path_body(K);
         else result_to_host(K);
     }
+    KT_STAMP(6);
 
     // ---- cleanup for the next query: clear the visited bits this query set.  Every vertex a
     // single-rank search marked sits in a queue, so a small search clears exactly those words;
@@ -1893,6 +1910,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
             for (u32 i = gtid; i < n2; i += gthreads) p[i] = make_ulonglong2(0ull, 0ull);
         }
     }
+    KT_STAMP(7);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -2030,6 +2048,10 @@ extern "C" int bibfs_debug_read(uint64_t* out, uint32_t* levels) {
     cudaMemcpyFromSymbol(levels, g_dbg_level, 4);
     u32 z = 0;
     cudaMemcpyToSymbol(g_dbg_level, &z, 4);
+    return 0;
+}
+extern "C" int bibfs_debug_read_kt(uint64_t* out32) {
+    cudaMemcpyFromSymbol(out32, g_kt, sizeof(u64) * 32);
     return 0;
 }
 #endif

@@ -111,6 +111,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
             rb = ps.fr[side][buf][idx][1];
             deg = ra.x; r0 = ra.y;
         }
+        DBG_STAMP(0, u + deg);
         my_edges += deg;
         if (tracing && deg) ptx::reds_add(&ps.tr_edges[par][side], deg);
         u32* const out_v = ps.fv[side][buf ^ 1u];
@@ -136,6 +137,8 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
                 const bool act = (u32)k < nact;
                 old[k] = ptx::atom_or_gpu(act ? &g_vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
             }
+            DBG_STAMP(1, qb[W - 1].w);
+            DBG_STAMP(2, old[W - 1]);
             const u32 shz = sh + ptx::zero_after(old[W - 1]);      // == sh; pins the tests behind the whole batch
             u32 newmask = 0, meetmask = 0;
 #pragma unroll
@@ -148,6 +151,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
             u32 slot = 0;
             if (wide) slot = warp_reserve(nnew, [&](u32 n) { return ptx::atoms_add(cursor, n); });
             else if (nnew) slot = ptx::atoms_add(cursor, nnew);
+            DBG_STAMP(3, slot);
             if (newmask) {
 #pragma unroll
                 for (int k = 0; k < W; ++k) {
@@ -182,7 +186,9 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
             }
             if (fl) reds_or(&ps.flag[par], fl);
         }
+        DBG_STAMP(4, fl);
         __syncthreads();
+        DBG_STAMP(5, tid);
         // ---- round end: every thread derives the next state from the round's counters
         const u32 c0 = ps.cnt[par][0], c1 = ps.cnt[par][1], f = ps.flag[par], mnew = ps.meet_new[par];
         if (tid == 0) {
@@ -198,6 +204,10 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
         if (e0) { d0 += 1; levels += 1; base0 += c0; n0 = c0; buf0 ^= 1u; visited += c0; }
         if (e1) { d1 += 1; levels += 1; base1 += c1; n1 = c1; buf1 ^= 1u; visited += c1; }
         par = (par + 1u) % 3u;
+        DBG_STAMP(6, n0 + n1);
+#ifdef BIBFS_FINE_TRACE
+        if (blockIdx.x == 0 && threadIdx.x == 0) { if (g_dbg_level < 256) g_dbg[g_dbg_level][7] = ((u64)(e0 ? 1 : 0) | (e1 ? 2 : 0)) | ((u64)n0 << 8) | ((u64)n1 << 32); g_dbg_level++; }
+#endif
         if (f & PT_HIT) {
             length = (i32)(d0 + d1); meet = mnew; depth_s = d0;
             if (e0 && e1) {

@@ -72,13 +72,13 @@ def test_pair_tier_special_graphs_and_grid(bb):
                 bb.validate_path(g_cpu, s, t, r.path, want)
         solver.close()
     # a grid: the frontier outgrows the tier after a few hundred levels -> hand-over to the cluster / grid tiers
-    spec = bb.grid_spec(700, 500)
+    spec = bb.grid_spec(1500, 1300)
     g = bb.Graph.generate(spec, device="cuda:0")
     solver = bb.GpuSolver(g)
     r = solver.query(0, spec.n - 1)
-    assert r.length == 699 + 499 and r.levels_paired > 0 and r.levels > r.levels_paired
+    assert r.length == 1499 + 1299 and r.levels_paired > 0 and r.levels > r.levels_paired
     bb.validate_path(bb.Graph.generate(spec), 0, spec.n - 1, r.path, r.length)
-    r = solver.query(5, 5 + 700 * 3)
+    r = solver.query(5, 5 + 1500 * 3)
     assert r.length == 3
     solver.close()
 
