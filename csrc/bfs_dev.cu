@@ -499,12 +499,15 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
     u32 src = K.src, dst = K.dst;
     if (K.h_query) { src = *reinterpret_cast<const volatile u32*>(K.h_query); dst = *reinterpret_cast<const volatile u32*>(K.h_query + 1); }
     if (lane == 0) { C->q_src = src; C->q_dst = dst; }
+    // (the resets are dealt over the lanes: thirty-odd stores issued by one lane were a visible part of the start-up chain)
+    if (lane < BAR_WAYS) C->bar_way[lane].count = 0;
+    if (lane >= 16 && lane < 16 + MAXR) { C->sent[0][lane - 16] = 0; C->sent[1][lane - 16] = 0; }
+    if (lane < MAXR) { G.rq_lo[0][lane] = 0; G.rq_hi[0][lane] = 0; G.rq_lo[1][lane] = 0; G.rq_hi[1][lane] = 0; }
+    __syncwarp();
     if (lane == 0) {
-        for (u32 w = 0; w < BAR_WAYS; ++w) C->bar_way[w].count = 0;
         A.q_tail[0] = 0; A.q_tail[1] = 0;
         A.new_count = 0; A.meet_local = NO_V; A.edges = 0;
         C->hub_packed = 0;
-        for (u32 p = 0; p < MAXR; ++p) { C->sent[0][p] = 0; C->sent[1][p] = 0; }
         C->trace_count = 0;
         G.edges_total = 0; G.visited_total = 2;
         C->t_begin_ns = ptx::globaltimer_ns();
@@ -514,7 +517,6 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
         for (u32 s = 0; s < 2; ++s) {
             G.q_lo[s] = G.q_hi[s] = 0;
             G.fbm_cur[s] = 0; G.fbm_valid[s] = 0;
-            for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
         }
         G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 0; G.pad = 0; G.rounds_paired = 0; G.levels_grid = 0;
         G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
@@ -1690,7 +1692,13 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     u32 hub_parity = 0;            // phase bits of this warp's two hub barriers
     if (tid == 0) { sm.cl_seq = 0; sm.cl_cmd = 0; sm.cl_n = cl_n; }
     __syncthreads();
-    if (cl_n > 1) ptx::cluster_sync_all();     // the helpers may now poll the leader's command word
+    // the helpers may poll the leader's command word once the leader CTA has started.  The leader itself only ARRIVES
+    // here and collects the barrier when it first needs its cluster: the CTAs of a cluster start up to ~2 us apart
+    bool cl_pending = false;
+    if (cl_n > 1) {
+        if (is_leader_cta) { ptx::cluster_arrive(); cl_pending = true; }
+        else ptx::cluster_sync_all();
+    }
 
     // non-leader CTAs: copy the published level state global -> shared after a wake-up
     auto load_state = [&]() {
@@ -1831,6 +1839,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 KT_STAMP(4);
                 if (st.phase != PH_TD_SOLO) { if (warp == 0) publish_and_wake(); __syncthreads(); continue; }
             }
+            if (cl_pending) { ptx::cluster_wait(); cl_pending = false; }
             solo_run<MULTI>(K, E, sm, deadline);
             if (s_fail) { if (warp == 0) publish_and_wake(); __syncthreads(); alive = false; break; }
             if (warp == 0) publish_and_wake();      // left solo mode: the grid is needed (or the query is done)
@@ -1881,6 +1890,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
             alive = sync_grid(SYNC_LEVEL, PH_BU);
         }
     }
+    if (cl_pending) { ptx::cluster_wait(); cl_pending = false; }
     if (!alive) {         // aborted: the host must reset the context (it still gets the status word)
         if (!MULTI && K.fuse_path && is_leader_cta) { __syncthreads(); result_to_host(K); }
         return;
@@ -1952,18 +1962,19 @@ __device__ __noinline__ void path_body(const KParams& K) {
     }
     __syncthreads();
     static_assert(sizeof(Result) == PATH_HDR_WORDS * 4, "result header size");
-    if (threadIdx.x < PATH_HDR_WORDS) hdr[threadIdx.x] = reinterpret_cast<const u32*>(&R)[threadIdx.x];
-    // short answers go straight to the caller's pinned buffer (posted PCIe writes): the host only waits for the stream
-    if (K.h_out) {
+    // [result | path] goes to the device buffer and, when the path is short, straight to the caller's pinned buffer
+    // (posted PCIe writes).  Only the threads that wrote fence, once; the completion word follows behind that fence and
+    // needs none of its own (the host polls it, and the end of the kernel flushes it anyway).
+    const u32 plen = ok ? L + 1u : 0u;
+    const u32 words = PATH_HDR_WORDS + ((K.h_out && plen <= K.h_out_words) ? plen : 0u);
+    for (u32 i = threadIdx.x; i < words; i += blockDim.x) {
+        const u32 w = i < PATH_HDR_WORDS ? reinterpret_cast<const u32*>(&R)[i] : __ldcg(hdr + i);
+        if (i < PATH_HDR_WORDS) hdr[i] = w;
+        if (K.h_out) { K.h_out[i] = w; __threadfence_system(); }
+    }
+    if (K.h_out && K.h_seq) {
         __syncthreads();
-        const u32 plen = ok ? L + 1u : 0u;
-        const u32 words = PATH_HDR_WORDS + (plen <= K.h_out_words ? plen : 0u);
-        for (u32 i = threadIdx.x; i < words; i += blockDim.x) K.h_out[i] = hdr[i];
-        __threadfence_system();
-        if (K.h_seq) {               // completion word: the host may be polling it instead of waiting for the stream
-            __syncthreads();
-            if (threadIdx.x == 0) { *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq; __threadfence_system(); }
-        }
+        if (threadIdx.x == 0) *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq;
     }
 }
 
@@ -1973,7 +1984,7 @@ __device__ __noinline__ void result_to_host(const KParams& K) {
     if (!K.h_out) return;
     if (threadIdx.x < PATH_HDR_WORDS) { K.h_out[threadIdx.x] = reinterpret_cast<const u32*>(&R)[threadIdx.x]; __threadfence_system(); }
     __syncthreads();
-    if (threadIdx.x == 0 && K.h_seq) { *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq; __threadfence_system(); }
+    if (threadIdx.x == 0 && K.h_seq) *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq;
 }
 
 __global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) { path_body(K); }

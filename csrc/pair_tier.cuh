@@ -64,7 +64,6 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
     const uint4* const vrec = K.vrec[E.me];
     const u32* const g_col = E.col;
     u64* const g_vis = E.vis;
-    u64* const dummy = dummy_of(K, E.me);
     const u32 g_lo = E.lo;
     const bool tracing = (K.flags & BIBFS_F_TRACE) != 0;
     // level state, identical in every thread
@@ -128,14 +127,15 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
             u64 old[W];
 #pragma unroll
             for (int k = 0; k < W; ++k) {
-                const uint4* p = vrec + 2 * (size_t)(((u32)k < nact ? v[k] : u) - g_lo);
-                qa[k] = ld_rec(p);
-                qb[k] = ld_rec(p + 1);
+                const bool act = (u32)k < nact;
+                const uint4* p = vrec + 2 * (size_t)((act ? v[k] : u) - g_lo);
+                qa[k] = ptx::ld_v4_gpu_if(act, p);
+                qb[k] = ptx::ld_v4_gpu_if(act, p + 1);
             }
 #pragma unroll
             for (int k = 0; k < W; ++k) {
                 const bool act = (u32)k < nact;
-                old[k] = ptx::atom_or_gpu(act ? &g_vis[v[k] >> 5] : dummy, act ? (1ull << ((v[k] & 31u) + sh)) : 0ull);
+                old[k] = ptx::atom_or_gpu_if(act, &g_vis[(act ? v[k] : u) >> 5], 1ull << ((v[k] & 31u) + sh));
             }
             DBG_STAMP(1, qb[W - 1].w);
             DBG_STAMP(2, old[W - 1]);

@@ -76,6 +76,33 @@ __device__ __forceinline__ u64 atom_or_gpu(u64* p, u64 v) {
     asm volatile("atom.relaxed.gpu.global.or.b64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(v) : "memory");
     return old;
 }
+// Predicated forms for branch-free batches: the instruction is issued under a predicate (no branch, so the batch stays
+// one straight line of independent memory operations) and idle slots cost no memory transaction at all.
+// atom_or_gpu_if returns all ones when not executed ("already marked").
+__device__ __forceinline__ u64 atom_or_gpu_if(bool on, u64* p, u64 v) {
+    u64 old;
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.u32 q, %3, 0;\n\t"
+        "mov.u64 %0, 0xffffffffffffffff;\n\t"
+        "@q atom.relaxed.gpu.global.or.b64 %0, [%1], %2;\n\t}"
+        : "=&l"(old)
+        : "l"(p), "l"(v), "r"((u32)on)
+        : "memory");
+    return old;
+}
+__device__ __forceinline__ uint4 ld_v4_gpu_if(bool on, const uint4* p) {
+    uint4 r;
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.u32 q, %5, 0;\n\t"
+        "mov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\tmov.u32 %2, 0;\n\tmov.u32 %3, 0;\n\t"
+        "@q ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+        : "=&r"(r.x), "=&r"(r.y), "=&r"(r.z), "=&r"(r.w)
+        : "l"(p), "r"((u32)on)
+        : "memory");
+    return r;
+}
 __device__ __forceinline__ void red_or_sys(u32* p, u32 v) {
     asm volatile("red.relaxed.sys.global.or.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -169,6 +196,10 @@ __device__ __forceinline__ u32 cluster_nctarank() {
     asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
     return r;
 }
+// split form: the leader CTA of a query arrives at kernel start and collects the barrier only when it first needs
+// its cluster (the other CTAs of a cluster start up to ~2 us after the first one)
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
