@@ -23,7 +23,8 @@ MAX_RANKS = 8
 NO_VERTEX = 0xFFFFFFFF
 
 # query flags (bibfs_b200.h)
-F_TRACE, F_FORCE_GRID, F_FORCE_TD, F_FORCE_BU, F_NO_PATH, F_DEVICE_CLOCK = 1, 2, 4, 8, 16, 32
+F_TRACE, F_FORCE_GRID, F_FORCE_TD, F_FORCE_BU, F_NO_PATH, F_DEVICE_CLOCK, F_NO_FRONT = 1, 2, 4, 8, 16, 32, 64
+STATUS_HANDED_OVER = 100
 
 
 class GenSpec(C.Structure):
@@ -112,6 +113,10 @@ def _declare(lib):
         "bibfs_ctx_attach_local": (C.c_int, [vp, u32, vp]),
         "bibfs_ctx_arena_bytes": (C.c_size_t, [vp]),
         "bibfs_ctx_reset": (C.c_int, [vp, vp]),
+        "bibfs_ctx_set_peer_graph": (C.c_int, [vp, u32, vp, vp]),
+        "bibfs_ctx_resume": (C.c_int, [vp, vp]),
+        "bibfs_ipc_export": (C.c_int, [vp, vp, P(u64)]),
+        "bibfs_ipc_import": (C.c_int, [vp, u64, P(vp)]),
         "bibfs_ctx_query": (C.c_int, [vp, u32, u32, vp, u32, vp]),
         "bibfs_ctx_result": (C.c_int, [vp, P(Result), vp, u32, vp]),
         "bibfs_ctx_query_result": (C.c_int, [vp, u32, u32, vp, u32, P(Result), vp, u32, vp]),

@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 import torch
 
-from .._lib import F_DEVICE_CLOCK, F_NO_PATH, Result, check, lib
+from .._lib import F_DEVICE_CLOCK, F_NO_PATH, STATUS_HANDED_OVER, Result, check, lib
 from ..graph import Graph
 from ..ops.search import PathResult, SearchContext, result_from_c
 
@@ -153,6 +153,16 @@ class MultiGpuSolver:
         for i, c in enumerate(self.ctxs):
             with torch.cuda.device(c.device):
                 r = c.fetch(src, dst, want_path and i == 0, self.variant)
+            if i == 0 and r.status == STATUS_HANDED_OVER:
+                # several devices driven by this process: rank 0's front kernel handed the search over, every context
+                # continues it in the general kernel
+                for c2 in self.ctxs:
+                    with torch.cuda.device(c2.device):
+                        c2.resume()
+                with torch.cuda.device(c.device):
+                    r = c.fetch(src, dst, want_path, self.variant)
+            elif i > 0 and r.status == STATUS_HANDED_OVER:
+                continue            # rank 0 answered alone: this context launched nothing
             if res is None:
                 res = r
             else:   # device time = max over ranks

@@ -34,6 +34,7 @@ class PathResult:
     variant: str = ""
     levels_grid: int = 0         # levels that needed the whole grid
     levels_paired: int = 0       # levels run by the pair tier (both directions per round)
+    status: int = 0
 
     @property
     def found(self) -> bool:
@@ -99,6 +100,35 @@ class SearchContext:
     def attach_local(self, rank: int, owner: "SearchContext") -> None:
         check(lib().bibfs_ctx_attach_local(self._h, rank, owner._h))
 
+    def graph_ipc(self, slot=0) -> tuple:
+        """(handle, offset) pairs of hosted rank `slot`'s col and vertex-record tensors for the other processes of the group
+        (None where there is nothing to share): with them rank 0's front kernel reads every shard through peer mappings."""
+        s = self.graph.shards[self.rank_lo + slot]
+        out = []
+        for t in (s.col if s.col.numel() else None, s.vrec):
+            if t is None:
+                out.append(None)
+                continue
+            buf, off = C.create_string_buffer(64), C.c_uint64(0)
+            with torch.cuda.device(self.device):
+                check(lib().bibfs_ipc_export(t.data_ptr(), buf, C.byref(off)))
+            out.append((buf.raw, int(off.value)))
+        return tuple(out)
+
+    def attach_graph_ipc(self, rank: int, shared: tuple) -> None:
+        ptrs = []
+        with torch.cuda.device(self.device):
+            for item in shared:
+                p = C.c_void_p(0)
+                if item is not None:
+                    check(lib().bibfs_ipc_import(C.create_string_buffer(item[0], 64), item[1], C.byref(p)))
+                ptrs.append(p)
+        if ptrs[0].value and ptrs[1].value:
+            check(lib().bibfs_ctx_set_peer_graph(self._h, rank, ptrs[0], ptrs[1]))
+
+    def resume(self) -> None:
+        check(lib().bibfs_ctx_resume(self._h, self._stream()))
+
     @property
     def arena_bytes(self) -> int:
         return int(lib().bibfs_ctx_arena_bytes(self._h))
@@ -119,7 +149,9 @@ class SearchContext:
         r = Result()
         check(lib().bibfs_ctx_result(self._h, C.byref(r), self._path.ctypes.data if want_path else None,
                                      self.max_path if want_path else 0, self._stream()))
-        return result_from_c(src, dst, r, self._path, variant)
+        out = result_from_c(src, dst, r, self._path, variant)
+        out.status = int(r.status)
+        return out
 
     def query(self, src, dst, flags=0, want_path=True, pinned_query=None, variant="gpu") -> PathResult:
         if _NVTX:       # BIBFS_NVTX=1: NVTX range per query for nsys timelines

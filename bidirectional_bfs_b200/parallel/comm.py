@@ -55,6 +55,13 @@ class DistributedSolver:
             for r, h in enumerate(handles):
                 if r != self.rank:
                     self.ctx.attach_ipc(r, h)
+            # the graph itself: col + vertex records of every shard mapped on every device, so that rank 0's front kernel
+            # can answer small queries alone (csrc/front.cuh)
+            shared = [None] * self.world
+            dist.all_gather_object(shared, self.ctx.graph_ipc(0))
+            for r, sh in enumerate(shared):
+                if r != self.rank:
+                    self.ctx.attach_graph_ipc(r, sh)
         dist.barrier()
 
     def launch(self, src, dst, flags=0, pinned_query=None):

@@ -102,6 +102,11 @@ constexpr u32 HUB_CHUNK = 256;    // adjacency entries per hub work item (1 KB: 
 // so that every chunk starts on a 16-byte boundary (cp.async.bulk requirement)
 BIBFS_HD u32 hub_nchunks(u64 r0, u64 r1) { return (u32)((r1 - (r0 & ~3ull) + HUB_CHUNK - 1) / HUB_CHUNK); }
 constexpr u32 BAR_WAYS = 16;
+// verdict of the front kernel, one tagged word per field
+enum : u32 { VD_KIND = 0, VD_LENGTH, VD_MEET, VD_D0, VD_D1, VD_LEVELS, VD_NF0, VD_NF1, VD_SENT0, VD_SENT1, VD_EDGES_LO, VD_EDGES_HI,
+             VD_VIS_LO, VD_VIS_HI, VD_PAIRED, VD_STATUS, VD_WORDS };
+enum : u32 { VK_DONE = 1, VK_HANDOVER = 2 };
+constexpr i32 ST_ESCALATED = 100;    // Result::status of a front kernel that handed the search over (never reaches the caller)
 constexpr u32 PATH_HDR_WORDS = 16;   // sizeof(Result) / 4
 constexpr u32 HUB_CAP = 16384;          // hub entries per level per rank (overflow: expanded in place)
 constexpr u32 DUMMY_WORDS = 512 * 512;   // one private scratch word per thread of up to 512 CTAs: target of no-op atomics
@@ -122,6 +127,9 @@ struct Ctrl {
     unsigned long long hub_packed;       // (entries << 40) | chunks, appended atomically
     u32 sent[2][MAXR];
     unsigned long long edges_total;
+    // front kernel (k_front) <-> peers: see "query flow" in bfs_dev.cu
+    alignas(128) u64 arrive[MAXR];       // at rank 0: arrive[p] = queries rank p has entered (one process per GPU only)
+    alignas(128) u64 verdict[2][VD_WORDS];   // written by rank 0: payload | (u32)query number << 32, [query number & 1]
     // persisted across launches
     alignas(128) u64 xepoch;
     u32 abort_flag;
@@ -133,6 +141,7 @@ struct Ctrl {
 
 struct Layout {
     size_t off_vis, off_fbm, off_parent, off_q, off_rq, off_path, off_trace, off_hub, off_dummy, total;
+    size_t off_log, off_pall, total0;   // P > 1, rank 0 only: log of the vertices its front kernel reached and their parents (all vertices)
     u32 nw;           // bitmap words covering P*B vertices
 };
 
@@ -151,6 +160,9 @@ inline Layout make_layout(u32 B, u32 P, u32 max_path) {
     L.off_hub = o;    o += al((size_t)HUB_CAP * sizeof(HubEntry));
     L.off_dummy = o;  o += al((size_t)DUMMY_WORDS * 8);
     L.total = o;
+    L.off_log = o;    o += (P > 1) ? al((size_t)B * P * 4 * 2) : 0;
+    L.off_pall = o;   o += (P > 1) ? al((size_t)B * P * 4 * 2) : 0;
+    L.total0 = o;
     return L;
 }
 
@@ -164,6 +176,9 @@ struct KParams {
     u32 fuse_path;                 // single rank, work of the leader CTA at the end of the search kernel: 0 nothing, 1 copy the result to h_out,
                                    // 2 walk the parent chains first (no path kernel)
     u32 src, dst, query_in_ctrl;   // query by value, or (query_in_ctrl) read from Ctrl::q_src/q_dst
+    u32 resume;                    // k_bibfs continues a search the front kernel handed over (no query start)
+    u32 async_peers;               // the other ranks are driven by other processes: arrival words order the queries
+    u64 qn;                        // number of this query in the context group (host counter, identical on every rank)
     u64 div_B;                     // 2^64 / B rounded up: owner(v) = umulhi64(div_B, v), exact for 32-bit v
     const u32* h_query;            // pinned host memory holding {src,dst}: read by the kernel itself (zero copy), or null
     u32* h_out;                    // pinned host buffer [Result | first path entries] written by the path kernel, or null
@@ -182,7 +197,9 @@ int bfs_max_ctas_per_device(bool multi, int* out);
 int bfs_max_ctas_clustered(u32 cluster, int* out);
 #if defined(__CUDACC__) || defined(BIBFS_WITH_CUDA_RUNTIME)
 int bfs_launch(const KParams& K, bool multi, cudaStream_t st);
-int path_launch(const KParams& K, cudaStream_t st);
+int front_launch(const KParams& K, bool multi, cudaStream_t st);
+int wait_launch(const KParams& K, cudaStream_t st);
+int front_prepare(bool multi);
 #endif
 
 }  // namespace bibfs

@@ -90,6 +90,7 @@ __device__ u64 g_kt[32];      // kernel-level stamps of the leader thread: entry
 #endif
 
 __device__ __noinline__ void path_body(const KParams& K);   // defined with the path kernel below
+__device__ __noinline__ void path_body_local(const KParams& K, const u32* par0, const u32* par1);
 __device__ __noinline__ void result_to_host(const KParams& K);
 
 namespace {
@@ -499,6 +500,7 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
     u32 src = K.src, dst = K.dst;
     if (K.h_query) { src = *reinterpret_cast<const volatile u32*>(K.h_query); dst = *reinterpret_cast<const volatile u32*>(K.h_query + 1); }
     if (lane == 0) { C->q_src = src; C->q_dst = dst; }
+    if (MULTI && K.async_peers && E.me != 0 && lane == 0) ptx::st_relaxed_sys(&ctrl_of(K, 0)->arrive[E.me], K.qn);
     // (the resets are dealt over the lanes: thirty-odd stores issued by one lane were a visible part of the start-up chain)
     if (lane < BAR_WAYS) C->bar_way[lane].count = 0;
     if (lane >= 16 && lane < 16 + MAXR) { C->sent[0][lane - 16] = 0; C->sent[1][lane - 16] = 0; }
@@ -551,6 +553,47 @@ __device__ __noinline__ bool leader_init(const KParams& K, const Env& E, LevelSt
     if (lane == 0) {
         if (!ok) { atomicExch(&C->abort_flag, 1u); G.status = 1; G.phase = PH_DONE; }
         if (G.phase != PH_DONE) decide_next(K, G);
+        if (G.phase == PH_DONE) write_result(K, C, G);
+    }
+    __syncwarp();
+    return ok;
+}
+
+// Query continuation (KParams::resume): the front kernel (front.cuh) started the query and handed it over.  Rank 0 finds
+// its level state in Ctrl::st, the other ranks theirs in the verdict rank 0 sent them.  Leader warp of each rank.
+__device__ bool wait_verdict(Ctrl* C, u64 qn, u32* out, u64 deadline);
+__device__ void state_from_verdict(const KParams& K, LevelState& G, const u32* v, u32 tag);
+
+template <bool MULTI>
+__device__ __noinline__ bool leader_resume(const KParams& K, const Env& E, LevelState& G, Acc& A, u64 deadline) {
+    Ctrl* C = E.C;
+    const u32 lane = threadIdx.x & 31;
+    if (lane < BAR_WAYS) C->bar_way[lane].count = 0;
+    bool ok = true;
+    if (E.me == 0) {
+        const u32* g = reinterpret_cast<const u32*>(&C->st);
+        u32* s = reinterpret_cast<u32*>(&G);
+        for (u32 i = lane; i < sizeof(LevelState) / 4; i += 32) s[i] = __ldcg(g + i);
+        if (lane == 0) { pull_acc(A, &C->acc); C->hub_packed = 0; }
+    } else if (MULTI) {
+        u32 v[VD_WORDS];
+        ok = wait_verdict(C, K.qn, v, deadline);
+        if (lane == 0) ptx::fence_sys();        // the hand-over's bits and parents were fenced before the verdict was sent
+        if (lane < MAXR) { C->sent[0][lane] = 0; C->sent[1][lane] = 0; }
+        if (lane == 0) {
+            const u64 xe = C->xepoch + 1;
+            state_from_verdict(K, G, v, (u32)xe);
+            G.xepoch = xe;
+            A.q_tail[0] = 0; A.q_tail[1] = 0; A.new_count = 0; A.meet_local = NO_V; A.edges = 0;
+            C->hub_packed = 0; C->trace_count = 0;
+            if (!K.async_peers) C->t_begin_ns = ptx::globaltimer_ns();
+            C->q_src = NO_V; C->q_dst = NO_V;
+        }
+    }
+    __syncwarp();
+    if (lane == 0) {
+        if (!ok) { atomicExch(&C->abort_flag, 1u); G.status = 1; G.length = -1; G.phase = PH_DONE; }
+        else decide_next(K, G);
         if (G.phase == PH_DONE) write_result(K, C, G);
     }
     __syncwarp();
@@ -1735,10 +1778,10 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     if (is_leader_cta) {
         if (warp == 0) {
             KT_STAMP(1);
-            const bool ok = leader_init<MULTI>(K, E, st, s_acc, deadline);
+            const bool ok = K.resume ? leader_resume<MULTI>(K, E, st, s_acc, deadline) : leader_init<MULTI>(K, E, st, s_acc, deadline);
             KT_STAMP(2);
             if (!ok && lane == 0) s_fail = 1;
-            if (lane == 0) {   // the seeds are the first mirrored entries
+            if (lane == 0 && !K.resume) {   // the seeds are the first mirrored entries
                 const u32 src = C->q_src, dst = C->q_dst;     // as resolved by leader_init
                 if (s_acc.q_tail[0] == 1) { s_q[0][0][0] = src; s_qvalid[0] = 1; }
                 if (s_acc.q_tail[1] == 1) { s_q[1][0][0] = dst; s_qvalid[1] = 1; }
@@ -1748,7 +1791,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
         }
         __syncthreads();
     } else {
-        if (K.warm_lines && E.cpr > 1) {
+        if (!MULTI && K.warm_lines && E.cpr > 1) {
             // the graph fits L2 with room to spare: the CTAs that would only wait stream the vertex records and the
             // visited words into L2 while the leader runs the first rounds (they were evicted since the last query
             // whenever anything else used the GPU; a cold record costs ~700 ns on the leader's chain, a hit 154 ns)
@@ -1766,7 +1809,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     }
     bool alive = (s_fail == 0);
     // latency tier first (leader CTA): paired rounds on vertex records, while both frontiers are small
-    bool pair_first = !MULTI && K.vrec[E.me] != nullptr && !(K.flags & (BIBFS_F_FORCE_GRID | BIBFS_F_FORCE_BU));
+    bool pair_first = !MULTI && !K.resume && K.vrec[E.me] != nullptr && !(K.flags & (BIBFS_F_FORCE_GRID | BIBFS_F_FORCE_BU));
 
     // Synchronisation point of grid-mode phases.  Returns false if the query was aborted.
     auto sync_grid = [&](int kind, u32 mode) -> bool {
@@ -1835,7 +1878,11 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
             if (pair_first) {
                 pair_first = false;
                 KT_STAMP(3);
-                pair_run(K, E, sm, ps);
+                {
+                    PairIO io;
+                    io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
+                    pair_run<false>(K, E, st, s_acc, s_qvalid, ps, io, C->q_src, C->q_dst);
+                }
                 KT_STAMP(4);
                 if (st.phase != PH_TD_SOLO) { if (warp == 0) publish_and_wake(); __syncthreads(); continue; }
             }
@@ -1892,13 +1939,15 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
     }
     if (cl_pending) { ptx::cluster_wait(); cl_pending = false; }
     if (!alive) {         // aborted: the host must reset the context (it still gets the status word)
-        if (!MULTI && K.fuse_path && is_leader_cta) { __syncthreads(); result_to_host(K); }
+        if (K.fuse_path && is_leader_cta && E.me == 0) { __syncthreads(); result_to_host(K); }
         return;
     }
 
-    // ---- single rank: the leader CTA reconstructs the path right here (one launch per query instead of two)
+    // ---- rank 0's leader CTA reconstructs the path right here (one launch per query instead of two); with several ranks it
+    // walks owner to owner through the peer mappings — every rank has passed the final fenced exchange, and no rank writes
+    // parents again before rank 0's NEXT query hands over, which comes after this kernel
     KT_STAMP(5);
-    if (!MULTI && K.fuse_path && is_leader_cta) {
+    if (K.fuse_path && is_leader_cta && E.me == 0) {
         __syncthreads();
         if (K.fuse_path == 2u) path_body(K);
         else result_to_host(K);
@@ -1928,8 +1977,9 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
 // (reference: v1/main-v1.cpp:86-97 walks on the host; v2/v4 re-run a whole serial BFS,
 //  v2/second_try.cpp:137-162, v4/mpi_bas.cpp:141-164)
 // ------------------------------------------------------------------------------------------
-// whole CTA (any size >= 64 threads)
-__device__ __noinline__ void path_body(const KParams& K) {
+// whole CTA (any size >= 64 threads).  par0 / par1: parent arrays indexed by the vertex id (front kernel), or null:
+// look the parent up at the vertex's owner
+static __device__ __forceinline__ void path_body_impl(const KParams& K, const u32* par0, const u32* par1) {
     Ctrl* C = ctrl_of(K, K.rank_lo);
     Result& R = C->res;
     u32* hdr = reinterpret_cast<u32*>(K.arena[K.rank_lo] + K.L.off_path);   // [copy of Result | path]
@@ -1943,14 +1993,14 @@ __device__ __noinline__ void path_body(const KParams& K) {
         for (u32 pos = ds;; --pos) {
             path[pos] = cur;
             if (pos == 0 || cur >= K.n) break;
-            const u32 o = owner_of(K, cur);
-            cur = __ldcg(parent_of(K, o, 0) + (cur - o * K.B));
+            if (par0) cur = __ldcg(par0 + cur);
+            else { const u32 o = owner_of(K, cur); cur = __ldcg(parent_of(K, o, 0) + (cur - o * K.B)); }
         }
     } else if (ok && threadIdx.x == 32) {
         u32 cur = R.meet;
         for (u32 pos = ds; pos < L && cur < K.n; ++pos) {
-            const u32 o = owner_of(K, cur);
-            cur = __ldcg(parent_of(K, o, 1) + (cur - o * K.B));
+            if (par1) cur = __ldcg(par1 + cur);
+            else { const u32 o = owner_of(K, cur); cur = __ldcg(parent_of(K, o, 1) + (cur - o * K.B)); }
             path[pos + 1] = cur;
         }
     }
@@ -1978,6 +2028,9 @@ __device__ __noinline__ void path_body(const KParams& K) {
     }
 }
 
+__device__ __noinline__ void path_body(const KParams& K) { path_body_impl(K, nullptr, nullptr); }
+__device__ __noinline__ void path_body_local(const KParams& K, const u32* par0, const u32* par1) { path_body_impl(K, par0, par1); }
+
 // no path wanted: only the 64-byte result goes to the host (whole CTA)
 __device__ __noinline__ void result_to_host(const KParams& K) {
     const Result& R = ctrl_of(K, K.rank_lo)->res;
@@ -1987,7 +2040,7 @@ __device__ __noinline__ void result_to_host(const KParams& K) {
     if (threadIdx.x == 0 && K.h_seq) *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq;
 }
 
-__global__ void __launch_bounds__(64) k_path(const __grid_constant__ KParams K) { path_body(K); }
+#include "front.cuh"
 
 // ------------------------------------------------------------------------------------------
 // launch helpers used by ctx.cu
@@ -2067,8 +2120,24 @@ extern "C" int bibfs_debug_read_kt(uint64_t* out32) {
 }
 #endif
 
-int path_launch(const KParams& K, cudaStream_t st) {
-    k_path<<<1, 64, 0, st>>>(K);
+constexpr unsigned FRONT_WARM_CTAS = 48;
+
+int front_prepare(bool multi) {
+    if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_front<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrontSmem)));
+    else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_front<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrontSmem)));
+    return 0;
+}
+
+int front_launch(const KParams& K, bool multi, cudaStream_t st) {
+    const unsigned grid = K.warm_lines ? 1u + FRONT_WARM_CTAS : 1u;      // CTA 0 runs the query; the others only warm L2
+    if (multi) k_front<true><<<grid, BFS_THREADS, sizeof(FrontSmem), st>>>(K);
+    else k_front<false><<<grid, BFS_THREADS, sizeof(FrontSmem), st>>>(K);
+    BIBFS_KERNEL_CHECK();
+    return 0;
+}
+
+int wait_launch(const KParams& K, cudaStream_t st) {
+    k_wait<<<1, 32, 0, st>>>(K);
     BIBFS_KERNEL_CHECK();
     return 0;
 }

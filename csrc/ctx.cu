@@ -26,14 +26,20 @@ struct bibfs_ctx {
     u32 seq = 0;
     u32 cpr = 0;
     u32 cluster = 1;
-    // launch geometry (single rank, clustered): a query that never needs the grid is launched as ONE cluster (its
-    // launch + teardown costs less than half of the 148-CTA cooperative launch); `grid_score` follows the recent
-    // queries' levels_grid and moves the context to the full grid when the graph keeps asking for it
-    u32 cpr_small = 0;
-    int grid_score = 0;
-    int geometry = 0;            // 0 auto, 1 always small, 2 always full (BIBFS_GEOMETRY)
-    bool last_small = false;
-    bool has_vrec = false;
+    u32 cpr_small = 0;           // BIBFS_GEOMETRY=small: launch the general kernel as one cluster (measured: no gain, kept as a switch)
+    int geometry = 0;
+    // ---- query flow (front.cuh): front kernel first, general kernel only when the front kernel hands the search over
+    const u32* col_all[MAXR] = {};       // every rank's adjacency / vertex records as seen from this device
+    const void* vrec_all[MAXR] = {};
+    bool hosts0 = false;         // this context hosts rank 0 (runs the front kernel, walks the path, delivers the result)
+    bool hosts_all = false;      // ... and every other rank too (single rank, or virtual ranks)
+    bool async_peers = false;    // peers live in other processes (attached through IPC): each rank resumes on its own verdict
+    int front_mode = 0;          // BIBFS_FRONT: 0 policy, 1 always, 2 never
+    int front_score = 0;         // policy: rises when the front kernel hands over after a few levels (hub graphs), falls otherwise
+    u64 qn = 0;                  // queries issued (identical on every rank of the group)
+    int stage = 0;               // what the last bibfs_ctx_query launched: 0 general kernel, 1 front kernel / wait kernel, 2 nothing yet (sync peer)
+    u32 pend_src = 0, pend_dst = 0, pend_flags = 0;
+    const u32* pend_hq = nullptr;
     bool last_fused = false;     // the last query wrote its result (and path) to h_stage from inside the search kernel
     bool last_lean = false;      // ... and was launched without events (BIBFS_F_DEVICE_CLOCK)
     u32* h_seq = nullptr;        // completion word inside h_stage
@@ -113,11 +119,16 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     }
 
     if (const char* g = getenv("BIBFS_GEOMETRY")) c->geometry = !strcmp(g, "small") ? 1 : !strcmp(g, "full") ? 2 : 0;
-    c->has_vrec = desc->d_vrec[0] != nullptr;
+    if (const char* f = getenv("BIBFS_FRONT")) c->front_mode = !strcmp(f, "1") ? 1 : !strcmp(f, "0") ? 2 : 0;
+    c->hosts0 = desc->rank_lo == 0;
+    c->hosts_all = desc->vranks == desc->nranks;
+    for (u32 i = 0; i < desc->vranks; ++i) { c->col_all[desc->rank_lo + i] = desc->d_col[i]; c->vrec_all[desc->rank_lo + i] = desc->d_vrec[i]; }
+    if (c->hosts0 && front_prepare(c->multi)) { delete c; return 1; }
     for (u32 i = 0; i < desc->vranks; ++i)
         if (reinterpret_cast<uintptr_t>(desc->d_vrec[i]) & 31u) { delete c; return fail("d_vrec of hosted rank %u is not 32-byte aligned", desc->rank_lo + i); }
     for (u32 i = 0; i < desc->vranks; ++i) {
-        cudaError_t e = cudaMalloc((void**)&c->arena_local[i], c->L.total);
+        const size_t bytes = (desc->rank_lo + i == 0) ? c->L.total0 : c->L.total;     // rank 0 also holds the front kernel's log
+        cudaError_t e = cudaMalloc((void**)&c->arena_local[i], bytes);
         if (e == cudaSuccess) e = cudaMemset(c->arena_local[i], 0, zero_prefix(c->L));
         if (e != cudaSuccess) {
             for (u32 j = 0; j <= i; ++j) if (c->arena_local[j]) cudaFree(c->arena_local[j]);
@@ -173,6 +184,7 @@ extern "C" int bibfs_ctx_attach_ipc(bibfs_ctx* c, uint32_t rank, const void* han
     BIBFS_CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
     c->arena_all[rank] = (char*)p;
     c->ipc_opened[rank] = true;
+    c->async_peers = true;
     return 0;
 }
 
@@ -189,12 +201,23 @@ extern "C" int bibfs_ctx_attach_local(bibfs_ctx* c, uint32_t rank, bibfs_ctx* ow
         cudaGetLastError();
     }
     c->arena_all[rank] = owner->arena_local[rank - owner->d.rank_lo];
+    c->col_all[rank] = owner->d.d_col[rank - owner->d.rank_lo];
+    c->vrec_all[rank] = owner->d.d_vrec[rank - owner->d.rank_lo];
+    return 0;
+}
+
+extern "C" int bibfs_ctx_set_peer_graph(bibfs_ctx* c, uint32_t rank, const uint32_t* d_col, const void* d_vrec) {
+    if (!c || rank >= c->d.nranks) return fail("bad rank");
+    if (reinterpret_cast<uintptr_t>(d_vrec) & 31u) return fail("d_vrec must be 32-byte aligned");
+    c->col_all[rank] = d_col;
+    c->vrec_all[rank] = d_vrec;
     return 0;
 }
 
 extern "C" int bibfs_ctx_reset(bibfs_ctx* c, void* stream) {
     if (!c) return fail("NULL ctx");
     DeviceGuard g(c->device);
+    c->qn = 0;
     for (u32 i = 0; i < c->d.vranks; ++i)
         BIBFS_CUDA_TRY(cudaMemsetAsync(c->arena_local[i], 0, zero_prefix(c->L), (cudaStream_t)stream));
     return 0;
@@ -205,11 +228,7 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     K.n = c->d.n; K.B = c->B; K.P = c->d.nranks;
     K.rank_lo = c->d.rank_lo; K.vranks = c->d.vranks; K.cpr = c->cpr;
     K.cluster = c->cluster;
-    c->last_small = false;
-    if (c->cpr_small && c->cpr_small < c->cpr && c->geometry != 2 && (c->geometry == 1 || c->grid_score < 4)) {
-        K.cpr = c->cpr_small;
-        c->last_small = true;
-    }
+    if (c->cpr_small && c->cpr_small < c->cpr && c->geometry == 1) K.cpr = c->cpr_small;
     K.solo_threshold = c->d.solo_threshold;
     K.bu_div = c->d.bottom_up_div;
     K.flags = flags;
@@ -224,10 +243,41 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     for (u32 i = 0; i < c->d.vranks; ++i) {
         K.row_ptr[c->d.rank_lo + i] = c->d.d_row_ptr[i];
         K.col[c->d.rank_lo + i] = c->d.d_col[i];
-        K.vrec[c->d.rank_lo + i] = reinterpret_cast<const uint4*>(c->d.d_vrec[i]);
     }
+    for (u32 r = 0; r < c->d.nranks; ++r) {
+        K.col[r] = c->col_all[r];
+        K.vrec[r] = reinterpret_cast<const uint4*>(c->vrec_all[r]);
+    }
+    K.qn = c->qn;
+    K.async_peers = c->async_peers ? 1u : 0u;
     // records + visited words of a small graph are streamed into L2 by the idle CTAs at query start (<= 24 MB: a fifth of L2)
-    if (c->has_vrec && !c->multi && c->d.vranks == 1 && (u64)c->B * 32ull <= (24ull << 20)) K.warm_lines = (u32)(((u64)c->d.n * 32ull + 127ull) / 128ull);
+    if (c->vrec_all[0] && c->hosts0 && (u64)c->B * 32ull <= (24ull << 20)) K.warm_lines = (u32)(((u64)(c->multi ? c->B : c->d.n) * 32ull + 127ull) / 128ull);
+}
+
+// Does this query start with the front kernel?  Needs every rank's vertex records on this device.  Policy (contexts that
+// host every rank or whose peers decide alike — they see the same verdicts): hand-overs after fewer than eight levels
+// (graphs with hub rows next to almost every vertex) push the score up, everything else pulls it down; at 4 the context
+// goes straight to the general kernel and looks at the front kernel again every 32nd query.  Contexts of a single
+// process spanning several devices (peers attached locally) leave the choice to the caller (BIBFS_F_NO_FRONT).
+static bool use_front(const bibfs_ctx* c, u32 flags) {
+    if (flags & (BIBFS_F_NO_FRONT | BIBFS_F_FORCE_GRID | BIBFS_F_FORCE_BU)) return false;
+    for (u32 r = 0; r < c->d.nranks; ++r)
+        if (!c->vrec_all[r] || !c->col_all[r]) return false;
+    if (c->front_mode) return c->front_mode == 1;
+    if (!c->hosts_all && !c->async_peers) return true;
+    return c->front_score < 4 || (c->qn & 31u) == 0;
+}
+
+static int launch_general(bibfs_ctx* c, KParams& K, bool want_path, bool resume, cudaStream_t st) {
+    K.resume = resume ? 1u : 0u;
+    const bool lean = c->last_lean;
+    c->last_fused = c->hosts0 && (want_path || lean || c->multi || resume);
+    K.fuse_path = c->last_fused ? (want_path ? 2u : 1u) : 0u;
+    if (c->last_fused) { K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = HOST_PATH_WORDS; K.h_seq = c->h_seq; }
+    else { K.h_out = nullptr; K.h_out_words = 0; K.h_seq = nullptr; }
+    if (bfs_launch(K, c->multi, st)) return 1;
+    if (!lean) BIBFS_CUDA_TRY(cudaEventRecord(c->ev[1], st));
+    return 0;
 }
 
 extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const uint32_t* h_query_pinned,
@@ -238,39 +288,55 @@ extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const u
         if (!c->arena_all[r]) return fail("rank %u is not attached", r);
     DeviceGuard g(c->device);
     cudaStream_t st = (cudaStream_t)stream;
+    c->qn += 1;
     KParams K;
     fill_params(c, K, src, dst, false, flags);
     K.h_query = h_query_pinned;          // read by the kernel itself: pinned memory is device-visible under UVA
     const bool want_path = !(flags & BIBFS_F_NO_PATH);
-    const bool single = !c->multi && c->d.vranks == 1;
-    if (want_path || single) { K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = HOST_PATH_WORDS; }
-    // one rank: the search kernel's leader CTA walks the parent chains itself and writes [result | path] into the
-    // pinned staging buffer, followed by a completion word: a query is ONE launch and the host need not wait for
-    // the stream to drain
-    c->last_lean = single && (flags & BIBFS_F_DEVICE_CLOCK);
-    c->last_fused = single && (want_path || c->last_lean);      // event-timed searches without a path: plain D2H copy of the result
-    K.fuse_path = c->last_fused ? (want_path ? 2u : 1u) : 0u;
-    K.h_seq = c->last_fused ? c->h_seq : nullptr;
+    c->last_lean = c->hosts_all && !c->multi && (flags & BIBFS_F_DEVICE_CLOCK);
     c->last_flags = flags;
+    c->pend_src = src; c->pend_dst = dst; c->pend_flags = flags; c->pend_hq = h_query_pinned;
     if (!c->last_lean) BIBFS_CUDA_TRY(cudaEventRecord(c->ev[0], st));
-    if (bfs_launch(K, c->multi, st)) return 1;
-    if (!c->last_lean) BIBFS_CUDA_TRY(cudaEventRecord(c->ev[1], st));
-    if (want_path && !c->last_fused) {
-        if (path_launch(K, st)) return 1;
-        BIBFS_CUDA_TRY(cudaEventRecord(c->ev[2], st));
+    if (use_front(c, flags)) {
+        // ---- front kernel on the context that hosts rank 0; a wait kernel on peers in other processes; nothing on peers of
+        // the same process (their caller resumes them with bibfs_ctx_resume when rank 0's context reports a hand-over)
+        c->stage = 1;
+        if (c->hosts0) {
+            c->last_fused = true;
+            K.fuse_path = want_path ? 2u : 1u;
+            K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = HOST_PATH_WORDS; K.h_seq = c->h_seq;
+            if (front_launch(K, c->multi, st)) return 1;
+        } else if (c->async_peers) {
+            c->last_fused = false;
+            if (wait_launch(K, st)) return 1;
+        } else {
+            c->last_fused = false;
+            c->stage = 2;
+        }
+        if (!c->last_lean) BIBFS_CUDA_TRY(cudaEventRecord(c->ev[1], st));
+        return 0;
     }
-    return 0;
+    c->stage = 0;
+    return launch_general(c, K, want_path, false, st);
 }
 
-extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path, uint32_t path_cap, void* stream) {
-    if (!c || !res) return fail("NULL argument");
+// Launch the general kernel for a query that the front kernel handed over.  Called by bibfs_ctx_result itself where the
+// context can decide alone; by the caller on EVERY context of a single-process multi-device group after rank 0's
+// context returned status BIBFS_STATUS_HANDED_OVER.
+extern "C" int bibfs_ctx_resume(bibfs_ctx* c, void* stream) {
+    if (!c) return fail("NULL ctx");
+    if (c->stage == 0) return fail("no handed-over query to resume");
     DeviceGuard g(c->device);
     cudaStream_t st = (cudaStream_t)stream;
+    KParams K;
+    fill_params(c, K, c->pend_src, c->pend_dst, false, c->pend_flags);
+    c->stage = 0;
+    return launch_general(c, K, !(c->pend_flags & BIBFS_F_NO_PATH), true, st);
+}
+
+// wait for what the last launch delivers into h_stage (fused) or copy the 64-byte result from the arena
+static int wait_stage(bibfs_ctx* c, cudaStream_t st) {
     Result* hr = reinterpret_cast<Result*>(c->h_stage);
-    u32* hp = reinterpret_cast<u32*>(c->h_stage + sizeof(Result));
-    const bool has_path = !(c->last_flags & BIBFS_F_NO_PATH);
-    // with a path kernel the answer ([Result | first path entries]) was written into h_stage by the device itself
-    const u32 first = has_path ? HOST_PATH_WORDS : 0u;
     if (c->last_fused) {
         // the kernel itself wrote h_stage and then the completion word: poll that word (posted PCIe writes arrive in
         // order) instead of waiting for the kernel to retire; look at the stream now and then in case it failed
@@ -291,11 +357,42 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
             if (*seq != c->seq) return fail("the search kernel finished without delivering a result (aborted launch?)");
         }
     } else {
-        if (!has_path)
-            BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, st));
+        BIBFS_CUDA_TRY(cudaMemcpyAsync(hr, c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, st));
         BIBFS_CUDA_TRY(cudaStreamSynchronize(st));
     }
+    return 0;
+}
+
+extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path, uint32_t path_cap, void* stream) {
+    if (!c || !res) return fail("NULL argument");
+    DeviceGuard g(c->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    Result* hr = reinterpret_cast<Result*>(c->h_stage);
+    u32* hp = reinterpret_cast<u32*>(c->h_stage + sizeof(Result));
+    const bool has_path = !(c->last_flags & BIBFS_F_NO_PATH) && c->hosts0;
+    const u32 first = has_path ? HOST_PATH_WORDS : 0u;
     *res = bibfs_result();
+    if (c->stage == 2) {            // peer of a single-process group, front stage: nothing was launched here
+        res->length = -1; res->meet = BIBFS_NO_VERTEX; res->status = BIBFS_STATUS_HANDED_OVER;
+        return 0;
+    }
+    const bool was_front = c->stage == 1;
+    if (wait_stage(c, st)) return 1;
+    if (was_front) {
+        const bool handed = hr->status == ST_ESCALATED;
+        // policy input: a hand-over after a handful of levels means the front kernel only added a launch
+        if (handed && hr->rounds_paired < 8) c->front_score = c->front_score + 2 > 8 ? 8 : c->front_score + 2;
+        else if (c->front_score > 0) c->front_score -= 1;
+        if (handed) {
+            if (!c->hosts_all && !c->async_peers) {      // the caller resumes every context of the group
+                res->length = -1; res->meet = BIBFS_NO_VERTEX; res->status = BIBFS_STATUS_HANDED_OVER;
+                res->levels = hr->levels; res->levels_paired = hr->rounds_paired;
+                return 0;
+            }
+            if (bibfs_ctx_resume(c, stream)) return 1;
+            if (wait_stage(c, st)) return 1;
+        }
+    }
     res->length = hr->length;
     res->meet = hr->meet;
     res->depth_s = hr->depth_s;
@@ -308,21 +405,14 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     res->levels_grid = hr->levels_grid;
     res->levels_paired = hr->rounds_paired;
     res->path_len = 0;
-    // launch-geometry policy: queries that needed the grid pull the context towards the full launch, the others back
-    if (hr->levels_grid) c->grid_score = c->grid_score + 2 > 8 ? 8 : c->grid_score + 2;
-    else if (c->grid_score > 0) c->grid_score -= 1;
-    float a = 0, b = 0;
+    float a = 0;
     if (c->last_lean) {
         res->search_ms = hr->search_ns * 1e-6;        // the device's own clock, launch latency not included
         res->path_ms = hr->path_ns * 1e-6;
-    } else if (cudaEventElapsedTime(&a, c->ev[0], c->ev[1]) == cudaSuccess) res->search_ms = a;
-    if (c->last_lean) {
-    } else if (c->last_fused) {
-        // the path walk ran inside the search kernel: split the event time with the device's own clock
-        res->path_ms = hr->path_ns * 1e-6;
+    } else if (cudaEventElapsedTime(&a, c->ev[0], c->ev[1]) == cudaSuccess) {
+        // the path walk runs inside the last kernel: split the event time with the device's own clock
+        res->path_ms = c->last_fused ? hr->path_ns * 1e-6 : 0.0;
         res->search_ms = a > res->path_ms ? a - res->path_ms : a;
-    } else if (has_path) {
-        if (cudaEventElapsedTime(&b, c->ev[1], c->ev[2]) == cudaSuccess) res->path_ms = b;
     }
     cudaGetLastError();
     if (hr->status == 1) return fail("search aborted by the device watchdog (a rank did not arrive); reset the context");
@@ -351,19 +441,12 @@ extern "C" int bibfs_ctx_query_result(bibfs_ctx* c, uint32_t src, uint32_t dst, 
 extern "C" int bibfs_ctx_timing(bibfs_ctx* c, float* search_ms, float* path_ms) {
     if (!c) return fail("NULL ctx");
     DeviceGuard g(c->device);
-    float a = 0, b = 0;
-    if (c->last_lean) {
-        const Result* hr = reinterpret_cast<const Result*>(c->h_stage);
-        if (search_ms) *search_ms = hr->search_ns * 1e-6f;
-        if (path_ms) *path_ms = hr->path_ns * 1e-6f;
-        return 0;
-    }
-    BIBFS_CUDA_TRY(cudaEventElapsedTime(&a, c->ev[0], c->ev[1]));
-    if (c->last_fused) {
-        b = reinterpret_cast<const Result*>(c->h_stage)->path_ns * 1e-6f;
+    const Result* hr = reinterpret_cast<const Result*>(c->h_stage);
+    float a = 0, b = c->last_fused ? hr->path_ns * 1e-6f : 0.0f;
+    if (c->last_lean) a = hr->search_ns * 1e-6f;
+    else {
+        BIBFS_CUDA_TRY(cudaEventElapsedTime(&a, c->ev[0], c->ev[1]));
         a = a > b ? a - b : a;
-    } else if (!(c->last_flags & BIBFS_F_NO_PATH)) {
-        BIBFS_CUDA_TRY(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
     }
     if (search_ms) *search_ms = a;
     if (path_ms) *path_ms = b;
@@ -487,5 +570,66 @@ extern "C" int bibfs_pool_query(bibfs_pool* p, const uint32_t* h_src, const uint
         if (h_edges) h_edges[q] = r.edges_scanned;
     }
     if (bad) return fail("a pooled query was aborted by the device watchdog");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// sharing device buffers that this library did not allocate (the graph tensors of the PyTorch
+// layer) with the other processes of a one-process-per-GPU group.  A CUDA IPC handle names a
+// whole ALLOCATION; a tensor usually sits somewhere inside a block of the framework's caching
+// allocator, so the exporter also reports the tensor's offset from the allocation base
+// (cuMemGetAddressRange, taken from the driver library that is already loaded).  The importer maps
+// each distinct allocation once per process and device.
+// ------------------------------------------------------------------------------------------
+#include <dlfcn.h>
+#include <map>
+#include <mutex>
+
+namespace {
+typedef int (*cuMemGetAddressRange_t)(unsigned long long*, size_t*, unsigned long long);
+cuMemGetAddressRange_t address_range_fn() {
+    static cuMemGetAddressRange_t fn = [] {
+        void* h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+        return h ? (cuMemGetAddressRange_t)dlsym(h, "cuMemGetAddressRange_v2") : (cuMemGetAddressRange_t) nullptr;
+    }();
+    return fn;
+}
+std::mutex g_ipc_mu;
+std::map<std::pair<int, std::string>, char*> g_ipc_open;
+}  // namespace
+
+extern "C" int bibfs_ipc_export(const void* d_ptr, void* handle64, uint64_t* offset) {
+    if (!d_ptr || !handle64 || !offset) return fail("NULL argument");
+    cuMemGetAddressRange_t fn = address_range_fn();
+    if (!fn) return fail("the CUDA driver library is not available");
+    unsigned long long base = 0;
+    size_t size = 0;
+    BIBFS_CUDA_TRY(cudaFree(0));      // make sure the runtime's context is current for the driver call
+    if (fn(&base, &size, (unsigned long long)(uintptr_t)d_ptr) != 0) return fail("cuMemGetAddressRange failed for %p", d_ptr);
+    cudaIpcMemHandle_t h;
+    BIBFS_CUDA_TRY(cudaIpcGetMemHandle(&h, (void*)(uintptr_t)base));
+    memcpy(handle64, &h, 64);
+    *offset = (uint64_t)((uintptr_t)d_ptr - (uintptr_t)base);
+    return 0;
+}
+
+extern "C" int bibfs_ipc_import(const void* handle64, uint64_t offset, void** d_ptr) {
+    if (!handle64 || !d_ptr) return fail("NULL argument");
+    int dev = 0;
+    BIBFS_CUDA_TRY(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(g_ipc_mu);
+    const std::pair<int, std::string> key(dev, std::string((const char*)handle64, 64));
+    auto it = g_ipc_open.find(key);
+    char* base = nullptr;
+    if (it != g_ipc_open.end()) base = it->second;
+    else {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handle64, 64);
+        void* p = nullptr;
+        BIBFS_CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        base = (char*)p;
+        g_ipc_open[key] = base;
+    }
+    *d_ptr = base + offset;
     return 0;
 }

@@ -1,0 +1,313 @@
+// front.cuh — query flow with a FRONT kernel (included by bfs_dev.cu after the search kernel).
+//
+//   k_front   one CTA on the GPU that hosts rank 0.  Starts the query, runs the pair tier (pair_tier.cuh) and, when
+//             the search ends inside the tier — every reference-sized query does — walks the path, delivers
+//             [result | path] to the caller's pinned buffer and clears the visited words it set.  Its code is a few
+//             KB, it needs no cooperative launch, no grid and no barrier other than __syncthreads: the fixed cost
+//             of a query (start-up + teardown of the general kernel: ~25 us of a 47 us query) shrinks to the launch
+//             of one small CTA.  When the tier has to stop (frontier > 512, a row >= 32 entries) it leaves the
+//             search where the general kernel k_bibfs can pick it up (KParams::resume): the level state in
+//             Ctrl::st, and with several ranks the HAND-OVER below.  The host launches k_bibfs only then.
+//   several ranks: rank 0's front kernel works alone on the whole graph through the peer mappings, so a small
+//             query costs the other GPUs nothing: no per-level handshake, no remote claim.  The reference pays an
+//             MPI_Allreduce over int[N] per level whatever the frontier size (v4/mpi_bas.cpp:107).
+//             verdict   rank 0 -> every peer, VD_WORDS tagged words (payload | query number << 32) in
+//                       Ctrl::verdict[query & 1]: DONE + the result, or HANDOVER + the level state of that peer.
+//             hand-over rank 0 scatters what it has reached to the owners: visited bits (red.or.sys), parents,
+//                       and the current frontiers into the owners' per-sender queue segments (tagged entries, the
+//                       same format the fused levels use), fences, then sends the verdict.  From there on all
+//                       ranks run the fused multi-GPU levels of k_bibfs.
+//             k_wait    (one process per GPU) a one-warp kernel on each peer: posts "I have entered query q" to
+//                       rank 0 (arrival words: rank 0 never writes into a peer that is still busy with the previous
+//                       query, and never gets more than one verdict ahead), waits for the verdict and hands it to its
+//                       host, which launches k_bibfs(resume) on HANDOVER.
+
+namespace {
+
+struct FrontSmem {
+    LevelState st;
+    Acc acc;
+    u32 qvalid[2];
+    u32 sent[2][MAXR];     // hand-over: frontier entries written into each peer's segment, per side
+    u32 own[2];            // hand-over: frontier entries of rank 0's own vertices
+    u32 fail, pad;
+    alignas(16) PairSmem ps;
+};
+
+// leader warp: lane p waits until word `w` of rank 0 holds a value >= want
+__device__ bool wait_arrivals(const KParams& K, Ctrl* C, u64 want, u64 deadline) {
+    const u32 lane = threadIdx.x & 31;
+    bool done = !(lane > 0 && lane < K.P);
+    u32 spins = 0;
+    while (true) {
+        if (!done) done = ptx::ld_relaxed_sys(&C->arrive[lane]) >= want;
+        if (__all_sync(FULL, done)) return true;
+        if (++spins > 64 && (spins & 255u) == 0 && expired_warp(C, deadline)) return false;
+    }
+}
+
+// leader warp of rank 0: lane p sends the verdict to peer p
+__device__ void send_verdict(const KParams& K, const LevelState& st, u32 kind, u64 qn, const u32 (*sent)[MAXR]) {
+    const u32 lane = threadIdx.x & 31;
+    if (lane == 0 || lane >= K.P) return;
+    u64* dst = ctrl_of(K, lane)->verdict[qn & 1];
+    const u64 tag = (u64)(u32)qn << 32;
+    u32 w[VD_WORDS];
+    w[VD_KIND] = kind; w[VD_LENGTH] = (u32)st.length; w[VD_MEET] = st.meet;
+    w[VD_D0] = st.depth[0]; w[VD_D1] = st.depth[1]; w[VD_LEVELS] = st.levels;
+    w[VD_NF0] = st.nf[0]; w[VD_NF1] = st.nf[1];
+    w[VD_SENT0] = sent ? sent[0][lane] : 0u; w[VD_SENT1] = sent ? sent[1][lane] : 0u;
+    w[VD_EDGES_LO] = (u32)st.edges_total; w[VD_EDGES_HI] = (u32)(st.edges_total >> 32);
+    w[VD_VIS_LO] = (u32)st.visited_total; w[VD_VIS_HI] = (u32)(st.visited_total >> 32);
+    w[VD_PAIRED] = st.rounds_paired; w[VD_STATUS] = st.status;
+#pragma unroll
+    for (u32 i = 0; i < VD_WORDS; ++i) ptx::st_relaxed_sys(dst + i, tag | w[i]);
+}
+
+// whole warp of a peer: poll this rank's verdict words until all carry the tag of query qn
+__device__ bool wait_verdict(Ctrl* C, u64 qn, u32* out /* VD_WORDS */, u64 deadline) {
+    const u32 lane = threadIdx.x & 31;
+    const u64* src = C->verdict[qn & 1];
+    bool done = lane >= VD_WORDS;
+    u64 w = 0;
+    u32 spins = 0;
+    bool ok = true;
+    while (true) {
+        if (!done) { w = ptx::ld_relaxed_sys(src + lane); done = (u32)(w >> 32) == (u32)qn; }
+        if (__all_sync(FULL, done)) break;
+        if (++spins > 64 && (spins & 255u) == 0 && expired_warp(C, deadline)) { ok = false; break; }
+    }
+#pragma unroll
+    for (u32 i = 0; i < VD_WORDS; ++i) out[i] = (u32)__shfl_sync(FULL, w, i);
+    return ok;
+}
+
+// level state of a peer (rank > 0) after a hand-over, from its verdict
+__device__ void state_from_verdict(const KParams& K, LevelState& G, const u32* v, u32 tag) {
+    G.phase = PH_TD_SOLO; G.side = 0; G.levels = v[VD_LEVELS]; G.levels_bu = 0;
+    G.depth[0] = v[VD_D0]; G.depth[1] = v[VD_D1];
+    G.nf[0] = v[VD_NF0]; G.nf[1] = v[VD_NF1];
+    for (u32 s = 0; s < 2; ++s) {
+        G.q_lo[s] = G.q_hi[s] = 0;
+        G.fbm_cur[s] = 0; G.fbm_valid[s] = 0;
+        for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
+        G.rq_tag[s] = tag;
+    }
+    G.rq_hi[0][0] = v[VD_SENT0]; G.rq_hi[1][0] = v[VD_SENT1];
+    G.local_front = 0; G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
+    G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.pad = 0;
+    G.rounds_paired = v[VD_PAIRED]; G.levels_grid = 0;
+    G.edges_total = (u64)v[VD_EDGES_LO] | ((u64)v[VD_EDGES_HI] << 32);
+    G.visited_total = (u64)v[VD_VIS_LO] | ((u64)v[VD_VIS_HI] << 32);
+}
+
+// Hand-over (whole CTA of rank 0's front kernel): everything the tier reached goes to its owner.
+__device__ void front_handover(const KParams& K, const Env& E, FrontSmem& fs, const PairIO io, u32 tag) {
+    const u32 tid = threadIdx.x;
+    LevelState& st = fs.st;
+    if (tid < 2 * MAXR) fs.sent[tid / MAXR][tid % MAXR] = 0;
+    if (tid < 2) fs.own[tid] = 0;
+    __syncthreads();
+    for (u32 side = 0; side < 2; ++side) {
+        const u32 total = st.q_hi[side], front_lo = st.q_lo[side];      // log window of the current frontier
+        u32* const own_parent = E.parent[side];
+        for (u32 i = tid; i < total; i += BFS_THREADS) {
+            const u32 v = io.log[side][i];
+            const u32 par = io.par[side][v];
+            const u32 o = owner_of(K, v);
+            if (o == E.me) {
+                own_parent[v - E.lo] = par;
+                if (i >= front_lo) E.q[side][ptx::atoms_add(&fs.own[side], 1u)] = v;
+            } else {
+                ptx::red_or_sys(reinterpret_cast<u32*>(vis_of(K, o) + (v >> 5)) + side, 1u << (v & 31u));
+                ptx::st_peer(parent_of(K, o, side) + (v - o * K.B), par);
+                if (i >= front_lo)
+                    ptx::st_relaxed_sys(rq_of(K, o, side, E.me) + ptx::atoms_add(&fs.sent[side][o], 1u), (u64)v | ((u64)tag << 32));
+            }
+        }
+    }
+    __threadfence_system();        // bits and parents were plain / relaxed stores: order them before the verdict
+    __syncthreads();
+    if (tid == 0) {
+        for (u32 s = 0; s < 2; ++s) {
+            st.q_lo[s] = 0; st.q_hi[s] = fs.own[s];
+            fs.acc.q_tail[s] = fs.own[s];
+            for (u32 p = 0; p < MAXR; ++p) { st.rq_lo[s][p] = 0; st.rq_hi[s][p] = 0; E.C->sent[s][p] = fs.sent[s][p]; }
+            st.rq_tag[s] = tag;
+        }
+    }
+    __syncthreads();
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// the front kernel: one CTA on rank 0's GPU
+// ------------------------------------------------------------------------------------------
+template <bool MULTI>
+__global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant__ KParams K) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    FrontSmem& fs = *reinterpret_cast<FrontSmem*>(smem_raw);
+    LevelState& st = fs.st;
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x > 0) {
+        // helper CTAs (launched only for graphs that fit L2 with room to spare): stream rank 0's vertex records and its
+        // visited words into L2 and leave — a cold record costs ~700 ns on the chain of a round, a hit 154 ns, and one
+        // CTA could not issue the ~25,000 prefetches of a 100k-vertex graph without stalling its own rounds
+        const char* rec = reinterpret_cast<const char*>(K.vrec[0]);
+        const char* vw = reinterpret_cast<const char*>(vis_of(K, 0));
+        const u32 vis_lines = (K.L.nw * 8u + 127u) / 128u;
+        const u32 stride = (gridDim.x - 1u) * BFS_THREADS;
+        for (u32 i = (blockIdx.x - 1u) * BFS_THREADS + tid; i < K.warm_lines + vis_lines; i += stride)
+            ptx::prefetch_l2(i < K.warm_lines ? rec + 128ull * i : vw + 128ull * (i - K.warm_lines));
+        return;
+    }
+    Env E;
+    E.cta = 0; E.cpr = 1; E.me = 0; E.lo = 0;
+    E.P = K.P; E.B = K.B; E.n = K.n; E.nw = K.L.nw;
+    E.C = ctrl_of(K, 0);
+    E.A = &fs.acc; E.sA = &fs.acc;
+    E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = false; E.solo = true; E.tag = 0; E.smem_src = false;
+    E.stage = nullptr; E.stage_cnt = nullptr; E.cta_new = nullptr; E.cta_edges = nullptr; E.s_sent = nullptr; E.s_rnew = nullptr;
+    E.vis = vis_of(K, 0);
+    E.parent[0] = parent_of(K, 0, 0); E.parent[1] = parent_of(K, 0, 1);
+    E.q[0] = q_of(K, 0, 0); E.q[1] = q_of(K, 0, 1);
+    E.row_ptr = K.row_ptr[0];
+    E.col = K.col[0];
+    Ctrl* const C = E.C;
+    const u64 deadline = ptx::globaltimer_ns() + (u64)K.watchdog_ms * 1000000ull;
+    KT_STAMP(0);
+    PairIO io;
+    if (MULTI) {
+        u32* lg = reinterpret_cast<u32*>(K.arena[0] + K.L.off_log);
+        u32* pa = reinterpret_cast<u32*>(K.arena[0] + K.L.off_pall);
+        const size_t nv = (size_t)K.B * K.P;
+        io.log[0] = lg; io.log[1] = lg + nv; io.par[0] = pa; io.par[1] = pa + nv;
+    } else {
+        io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
+    }
+    // ---- query start
+    u32 src = K.src, dst = K.dst;
+    if (K.h_query) { src = *reinterpret_cast<const volatile u32*>(K.h_query); dst = *reinterpret_cast<const volatile u32*>(K.h_query + 1); }
+    const u64 qn = K.qn;
+    const bool bad = src >= K.n || dst >= K.n;
+    bool tier = !bad && src != dst && !(K.flags & (BIBFS_F_FORCE_GRID | BIBFS_F_FORCE_BU));
+    if (MULTI) for (u32 p = 0; p < K.P; ++p) tier = tier && K.vrec[p] != nullptr;
+    else tier = tier && K.vrec[0] != nullptr;
+    if (tid == 0) {
+        LevelState& G = st;
+        C->q_src = src; C->q_dst = dst;
+        C->trace_count = 0;
+        C->t_begin_ns = ptx::globaltimer_ns();
+        fs.acc.q_tail[0] = 1; fs.acc.q_tail[1] = 1; fs.acc.new_count = 0; fs.acc.meet_local = NO_V; fs.acc.edges = 0;
+        fs.fail = 0;
+        G.phase = PH_TD_SOLO; G.side = 0; G.levels = 0; G.levels_bu = 0;
+        G.depth[0] = G.depth[1] = 0; G.nf[0] = G.nf[1] = 1;
+        for (u32 s = 0; s < 2; ++s) {
+            G.q_lo[s] = 0; G.q_hi[s] = 1; G.fbm_cur[s] = 0; G.fbm_valid[s] = 0; G.rq_tag[s] = 0;
+            for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
+        }
+        G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 1; G.pad = 0; G.rounds_paired = 0; G.levels_grid = 0;
+        G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
+        G.edges_total = 0; G.visited_total = 2;
+        G.xepoch = C->xepoch;
+        if (bad) { G.status = 2; G.phase = PH_DONE; }
+        else if (src == dst) { G.length = 0; G.meet = src; G.phase = PH_DONE; G.visited_total = 1; fs.acc.q_tail[0] = 0; fs.acc.q_tail[1] = 0; G.q_hi[0] = G.q_hi[1] = 0; }
+        else {
+            // seeds: marked in rank 0's visited words whoever owns them; the owners learn about them at a hand-over
+            atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[src >> 5]), 1ull << (src & 31));
+            atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[dst >> 5]), 1ull << ((dst & 31) + 32));
+            io.log[0][0] = src; io.par[0][src] = NO_V;
+            io.log[1][0] = dst; io.par[1][dst] = NO_V;
+        }
+        if (G.phase == PH_DONE) write_result(K, C, G);
+    }
+    if (MULTI && K.async_peers && warp == 1) {
+        // never more than one verdict ahead of a peer (the verdict slots alternate by query parity)
+        if (!wait_arrivals(K, C, qn - 1, deadline) && lane == 0) fs.fail = 1;
+    }
+    __syncthreads();
+    KT_STAMP(2);
+    if (st.phase != PH_DONE && !fs.fail && tier) {
+        KT_STAMP(3);
+        pair_run<MULTI>(K, E, st, fs.acc, fs.qvalid, fs.ps, io, src, dst);
+        KT_STAMP(4);
+    }
+    if (fs.fail) {
+        if (tid == 0) { st.status = 1; st.length = -1; st.phase = PH_DONE; write_result(K, C, st); atomicExch(&C->abort_flag, 1u); }
+        __syncthreads();
+    }
+    if (st.phase == PH_DONE) {
+        // ---- the query ended here: verdict to the peers, path, result, cleanup
+        if (MULTI && warp == 0 && !fs.fail) send_verdict(K, st, VK_DONE, qn, nullptr);
+        KT_STAMP(5);
+        if (K.fuse_path == 2u) path_body_local(K, io.par[0], io.par[1]);
+        else if (K.fuse_path) result_to_host(K);
+        KT_STAMP(6);
+        const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
+        for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
+        for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+        KT_STAMP(7);
+        return;
+    }
+    // ---- the search goes on in the general kernel
+    if (MULTI) {
+        if (K.async_peers && warp == 0 && !wait_arrivals(K, C, qn, deadline) && lane == 0) fs.fail = 1;
+        __syncthreads();
+        if (fs.fail) {
+            if (tid == 0) { st.status = 1; st.length = -1; st.phase = PH_DONE; write_result(K, C, st); atomicExch(&C->abort_flag, 1u); }
+            __syncthreads();
+            if (K.fuse_path) result_to_host(K);
+            return;
+        }
+        const u32 tag = (u32)(st.xepoch + 1);
+        front_handover(K, E, fs, io, tag);
+        if (warp == 0) send_verdict(K, st, VK_HANDOVER, qn, fs.sent);
+        if (tid == 0) { st.xepoch += 1; C->xepoch = st.xepoch; }
+        // rank 0's filter bits of other ranks' vertices stay set: "already forwarded to the owner"
+    }
+    __syncthreads();
+    {
+        u32* g = reinterpret_cast<u32*>(&C->st);
+        const u32* s = reinterpret_cast<const u32*>(&st);
+        for (u32 i = tid; i < sizeof(LevelState) / 4; i += BFS_THREADS) g[i] = s[i];
+        if (tid == 0) {
+            C->acc = fs.acc;
+            Result& R = C->res;
+            R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
+            R.depth_s = st.depth[0]; R.depth_t = st.depth[1]; R.levels_bu = 0; R.levels_grid = 0;
+            R.edges_scanned = st.edges_total; R.vertices_visited = st.visited_total; R.search_ns = 0; R.path_ns = 0;
+        }
+    }
+    __syncthreads();
+    if (K.fuse_path) result_to_host(K);
+}
+
+// ------------------------------------------------------------------------------------------
+// k_wait: a peer (rank > 0) in the one-process-per-GPU deployment; one warp
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) k_wait(const __grid_constant__ KParams K) {
+    const u32 lane = threadIdx.x;
+    const u32 me = K.rank_lo;
+    Ctrl* const C = ctrl_of(K, me);
+    const u64 deadline = ptx::globaltimer_ns() + (u64)K.watchdog_ms * 1000000ull;
+    const u64 qn = K.qn;
+    if (lane == 0) { C->t_begin_ns = ptx::globaltimer_ns(); ptx::st_relaxed_sys(&ctrl_of(K, 0)->arrive[me], qn); }
+    u32 v[VD_WORDS];
+    const bool ok = wait_verdict(C, qn, v, deadline);
+    if (lane == 0) {
+        Result& R = C->res;
+        R.length = -1; R.meet = NO_V; R.path_len = 0; R.levels_bu = 0; R.levels_grid = 0; R.path_ns = 0;
+        if (!ok) { R.status = 1; atomicExch(&C->abort_flag, 1u); }
+        else {
+            R.depth_s = v[VD_D0]; R.depth_t = v[VD_D1]; R.levels = v[VD_LEVELS]; R.rounds_paired = v[VD_PAIRED];
+            R.edges_scanned = (u64)v[VD_EDGES_LO] | ((u64)v[VD_EDGES_HI] << 32);
+            R.vertices_visited = (u64)v[VD_VIS_LO] | ((u64)v[VD_VIS_HI] << 32);
+            if (v[VD_KIND] == VK_DONE) { R.length = (i32)v[VD_LENGTH]; R.meet = v[VD_MEET]; R.status = (i32)v[VD_STATUS]; }
+            else R.status = ST_ESCALATED;
+        }
+        const u64 dt = ptx::globaltimer_ns() - C->t_begin_ns;
+        R.search_ns = dt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)dt;
+    }
+    __syncwarp();
+}

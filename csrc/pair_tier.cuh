@@ -30,6 +30,24 @@
 // and no row of >= PT_MAXDEG entries has been discovered; then it hands the search to the general
 // machinery (solo / cluster / grid / hub / bottom-up) through the same LevelState those use.
 
+// PT_MARK: points of a round where the fine-trace build takes time stamps.  The regular build keeps a NEVER-TAKEN branch
+// at each of them (query flag bit 31 is rejected by bibfs_ctx_query): measured on B200, the same round loop runs 36.3 us
+// per er100k query (device clock, L2-hot) without the branches, 36.3 us with empty asm statements in their place, and
+// 24.7 us with them — ptxas schedules the batch of record loads and claims differently when the basic blocks end there
+// (profiles/r2/scheduling_marks.md).  The fine-trace build (27.3 us including its stamps) gave the hint.
+#ifdef BIBFS_FINE_TRACE
+#define PT_MARK(slot, dep) DBG_STAMP(slot, dep)
+#else
+#define PT_MARK(slot, dep)                                                                                   \
+    do {                                                                                                     \
+        if (threadIdx.x == 0 && (K.flags & 0x80000000u)) {                                                   \
+            u64 _t;                                                                                          \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t) : "l"((u64)(dep)) : "memory");             \
+            *reinterpret_cast<volatile u64*>(E.vis) = _t;                                                    \
+        }                                                                                                    \
+    } while (0)
+#endif
+
 constexpr u32 PT_CAP = 512;          // frontier entries per side
 constexpr u32 PT_MAXDEG = 32;        // a discovered row at least this long ends the tier
 constexpr int PT_NB = 6;             // neighbours inlined in a vertex record
@@ -47,31 +65,43 @@ struct PairSmem {
     alignas(16) uint4 fr[2][2][PT_CAP][2];       // ... and their records
 };
 
-__device__ __forceinline__ uint4 ld_rec(const uint4* p) {
-    uint4 r;
-    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
-    return r;
-}
 __device__ __forceinline__ void reds_or(u32* p, u32 v) {
     asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(ptx::smem_addr(p)), "r"(v) : "memory");
 }
 
+// What the tier works on.  Single rank: the rank's own queue / parent arrays (so that the general tiers continue on
+// them).  Several ranks (MULTI): rank 0 runs the tier ALONE over the whole graph — records and long rows of other
+// ranks' vertices are read through the peer mappings, claims go to rank 0's own all-vertex visited words, and the
+// vertices it reaches are logged locally (log / pall regions of rank 0's arena); the other ranks are not touched
+// unless the search has to be handed over to them (front_handover below).
+struct PairIO {
+    u32* log[2];        // vertices reached per side, in discovery order (entry 0 = the seed)
+    u32* par[2];        // parent of a vertex per side, indexed by the vertex id
+};
+
 // Returns with st.phase == PH_DONE (result written) or with the level state handed over (decide_next done).
-__device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSmem& ps) {
+template <bool MULTI>
+__device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, Acc& acc, u32* qvalid, PairSmem& ps, const PairIO io,
+                                      const u32 src, const u32 dst) {
     const u32 tid = threadIdx.x, lane = tid & 31;
-    LevelState& st = sm.st;
     Ctrl* const C = E.C;
-    const uint4* const vrec = K.vrec[E.me];
-    const u32* const g_col = E.col;
     u64* const g_vis = E.vis;
-    const u32 g_lo = E.lo;
     const bool tracing = (K.flags & BIBFS_F_TRACE) != 0;
+    // record / adjacency bases indexed by the GLOBAL vertex id resp. the owner's row start
+    __shared__ const uint4* s_vrecb[MAXR];
+    __shared__ const u32* s_colb[MAXR];
+    if (MULTI && tid < K.P) { s_vrecb[tid] = K.vrec[tid] - 2 * (size_t)tid * K.B; s_colb[tid] = K.col[tid]; }
+    const uint4* const vrec0 = MULTI ? nullptr : K.vrec[E.me] - 2 * (size_t)E.lo;
+    auto rec_of = [&](u32 v) -> const uint4* { return (MULTI ? s_vrecb[owner_of(K, v)] : vrec0) + 2 * (size_t)v; };
+    auto ld_rec_if = [&](bool on, const uint4* p) -> uint4 { return MULTI ? ptx::ld_v4_sys_if(on, p) : ptx::ld_v4_gpu_if(on, p); };
+    if (MULTI) __syncthreads();
     // level state, identical in every thread
     u32 n0 = 1, n1 = 1, base0 = 1, base1 = 1, d0 = 0, d1 = 0, levels = 0, buf0 = 0, buf1 = 0, par = 0;
     u64 my_edges = 0;
     if (tid < 2) {
-        const u32 v = tid ? C->q_dst : C->q_src;
-        const uint4 a = ld_rec(vrec + 2 * (size_t)(v - g_lo)), b = ld_rec(vrec + 2 * (size_t)(v - g_lo) + 1);
+        const u32 v = tid ? dst : src;
+        const uint4* p = rec_of(v);
+        const uint4 a = ld_rec_if(true, p), b = ld_rec_if(true, p + 1);
         ps.fv[tid][0][0] = v;
         ps.fr[tid][0][0][0] = a;
         ps.fr[tid][0][0][1] = b;
@@ -110,14 +140,15 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
             rb = ps.fr[side][buf][idx][1];
             deg = ra.x; r0 = ra.y;
         }
-        DBG_STAMP(0, u + deg);
+        PT_MARK(0, u + deg);
         my_edges += deg;
         if (tracing && deg) ptx::reds_add(&ps.tr_edges[par][side], deg);
         u32* const out_v = ps.fv[side][buf ^ 1u];
         uint4(*const out_r)[2] = ps.fr[side][buf ^ 1u];
         u32* const cursor = &ps.cnt[par][side];
-        u32* const qs = E.q[side];
-        u32* const pp = E.parent[side];
+        u32* const qs = io.log[side];
+        u32* const pp = io.par[side];
+        const u32* const g_col = MULTI ? s_colb[owner_of(K, u)] : E.col;
 
         // one batch of W candidates: claims and record fetches in flight together (branch-free: idle slots OR a zero
         // into the thread's scratch word and re-read the thread's own record)
@@ -128,17 +159,17 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
 #pragma unroll
             for (int k = 0; k < W; ++k) {
                 const bool act = (u32)k < nact;
-                const uint4* p = vrec + 2 * (size_t)((act ? v[k] : u) - g_lo);
-                qa[k] = ptx::ld_v4_gpu_if(act, p);
-                qb[k] = ptx::ld_v4_gpu_if(act, p + 1);
+                const uint4* p = rec_of(act ? v[k] : u);
+                qa[k] = ld_rec_if(act, p);
+                qb[k] = ld_rec_if(act, p + 1);
             }
 #pragma unroll
             for (int k = 0; k < W; ++k) {
                 const bool act = (u32)k < nact;
                 old[k] = ptx::atom_or_gpu_if(act, &g_vis[(act ? v[k] : u) >> 5], 1ull << ((v[k] & 31u) + sh));
             }
-            DBG_STAMP(1, qb[W - 1].w);
-            DBG_STAMP(2, old[W - 1]);
+            PT_MARK(1, qb[W - 1].w);
+            PT_MARK(2, old[W - 1]);
             const u32 shz = sh + ptx::zero_after(old[W - 1]);      // == sh; pins the tests behind the whole batch
             u32 newmask = 0, meetmask = 0;
 #pragma unroll
@@ -151,13 +182,13 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
             u32 slot = 0;
             if (wide) slot = warp_reserve(nnew, [&](u32 n) { return ptx::atoms_add(cursor, n); });
             else if (nnew) slot = ptx::atoms_add(cursor, nnew);
-            DBG_STAMP(3, slot);
+            PT_MARK(3, slot);
             if (newmask) {
 #pragma unroll
                 for (int k = 0; k < W; ++k) {
                     if ((newmask >> k) & 1u) {
                         qs[base + slot] = v[k];
-                        pp[v[k] - g_lo] = u;
+                        pp[v[k]] = u;
                         if (slot < PT_CAP) { out_v[slot] = v[k]; out_r[slot][0] = qa[k]; out_r[slot][1] = qb[k]; }
                         else fl |= PT_OVF;
                         if (qa[k].x >= PT_MAXDEG) fl |= PT_BIG;
@@ -181,14 +212,17 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
                 u32 c[PT_W];
                 const u32 left = deg > e ? deg - e : 0u;
 #pragma unroll
-                for (int k = 0; k < PT_W; ++k) c[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((u32)k < left ? e + k : 0u));
+                for (int k = 0; k < PT_W; ++k) {
+                    const u32* a = g_col + r0 + ((u32)k < left ? e + k : 0u);
+                    c[k] = MULTI ? ptx::ld_relaxed_sys(a) : ptx::ld_relaxed_gpu(a);
+                }
                 batch(std::integral_constant<int, PT_W>{}, c, min(left, (u32)PT_W));
             }
             if (fl) reds_or(&ps.flag[par], fl);
         }
-        DBG_STAMP(4, fl);
+        PT_MARK(4, fl);
         __syncthreads();
-        DBG_STAMP(5, tid);
+        PT_MARK(5, tid);
         // ---- round end: every thread derives the next state from the round's counters
         const u32 c0 = ps.cnt[par][0], c1 = ps.cnt[par][1], f = ps.flag[par], mnew = ps.meet_new[par];
         if (tid == 0) {
@@ -204,7 +238,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
         if (e0) { d0 += 1; levels += 1; base0 += c0; n0 = c0; buf0 ^= 1u; visited += c0; }
         if (e1) { d1 += 1; levels += 1; base1 += c1; n1 = c1; buf1 ^= 1u; visited += c1; }
         par = (par + 1u) % 3u;
-        DBG_STAMP(6, n0 + n1);
+        PT_MARK(6, n0 + n1);
 #ifdef BIBFS_FINE_TRACE
         if (blockIdx.x == 0 && threadIdx.x == 0) { if (g_dbg_level < 256) g_dbg[g_dbg_level][7] = ((u64)(e0 ? 1 : 0) | (e1 ? 2 : 0)) | ((u64)n0 << 8) | ((u64)n1 << 32); g_dbg_level++; }
 #endif
@@ -241,9 +275,9 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
         st.levels = levels;
         st.q_lo[0] = base0 - n0; st.q_hi[0] = base0;
         st.q_lo[1] = base1 - n1; st.q_hi[1] = base1;
-        sm.acc.q_tail[0] = base0; sm.acc.q_tail[1] = base1;
-        sm.acc.new_count = 0; sm.acc.meet_local = NO_V; sm.acc.edges = 0;
-        sm.qvalid[0] = 0; sm.qvalid[1] = 0;             // the general tiers read the frontier from the queue
+        acc.q_tail[0] = base0; acc.q_tail[1] = base1;
+        acc.new_count = 0; acc.meet_local = NO_V; acc.edges = 0;
+        qvalid[0] = 0; qvalid[1] = 0;                   // the general tiers read the frontier from the queue
         st.edges_total += ps.edges;
         st.visited_total += visited;
         st.rounds_paired = levels;
@@ -252,7 +286,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, Smem& sm, PairSme
             st.depth[0] = depth_s; st.depth[1] = depth_t;
             st.phase = PH_DONE;
             write_result(K, C, st);
-        } else {
+        } else if (!MULTI) {
             decide_next(K, st);
             if (st.phase == PH_DONE) write_result(K, C, st);
         }

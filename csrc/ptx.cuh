@@ -103,6 +103,23 @@ __device__ __forceinline__ uint4 ld_v4_gpu_if(bool on, const uint4* p) {
         : "memory");
     return r;
 }
+__device__ __forceinline__ uint4 ld_v4_sys_if(bool on, const uint4* p) {
+    uint4 r;
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.u32 q, %5, 0;\n\t"
+        "mov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\tmov.u32 %2, 0;\n\tmov.u32 %3, 0;\n\t"
+        "@q ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+        : "=&r"(r.x), "=&r"(r.y), "=&r"(r.z), "=&r"(r.w)
+        : "l"(p), "r"((u32)on)
+        : "memory");
+    return r;
+}
+__device__ __forceinline__ u32 ld_relaxed_sys(const u32* p) {
+    u32 v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void red_or_sys(u32* p, u32 v) {
     asm volatile("red.relaxed.sys.global.or.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }

@@ -207,7 +207,17 @@ int bibfs_ctx_ipc_handle(bibfs_ctx* ctx, uint32_t i, void* handle64);
 int bibfs_ctx_attach_ipc(bibfs_ctx* ctx, uint32_t rank, const void* handle64);
 int bibfs_ctx_attach_local(bibfs_ctx* ctx, uint32_t rank, bibfs_ctx* owner);
 size_t bibfs_ctx_arena_bytes(const bibfs_ctx* ctx);
-/* re-zero all per-query state (needed only after a watchdog abort). */
+/* adjacency entries / vertex records of a rank hosted elsewhere, as mapped on this device (peer access or an IPC
+ * mapping): with them for every rank, small queries are answered by rank 0 alone (front kernel, csrc/front.cuh). */
+int bibfs_ctx_set_peer_graph(bibfs_ctx* ctx, uint32_t rank, const uint32_t* d_col, const void* d_vrec);
+/* Share a device buffer allocated by somebody else (a framework's caching allocator) with another process: the IPC
+ * handle of the allocation it lies in plus its offset; the importer maps each allocation once per process and device
+ * and keeps it mapped.  Used for the col / vertex-record tensors of the one-process-per-GPU deployment. */
+int bibfs_ipc_export(const void* d_ptr, void* handle64, uint64_t* offset);
+int bibfs_ipc_import(const void* handle64, uint64_t offset, void** d_ptr);
+/* continue a query that returned BIBFS_STATUS_HANDED_OVER: call it on every context of the group, then fetch the results */
+int bibfs_ctx_resume(bibfs_ctx* ctx, void* stream);
+/* re-zero all per-query state (needed only after a watchdog abort; on every rank of the group). */
 int bibfs_ctx_reset(bibfs_ctx* ctx, void* stream);
 
 /* flags for bibfs_ctx_query */
@@ -218,7 +228,11 @@ int bibfs_ctx_reset(bibfs_ctx* ctx, void* stream);
 #define BIBFS_F_NO_PATH     16u   /* skip the path kernel                                   */
 #define BIBFS_F_DEVICE_CLOCK 32u  /* one rank: no CUDA events around the launch; search_ms / path_ms come from the
                                      device's own clock and completion is detected by polling the pinned result    */
-#define BIBFS_F_ALL         63u   /* every defined flag bit; bibfs_ctx_query rejects any other bit */
+#define BIBFS_F_NO_FRONT    64u   /* go straight to the general kernel (no front kernel / pair tier launch)                */
+#define BIBFS_F_ALL        127u   /* every defined flag bit; bibfs_ctx_query rejects any other bit */
+/* bibfs_result::status of a context whose query was handed over by the front kernel and must be continued with
+ * bibfs_ctx_resume on every context of the group (only contexts of ONE process spanning several devices see it) */
+#define BIBFS_STATUS_HANDED_OVER 100
 
 /* Enqueue one query: (optional) H2D of the query from pinned host memory, the persistent
  * search kernel, and the path kernel.  h_query_pinned = {src,dst} in pinned memory, or NULL

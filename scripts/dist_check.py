@@ -18,7 +18,7 @@ for name, spec in (("er", bb.er_spec(30000, 2.2 / 30000, seed=1)), ("rmat", bb.r
     oracle = bb.SerialSolver(bb.Graph.generate(spec), policy=1)
     rng = np.random.default_rng(5)
     pairs = [(0, spec.n - 1), (3, 3)] + [(int(rng.integers(spec.n)), int(rng.integers(spec.n))) for _ in range(25)]
-    for flags in (0, 2, 2 | 8):
+    for flags in (0, 64, 2, 2 | 8):          # default flow (front kernel), fused levels from the start, forced grid, forced bottom-up
         t0 = time.time()
         for s, t in pairs:
             want = oracle.query(s, t, want_path=False).length
@@ -30,6 +30,23 @@ for name, spec in (("er", bb.er_spec(30000, 2.2 / 30000, seed=1)), ("rmat", bb.r
                 bb.validate_path(oracle.graph, s, t, r.path, want)
         if rank == 0:
             print(f"{name} flags={flags}: {len(pairs)} queries ok={ok} {time.time()-t0:.2f}s last search_ms={r.search_ms:.4f}", flush=True)
+    # back to back: query k+1 starts on the path of query k (rank 0 walks the parents inside its kernel; nobody may
+    # overwrite them meanwhile)
+    s, t = 0, spec.n - 1
+    for _ in range(10):
+        want = oracle.query(s, t, want_path=False).length
+        r = solver.query(s, t)
+        if r.length != want:
+            ok = False
+            print(f"[rank {rank}] MISMATCH {name} chained {s}->{t}: got {r.length} want {want}", flush=True)
+        if want is None or want < 4:
+            break
+        p = [None]
+        if rank == 0:
+            bb.validate_path(oracle.graph, s, t, r.path, want)
+            p[0] = (r.path[len(r.path) // 3], r.path[-1 - len(r.path) // 5])
+        dist.broadcast_object_list(p, src=0)
+        s, t = p[0]
     solver.close()
 t = torch.tensor([0 if ok else 1], device=dev)
 dist.all_reduce(t)

@@ -1,0 +1,116 @@
+"""GPU: query flow with the front kernel (csrc/front.cuh) — rank 0 answers small queries alone over the whole
+partitioned graph, hands larger searches over to the fused multi-rank levels — with P virtual ranks on one device
+(same protocol as P GPUs: peer pointers are plain device pointers), plus the watchdog / reset path."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import query_pairs
+
+pytestmark = pytest.mark.gpu
+F_FORCE_GRID, F_NO_FRONT = 2, 64
+
+
+def _check(bb, g_cpu, oracle, solver, s, t, flags=0):
+    want = oracle.query(s, t, want_path=False).length
+    r = solver.query(s, t, flags=flags)
+    assert r.length == want, (s, t, r.length, want, flags)
+    if want is not None:
+        bb.validate_path(g_cpu, s, t, r.path, want)
+    return r
+
+
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+def test_front_kernel_answers_small_queries_alone(bb, nranks):
+    spec = bb.er_spec(40000, 2.2 / 40000, seed=7)
+    g_cpu = bb.Graph.generate(spec)
+    oracle = bb.SerialSolver(g_cpu, policy=1)
+    solver = bb.MultiGpuSolver(bb.Graph.generate(spec, device="cuda:0", nranks=nranks))
+    alone = 0
+    for s, t in query_pairs(spec.n, 80, nranks):
+        r = _check(bb, g_cpu, oracle, solver, s, t)
+        if r.length not in (None, 0) and r.levels_paired == r.levels:
+            alone += 1
+        r2 = _check(bb, g_cpu, oracle, solver, s, t, F_NO_FRONT)          # the fused levels from the first level on
+        assert r2.levels_paired == 0
+    assert alone > 20, "the front kernel should finish most ER queries without a hand-over"
+    solver.close()
+
+
+@pytest.mark.parametrize("nranks", [2, 3, 8])
+def test_hand_over_to_the_fused_levels(bb, nranks):
+    """Searches that outgrow the front kernel: a grid whose diagonal passes 512 vertices, R-MAT hubs after a level or two."""
+    for spec, pairs in ((bb.grid_spec(1400, 1100), [(0, 1400 * 1100 - 1), (1399, 1400 * 1099), (5, 700 * 1400 + 9)]),
+                        (bb.rmat_spec(15, edgefactor=16, seed=3), None), (bb.er_spec(6000, 9.0 / 6000, seed=4), None)):
+        g_cpu = bb.Graph.generate(spec)
+        oracle = bb.SerialSolver(g_cpu, policy=1)
+        solver = bb.MultiGpuSolver(bb.Graph.generate(spec, device="cuda:0", nranks=nranks))
+        handed = 0
+        for s, t in (pairs or query_pairs(spec.n, 40, nranks + 11)):
+            r = _check(bb, g_cpu, oracle, solver, s, t)
+            handed += int(r.length is not None and r.levels > r.levels_paired)
+        assert handed > 0 or spec.kind == 0       # (the dense ER graph is small enough for rank 0 to finish alone)
+        solver.close()
+
+
+def test_single_rank_front_then_general_kernel(bb):
+    spec = bb.grid_spec(1500, 1300)
+    g_cpu = bb.Graph.generate(spec)
+    solver = bb.GpuSolver(bb.Graph.generate(spec, device="cuda:0"))
+    for timing in ("device", "events"):
+        r = solver.query(0, spec.n - 1, timing=timing)
+        assert r.length == 1499 + 1299 and 0 < r.levels_paired < r.levels
+        bb.validate_path(g_cpu, 0, spec.n - 1, r.path, r.length)
+        r = solver.query(7, 7 + 1500 * 2 + 3, timing=timing)
+        assert r.length == 5 and r.levels_paired == r.levels
+    solver.close()
+
+
+def test_back_to_back_queries_on_each_others_paths(bb):
+    """Query k+1 starts on the path of query k (the parents of k must not be disturbed while they are walked)."""
+    spec = bb.grid_spec(300, 40)
+    g_cpu = bb.Graph.generate(spec)
+    oracle = bb.SerialSolver(g_cpu, policy=1)
+    solver = bb.MultiGpuSolver(bb.Graph.generate(spec, device="cuda:0", nranks=4))
+    s, t = 0, spec.n - 1
+    for _ in range(12):
+        r = _check(bb, g_cpu, oracle, solver, s, t)
+        s, t = r.path[len(r.path) // 3], r.path[-1 - len(r.path) // 5]
+    solver.close()
+
+
+def test_watchdog_abort_and_reset(bb):
+    """A rank whose peer never launches: the device-side watchdog ends the query with an error instead of a hang; after
+    bibfs_ctx_reset on both contexts the group answers again."""
+    from bidirectional_bfs_b200.ops.search import SearchContext
+    from bidirectional_bfs_b200._lib import BibfsError
+    spec = bb.er_spec(20000, 2.2 / 20000, seed=2)
+    g_cpu = bb.Graph.generate(spec)
+    oracle = bb.SerialSolver(g_cpu, policy=1)
+    g = bb.Graph.generate(spec, device="cuda:0", nranks=2)
+    c0 = SearchContext(g, 0, 1, max_ctas=32, watchdog_ms=60)
+    c1 = SearchContext(g, 1, 1, max_ctas=32, watchdog_ms=60)
+    c0.attach_local(1, c1)
+    c1.attach_local(0, c0)
+    s, t = next((a, b) for a, b in query_pairs(spec.n, 60, 3) if (oracle.query(a, b, want_path=False).length or 0) > 3)
+    c0.launch(s, t, F_NO_FRONT)                    # rank 1 is never launched
+    with pytest.raises(BibfsError, match="watchdog"):
+        c0.fetch(s, t)
+    c0.reset(); c1.reset()
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    for flags in (F_NO_FRONT, 0):
+        c0.launch(s, t, flags)
+        with torch.cuda.stream(side):
+            c1.launch(s, t, flags)
+        r = c0.fetch(s, t)
+        if r.status == 100:
+            c0.resume()
+            with torch.cuda.stream(side):
+                c1.resume()
+            r = c0.fetch(s, t)
+        with torch.cuda.stream(side):
+            c1.fetch(s, t, want_path=False)
+        assert r.length == oracle.query(s, t, want_path=False).length
+        bb.validate_path(g_cpu, s, t, r.path, r.length)
+    c0.close(); c1.close()
