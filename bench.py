@@ -224,6 +224,8 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
     wall_dev_loop = time.perf_counter() - wall0
     launches = bb.lib().bibfs_launch_count() - launches0
     if world > 1:
+        if os.environ.get("BIBFS_BENCH_VERBOSE"):
+            print(f"[rank {rank}] {config}: own event-timed search ms mean {ms.mean():.4f} min {ms.min():.4f} max {ms.max():.4f}", file=sys.stderr, flush=True)
         tms = torch.from_numpy(ms).to(dev)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)     # max over ranks, per step
         ms = tms.cpu().numpy()
@@ -236,7 +238,7 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
         e0 = time.perf_counter()
         for s, t, length, _, _ in queries[W:W + K]:
             pinned_np[0], pinned_np[1] = s, t
-            r = solver.query(-1 & 0x7FFFFFFF, -1 & 0x7FFFFFFF, want_path=True, pinned_query=pinned)
+            r = solver.query(-1 & 0x7FFFFFFF, -1 & 0x7FFFFFFF, want_path=True, pinned_query=pinned, timing="device")
             assert r.length == length
             d2h += 64 + 4 * (length + 1)
         barrier()

@@ -117,6 +117,7 @@ def _declare(lib):
         "bibfs_ctx_resume": (C.c_int, [vp, vp]),
         "bibfs_ipc_export": (C.c_int, [vp, vp, P(u64)]),
         "bibfs_ipc_import": (C.c_int, [vp, u64, P(vp)]),
+        "bibfs_copy_device": (C.c_int, [vp, vp, C.c_size_t, vp]),
         "bibfs_ctx_query": (C.c_int, [vp, u32, u32, vp, u32, vp]),
         "bibfs_ctx_result": (C.c_int, [vp, P(Result), vp, u32, vp]),
         "bibfs_ctx_query_result": (C.c_int, [vp, u32, u32, vp, u32, P(Result), vp, u32, vp]),

@@ -115,16 +115,48 @@ class SearchContext:
             out.append((buf.raw, int(off.value)))
         return tuple(out)
 
-    def attach_graph_ipc(self, rank: int, shared: tuple) -> None:
+    def _import(self, shared: tuple):
         ptrs = []
+        for item in shared:
+            p = C.c_void_p(0)
+            if item is not None:
+                check(lib().bibfs_ipc_import(C.create_string_buffer(item[0], 64), item[1], C.byref(p)))
+            ptrs.append(p)
+        return ptrs
+
+    def attach_graph_ipc(self, rank: int, shared: tuple) -> None:
+        """Map rank `rank`'s col / vertex-record tensors (exported by graph_ipc in its process) on this device."""
         with torch.cuda.device(self.device):
-            for item in shared:
-                p = C.c_void_p(0)
-                if item is not None:
-                    check(lib().bibfs_ipc_import(C.create_string_buffer(item[0], 64), item[1], C.byref(p)))
-                ptrs.append(p)
-        if ptrs[0].value and ptrs[1].value:
-            check(lib().bibfs_ctx_set_peer_graph(self._h, rank, ptrs[0], ptrs[1]))
+            col, vrec = self._import(shared)
+            if col.value and vrec.value:
+                check(lib().bibfs_ctx_set_peer_graph(self._h, rank, col, vrec))
+
+    def replicate_records(self, shared_by_rank: list) -> bool:
+        """Keep a LOCAL, contiguous copy of every shard's vertex records (32 bytes per vertex: the index the front kernel
+        walks) instead of reading the other shards' records over NVLink: a round of the front kernel then costs what it
+        costs on one GPU, and the copy is streamed into L2 at query start like on one GPU.  The adjacency itself (col)
+        stays with its owner; rows longer than six entries are still read from there."""
+        B, P = self.graph.partition.B, self.nranks
+        with torch.cuda.device(self.device):
+            full = torch.zeros(B * P * 8, dtype=torch.int32, device=self.device)
+            cols = {}
+            for r in range(P):
+                lo, hi = self.graph.partition.range(r)
+                if r in self.graph.shards:
+                    s = self.graph.shards[r]
+                    src, cols[r] = (s.vrec.data_ptr() if s.vrec is not None else 0), (s.col.data_ptr() if s.col.numel() else s.row_ptr.data_ptr())
+                else:
+                    col, vrec = self._import(shared_by_rank[r])
+                    src, cols[r] = vrec.value or 0, col.value or 0
+                if hi > lo and not src:
+                    return False
+                if hi > lo:
+                    check(lib().bibfs_copy_device(full.data_ptr() + r * B * 32, src, (hi - lo) * 32, self._stream()))
+            torch.cuda.synchronize(self.device)
+            self._record_replica = full
+            for r in range(P):
+                check(lib().bibfs_ctx_set_peer_graph(self._h, r, C.c_void_p(cols[r]), C.c_void_p(full.data_ptr() + r * B * 32)))
+        return True
 
     def resume(self) -> None:
         check(lib().bibfs_ctx_resume(self._h, self._stream()))

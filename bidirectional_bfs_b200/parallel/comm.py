@@ -13,7 +13,7 @@ import os
 import torch
 import torch.distributed as dist
 
-from .._lib import F_NO_PATH
+from .._lib import F_DEVICE_CLOCK, F_NO_PATH
 from ..graph import Graph
 from ..ops.search import PathResult, SearchContext
 
@@ -41,7 +41,10 @@ class DistributedSolver:
     """Rank-local handle of a P-GPU search; every rank must make the same calls in the same order."""
     variant = "multi-gpu"
 
-    def __init__(self, graph: Graph, **ctx_kw):
+    def __init__(self, graph: Graph, record_replica_mb: int | None = None, **ctx_kw):
+        """record_replica_mb: rank 0 keeps a local copy of the other shards' vertex records (32 bytes per vertex, the index
+        its front kernel walks) when all of them fit this many MB; beyond that it reads them through the peer mappings.
+        Default 1024 (BIBFS_RECORD_REPLICA_MB overrides; 0 = never).  The CSR itself is never replicated."""
         if not dist.is_initialized():
             raise RuntimeError("torch.distributed is not initialised (use init_distributed())")
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
@@ -59,9 +62,15 @@ class DistributedSolver:
             # can answer small queries alone (csrc/front.cuh)
             shared = [None] * self.world
             dist.all_gather_object(shared, self.ctx.graph_ipc(0))
-            for r, sh in enumerate(shared):
-                if r != self.rank:
-                    self.ctx.attach_graph_ipc(r, sh)
+            if record_replica_mb is None:
+                record_replica_mb = int(os.environ.get("BIBFS_RECORD_REPLICA_MB", "1024"))
+            self.records_replicated = False
+            if self.rank == 0 and graph.n * 32 <= record_replica_mb << 20:
+                self.records_replicated = self.ctx.replicate_records(shared)
+            if not self.records_replicated:
+                for r, sh in enumerate(shared):
+                    if r != self.rank:
+                        self.ctx.attach_graph_ipc(r, sh)
         dist.barrier()
 
     def launch(self, src, dst, flags=0, pinned_query=None):
@@ -70,9 +79,13 @@ class DistributedSolver:
     def fetch(self, src, dst, want_path=True) -> PathResult:
         return self.ctx.fetch(src, dst, want_path, self.variant)
 
-    def query(self, src, dst, want_path=True, flags=0, pinned_query=None, timing=None) -> PathResult:   # timing: always CUDA events
+    def query(self, src, dst, want_path=True, flags=0, pinned_query=None, timing="events") -> PathResult:
+        """timing="events": CUDA events around this rank's launches; "device": no events, completion by polling the pinned
+        result, search_ms from the device clock (the latency path, like GpuSolver.query's default)."""
         if not want_path:
             flags |= F_NO_PATH
+        if timing == "device":
+            flags |= F_DEVICE_CLOCK
         return self.ctx.query(src, dst, flags, want_path, pinned_query, self.variant)
 
     def query_many(self, srcs, dsts, want_path=False) -> list[PathResult]:

@@ -1693,8 +1693,21 @@ static_assert(SMEM_BYTES <= 227 * 1024, "shared memory of the search kernel");
 // the kernel
 // ------------------------------------------------------------------------------------------
 template <bool MULTI>
-__global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant__ KParams K) {
+__global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant__ KParams Kp) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    // The parameters are copied into shared memory and every function below works on THAT copy.  The device functions
+    // of this file take `const KParams&`; a reference to a __grid_constant__ parameter is a generic pointer into the
+    // parameter window, every K.x behind it is a generic load (~0.5 us, and reloaded after each asm memory clobber),
+    // and those loads sat on the dependent chain of the levels (measured in the pair tier: +2 us per round from
+    // owner_of's reciprocal alone).  Shared memory answers in ~30 cycles.
+    __shared__ KParams sK;
+    {
+        const u32* src = reinterpret_cast<const u32*>(&Kp);
+        u32* dst = reinterpret_cast<u32*>(&sK);
+        for (u32 i = threadIdx.x; i < sizeof(KParams) / 4; i += BFS_THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    const KParams& K = sK;
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
     PairSmem& ps = *reinterpret_cast<PairSmem*>(smem_raw + sizeof(Smem));
     KT_STAMP(0);
@@ -1881,7 +1894,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 {
                     PairIO io;
                     io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
-                    pair_run<false>(K, E, st, s_acc, s_qvalid, ps, io, C->q_src, C->q_dst);
+                    pair_run<false, PT_CAP_SMALL>(K, E, st, s_acc, s_qvalid, ps, io, C->q_src, C->q_dst);
                 }
                 KT_STAMP(4);
                 if (st.phase != PH_TD_SOLO) { if (warp == 0) publish_and_wake(); __syncthreads(); continue; }

@@ -251,7 +251,13 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     K.qn = c->qn;
     K.async_peers = c->async_peers ? 1u : 0u;
     // records + visited words of a small graph are streamed into L2 by the idle CTAs at query start (<= 24 MB: a fifth of L2)
-    if (c->vrec_all[0] && c->hosts0 && (u64)c->B * 32ull <= (24ull << 20)) K.warm_lines = (u32)(((u64)(c->multi ? c->B : c->d.n) * 32ull + 127ull) / 128ull);
+    if (c->vrec_all[0] && c->hosts0) {
+        // how many of the records are local and contiguous behind rank 0's (its own shard; every shard with a record replica)
+        u32 local = 1;
+        while (local < c->d.nranks && c->vrec_all[local] == (const char*)c->vrec_all[0] + (size_t)local * c->B * 32) ++local;
+        const u64 bytes = local == c->d.nranks ? (u64)c->d.n * 32ull : (u64)c->B * 32ull;
+        if (bytes <= (24ull << 20)) K.warm_lines = (u32)((bytes + 127ull) / 128ull);
+    }
 }
 
 // Does this query start with the front kernel?  Needs every rank's vertex records on this device.  Policy (contexts that
@@ -284,6 +290,7 @@ extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const u
                                uint32_t flags, void* stream) {
     if (!c) return fail("NULL ctx");
     if (flags & ~BIBFS_F_ALL) return fail("unknown query flag bits 0x%x", flags & ~BIBFS_F_ALL);
+    if (reinterpret_cast<uintptr_t>(h_query_pinned) & 7u) return fail("h_query_pinned must be 8-byte aligned");
     for (u32 r = 0; r < c->d.nranks; ++r)
         if (!c->arena_all[r]) return fail("rank %u is not attached", r);
     DeviceGuard g(c->device);
@@ -293,7 +300,7 @@ extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const u
     fill_params(c, K, src, dst, false, flags);
     K.h_query = h_query_pinned;          // read by the kernel itself: pinned memory is device-visible under UVA
     const bool want_path = !(flags & BIBFS_F_NO_PATH);
-    c->last_lean = c->hosts_all && !c->multi && (flags & BIBFS_F_DEVICE_CLOCK);
+    c->last_lean = (flags & BIBFS_F_DEVICE_CLOCK) != 0;
     c->last_flags = flags;
     c->pend_src = src; c->pend_dst = dst; c->pend_flags = flags; c->pend_hq = h_query_pinned;
     if (!c->last_lean) BIBFS_CUDA_TRY(cudaEventRecord(c->ev[0], st));
@@ -307,7 +314,9 @@ extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const u
             K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = HOST_PATH_WORDS; K.h_seq = c->h_seq;
             if (front_launch(K, c->multi, st)) return 1;
         } else if (c->async_peers) {
-            c->last_fused = false;
+            c->last_fused = true;         // the wait kernel delivers the verdict to the pinned buffer itself
+            K.fuse_path = 1u;
+            K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = 0; K.h_seq = c->h_seq;
             if (wait_launch(K, st)) return 1;
         } else {
             c->last_fused = false;
@@ -597,6 +606,13 @@ cuMemGetAddressRange_t address_range_fn() {
 std::mutex g_ipc_mu;
 std::map<std::pair<int, std::string>, char*> g_ipc_open;
 }  // namespace
+
+extern "C" int bibfs_copy_device(void* d_dst, const void* d_src, size_t bytes, void* stream) {
+    if (!bytes) return 0;
+    if (!d_dst || !d_src) return fail("NULL argument");
+    BIBFS_CUDA_TRY(cudaMemcpyAsync(d_dst, d_src, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
+    return 0;
+}
 
 extern "C" int bibfs_ipc_export(const void* d_ptr, void* handle64, uint64_t* offset) {
     if (!d_ptr || !handle64 || !offset) return fail("NULL argument");

@@ -40,7 +40,7 @@
 #else
 #define PT_MARK(slot, dep)                                                                                   \
     do {                                                                                                     \
-        if (threadIdx.x == 0 && (K.flags & 0x80000000u)) {                                                   \
+        if (threadIdx.x == 0 && mark_on) {                                                                   \
             u64 _t;                                                                                          \
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t) : "l"((u64)(dep)) : "memory");             \
             *reinterpret_cast<volatile u64*>(E.vis) = _t;                                                    \
@@ -48,22 +48,25 @@
     } while (0)
 #endif
 
-constexpr u32 PT_CAP = 512;          // frontier entries per side
+constexpr u32 PT_CAP_SMALL = 512;    // frontier entries per side: inside the general kernel (shares its shared memory) ...
+constexpr u32 PT_CAP_FRONT = 1024;   // ... and in the front kernel (frontiers beyond the CTA's 512 threads are walked in passes)
 constexpr u32 PT_MAXDEG = 32;        // a discovered row at least this long ends the tier
 constexpr int PT_NB = 6;             // neighbours inlined in a vertex record
 constexpr int PT_W = 4;              // adjacency entries per lane per batch beyond the inlined ones
 enum : u32 { PT_HIT = 1u, PT_BIG = 2u, PT_OVF = 4u };
 
-struct PairSmem {
+template <u32 CAP>
+struct PairSmemT {
     u32 cnt[3][2];                   // vertices discovered in the round, per side (three rotating sets)
     u32 flag[3];
     u32 meet_new[3];                 // smallest vertex a claim of the round found marked by the other side
     u32 tr_edges[3][2];              // (tracing only) adjacency entries per side
     u32 meet_old[2];                 // old-hit test: smallest frontier vertex of side x that carries the other side's mark
     unsigned long long edges, visited;
-    alignas(16) u32 fv[2][2][PT_CAP];            // frontier vertices [side][buffer]
-    alignas(16) uint4 fr[2][2][PT_CAP][2];       // ... and their records
+    alignas(16) u32 fv[2][2][CAP];               // frontier vertices [side][buffer]
+    alignas(16) uint4 fr[2][2][CAP][2];          // ... and their records
 };
+using PairSmem = PairSmemT<PT_CAP_SMALL>;
 
 __device__ __forceinline__ void reds_or(u32* p, u32 v) {
     asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(ptx::smem_addr(p)), "r"(v) : "memory");
@@ -80,20 +83,31 @@ struct PairIO {
 };
 
 // Returns with st.phase == PH_DONE (result written) or with the level state handed over (decide_next done).
-template <bool MULTI>
-__device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, Acc& acc, u32* qvalid, PairSmem& ps, const PairIO io,
+template <bool MULTI, u32 PT_CAP>
+__device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, Acc& acc, u32* qvalid, PairSmemT<PT_CAP>& ps, const PairIO io,
                                       const u32 src, const u32 dst) {
     const u32 tid = threadIdx.x, lane = tid & 31;
     Ctrl* const C = E.C;
     u64* const g_vis = E.vis;
     const bool tracing = (K.flags & BIBFS_F_TRACE) != 0;
+    // Everything the round loop needs from the kernel parameters is copied into registers here: K is reached through a
+    // pointer, and every asm statement of the loop is a memory clobber, so each K.x inside it would be a fresh load on
+    // the chain of the round (owner_of's reciprocal alone cost two of them per round: +2 us per round, measured).
+    const u64 div_b = K.div_B;
+    const bool mark_on = (K.flags & 0x80000000u) != 0; (void)mark_on;      // never set (see PT_MARK)
+    const u32* const e_col = E.col;
+    u32* const log0 = io.log[0]; u32* const log1 = io.log[1];
+    u32* const par0 = io.par[0]; u32* const par1 = io.par[1];
+    auto owner = [div_b](u32 v) -> u32 { return (u32)__umul64hi(div_b, (u64)v); };
     // record / adjacency bases indexed by the GLOBAL vertex id resp. the owner's row start
     __shared__ const uint4* s_vrecb[MAXR];
     __shared__ const u32* s_colb[MAXR];
     if (MULTI && tid < K.P) { s_vrecb[tid] = K.vrec[tid] - 2 * (size_t)tid * K.B; s_colb[tid] = K.col[tid]; }
     const uint4* const vrec0 = MULTI ? nullptr : K.vrec[E.me] - 2 * (size_t)E.lo;
-    auto rec_of = [&](u32 v) -> const uint4* { return (MULTI ? s_vrecb[owner_of(K, v)] : vrec0) + 2 * (size_t)v; };
-    auto ld_rec_if = [&](bool on, const uint4* p) -> uint4 { return MULTI ? ptx::ld_v4_sys_if(on, p) : ptx::ld_v4_gpu_if(on, p); };
+    auto rec_of = [&](u32 v) -> const uint4* { return (MULTI ? s_vrecb[owner(v)] : vrec0) + 2 * (size_t)v; };
+    // (records and adjacency never change: gpu-scope loads are enough also when they come from a peer's memory, and
+    //  system-scope loads were measured 2 us per round slower even on local memory)
+    auto ld_rec_if = [&](bool on, const uint4* p) -> uint4 { return ptx::ld_v4_gpu_if(on, p); };
     if (MULTI) __syncthreads();
     // level state, identical in every thread
     u32 n0 = 1, n1 = 1, base0 = 1, base1 = 1, d0 = 0, d1 = 0, levels = 0, buf0 = 0, buf1 = 0, par = 0;
@@ -122,17 +136,21 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
         const u32 mx = max(n0, n1), mn = min(n0, n1);
         if (mn > PT_CAP) break;
         const u32 pad0 = (n0 + 31u) & ~31u;
-        const bool both = (mx <= 4u * mn || mx <= 32u) && pad0 + n1 <= (u32)BFS_THREADS && mx <= PT_CAP;
+        const bool both = (mx <= 4u * mn || mx <= 32u) && mx <= PT_CAP;
         const bool e0 = both || n0 <= n1, e1 = both || n1 < n0;
         const u32 off1 = e0 ? pad0 : 0u;                        // the target side starts on a warp boundary
-        const u32 side = (e0 && (!e1 || tid < off1)) ? 0u : 1u;      // warp-uniform
-        const u32 idx = side ? tid - off1 : tid;
-        const bool have = side ? (e1 && tid >= off1 && idx < n1) : (e0 && tid < n0);
+        const u32 span = off1 + (e1 ? n1 : 0u);                 // frontier positions of the round; the CTA walks them in passes of 512
+        const bool wide = (e0 ? n0 : 0u) + (e1 ? n1 : 0u) > 64u;  // aggregate the cursor reservations per warp
+        const u32 pb0 = buf0, pb1 = buf1;
+        u32 fl = 0;
+        for (u32 vt = tid; (vt & ~31u) < span; vt += BFS_THREADS) {
+        const u32 side = (e0 && (!e1 || vt < off1)) ? 0u : 1u;      // warp-uniform
+        const u32 idx = side ? vt - off1 : vt;
+        const bool have = side ? (e1 && vt >= off1 && idx < n1) : (e0 && vt < n0);
         const u32 sh = 32u * side, osh = 32u - sh;
         const u32 buf = side ? buf1 : buf0;
         const u32 base = side ? base1 : base0;
-        const bool wide = (e0 ? n0 : 0u) + (e1 ? n1 : 0u) > 64u;  // aggregate the cursor reservations per warp
-        u32 u = 0, deg = 0, r0 = 0, fl = 0;
+        u32 u = 0, deg = 0, r0 = 0;
         uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
         if (have) {
             u = ps.fv[side][buf][idx];
@@ -146,9 +164,9 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
         u32* const out_v = ps.fv[side][buf ^ 1u];
         uint4(*const out_r)[2] = ps.fr[side][buf ^ 1u];
         u32* const cursor = &ps.cnt[par][side];
-        u32* const qs = io.log[side];
-        u32* const pp = io.par[side];
-        const u32* const g_col = MULTI ? s_colb[owner_of(K, u)] : E.col;
+        u32* const qs = side ? log1 : log0;
+        u32* const pp = side ? par1 : par0;
+        const u32* const g_col = MULTI ? s_colb[owner(u)] : e_col;
 
         // one batch of W candidates: claims and record fetches in flight together (branch-free: idle slots OR a zero
         // into the thread's scratch word and re-read the thread's own record)
@@ -214,12 +232,13 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
 #pragma unroll
                 for (int k = 0; k < PT_W; ++k) {
                     const u32* a = g_col + r0 + ((u32)k < left ? e + k : 0u);
-                    c[k] = MULTI ? ptx::ld_relaxed_sys(a) : ptx::ld_relaxed_gpu(a);
+                    c[k] = ptx::ld_relaxed_gpu(a);
                 }
                 batch(std::integral_constant<int, PT_W>{}, c, min(left, (u32)PT_W));
             }
-            if (fl) reds_or(&ps.flag[par], fl);
         }
+        }       // passes
+        if (fl) reds_or(&ps.flag[par], fl);
         PT_MARK(4, fl);
         __syncthreads();
         PT_MARK(5, tid);
@@ -235,6 +254,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
                 ps.tr_edges[z][0] = 0; ps.tr_edges[z][1] = 0;
             }
         }
+        const u32 c0_prev = n0, c1_prev = n1;        // sizes of the frontiers this round expanded
         if (e0) { d0 += 1; levels += 1; base0 += c0; n0 = c0; buf0 ^= 1u; visited += c0; }
         if (e1) { d1 += 1; levels += 1; base1 += c1; n1 = c1; buf1 ^= 1u; visited += c1; }
         par = (par + 1u) % 3u;
@@ -246,9 +266,14 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
             length = (i32)(d0 + d1); meet = mnew; depth_s = d0;
             if (e0 && e1) {
                 // old-hit test (see the header): is a vertex of an expanded frontier marked by the other side now?
-                if (have) {
-                    const u64 w = ptx::ld_relaxed_gpu(&g_vis[u >> 5]);
-                    if ((w >> ((u & 31u) + osh)) & 1ull) ptx::reds_min(&ps.meet_old[side], u);
+                for (u32 vt = tid; vt < span; vt += BFS_THREADS) {
+                    const u32 side = vt < off1 ? 0u : 1u;
+                    const u32 idx = side ? vt - off1 : vt;
+                    if (idx < (side ? c1_prev : c0_prev)) {
+                        const u32 u = ps.fv[side][side ? pb1 : pb0][idx];
+                        const u64 w = ptx::ld_relaxed_gpu(&g_vis[u >> 5]);
+                        if ((w >> ((u & 31u) + 32u - 32u * side)) & 1ull) ptx::reds_min(&ps.meet_old[side], u);
+                    }
                 }
                 __syncthreads();
                 const u32 m0 = ps.meet_old[0], m1 = ps.meet_old[1];

@@ -214,6 +214,8 @@ int bibfs_ctx_set_peer_graph(bibfs_ctx* ctx, uint32_t rank, const uint32_t* d_co
  * handle of the allocation it lies in plus its offset; the importer maps each allocation once per process and device
  * and keeps it mapped.  Used for the col / vertex-record tensors of the one-process-per-GPU deployment. */
 int bibfs_ipc_export(const void* d_ptr, void* handle64, uint64_t* offset);
+/* device-to-device copy between raw pointers (e.g. from an imported peer mapping into a local tensor) */
+int bibfs_copy_device(void* d_dst, const void* d_src, size_t bytes, void* stream);
 int bibfs_ipc_import(const void* handle64, uint64_t offset, void** d_ptr);
 /* continue a query that returned BIBFS_STATUS_HANDED_OVER: call it on every context of the group, then fetch the results */
 int bibfs_ctx_resume(bibfs_ctx* ctx, void* stream);
@@ -235,7 +237,7 @@ int bibfs_ctx_reset(bibfs_ctx* ctx, void* stream);
 #define BIBFS_STATUS_HANDED_OVER 100
 
 /* Enqueue one query: (optional) H2D of the query from pinned host memory, the persistent
- * search kernel, and the path kernel.  h_query_pinned = {src,dst} in pinned memory, or NULL
+ * search kernel, and the path kernel.  h_query_pinned = {src,dst} in pinned memory (8-byte aligned), or NULL
  * to pass src/dst by value.  Asynchronous on `stream`.  Every rank must call it with the same
  * arguments. */
 int bibfs_ctx_query(bibfs_ctx* ctx, uint32_t src, uint32_t dst, const uint32_t* h_query_pinned,

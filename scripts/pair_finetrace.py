@@ -7,10 +7,11 @@ import bidirectional_bfs_b200 as bb
 import bench
 L = bb.lib()
 cfg = sys.argv[1] if len(sys.argv) > 1 else "er100k"
+P = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 info = bench.prepare(cfg, 1, 25)
 spec = bench.make_spec(bb, cfg, 1)
-g = bb.Graph.generate(spec, device="cuda:0")
-s = bb.GpuSolver(g)
+g = bb.Graph.generate(spec, device="cuda:0", nranks=P)
+s = bb.GpuSolver(g) if P == 1 else bb.MultiGpuSolver(g)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
 out = np.zeros((512, 8), dtype=np.uint64); lv = C.c_uint32(0); kt = np.zeros(32, dtype=np.uint64)
 for a, b, Lq, _, _ in info["queries"][:4]: s.query(a, b)
