@@ -127,6 +127,15 @@ struct Ctrl {
     unsigned long long hub_packed;       // (entries << 40) | chunks, appended atomically
     u32 sent[2][MAXR];
     unsigned long long edges_total;
+    // wide rounds of the front kernel's cluster (pair_tier.cuh): counters shared by its CTAs, three rotating sets
+    struct alignas(128) Wide {
+        u32 cnt[3][2];
+        u32 flag[3];
+        u32 meet[3];
+        u32 tr_edges[3][2];
+        u32 meet_old[2];
+        unsigned long long edges;
+    } wide;
     // front kernel (k_front) <-> peers: see "query flow" in bfs_dev.cu
     alignas(128) u64 arrive[MAXR];       // at rank 0: arrive[p] = queries rank p has entered (one process per GPU only)
     alignas(128) u64 verdict[2][VD_WORDS];   // written by rank 0: payload | (u32)query number << 32, [query number & 1]
@@ -178,6 +187,7 @@ struct KParams {
     u32 src, dst, query_in_ctrl;   // query by value, or (query_in_ctrl) read from Ctrl::q_src/q_dst
     u32 resume;                    // k_bibfs continues a search the front kernel handed over (no query start)
     u32 async_peers;               // the other ranks are driven by other processes: arrival words order the queries
+    u32 wide_min;                  // front kernel: frontier positions of a round from which its whole cluster takes the round
     u64 qn;                        // number of this query in the context group (host counter, identical on every rank)
     u64 div_B;                     // 2^64 / B rounded up: owner(v) = umulhi64(div_B, v), exact for 32-bit v
     const u32* h_query;            // pinned host memory holding {src,dst}: read by the kernel itself (zero copy), or null
@@ -197,9 +207,9 @@ int bfs_max_ctas_per_device(bool multi, int* out);
 int bfs_max_ctas_clustered(u32 cluster, int* out);
 #if defined(__CUDACC__) || defined(BIBFS_WITH_CUDA_RUNTIME)
 int bfs_launch(const KParams& K, bool multi, cudaStream_t st);
-int front_launch(const KParams& K, bool multi, cudaStream_t st);
+int front_launch(const KParams& K, bool multi, u32 cluster, cudaStream_t st);
 int wait_launch(const KParams& K, cudaStream_t st);
-int front_prepare(bool multi);
+int front_prepare(bool multi, u32* cluster_out);
 #endif
 
 }  // namespace bibfs

@@ -40,6 +40,7 @@
 // With P "virtual ranks" hosted by one launch (blockIdx.x / cpr = rank) the very same protocol
 // runs on a single GPU, which is how the multi-rank path is tested without 8 GPUs.
 #include "bfs.h"
+#include <cstdlib>
 #include <type_traits>
 #include "ptx.cuh"
 
@@ -1894,7 +1895,9 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 {
                     PairIO io;
                     io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
-                    pair_run<false, PT_CAP_SMALL>(K, E, st, s_acc, s_qvalid, ps, io, C->q_src, C->q_dst);
+                    pair_run<false, PT_CAP_SMALL>(K, E, ps, io, C->q_src, C->q_dst, false);
+                    if (tid == 0) pair_finish<false>(K, E, st, s_acc, s_qvalid, ps.out, ps.edges);
+                    __syncthreads();
                 }
                 KT_STAMP(4);
                 if (st.phase != PH_TD_SOLO) { if (warp == 0) publish_and_wake(); __syncthreads(); continue; }
@@ -2135,17 +2138,58 @@ extern "C" int bibfs_debug_read_kt(uint64_t* out32) {
 
 constexpr unsigned FRONT_WARM_CTAS = 48;
 
-int front_prepare(bool multi) {
+template <bool MULTI>
+static int front_cluster_fit(u32 cluster, int* fit) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cluster);
+    cfg.blockDim = dim3(BFS_THREADS);
+    cfg.dynamicSmemBytes = sizeof(FrontSmem);
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    *fit = 0;
+    return cudaOccupancyMaxActiveClusters(fit, k_front<MULTI>, &cfg) == cudaSuccess ? 0 : 1;
+}
+
+// opt in to the front kernel's shared memory and pick the size of its cluster: 16 (beyond the portable 8; B200 takes it),
+// else 8, 4, 2, 1.  BIBFS_FRONT_CLUSTER=n overrides.
+int front_prepare(bool multi, u32* cluster_out) {
     if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_front<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrontSmem)));
     else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_front<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrontSmem)));
+    if (multi) cudaFuncSetAttribute(k_front<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    else cudaFuncSetAttribute(k_front<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    cudaGetLastError();
+    const char* want = getenv("BIBFS_FRONT_CLUSTER");
+    u32 cl = want ? (u32)atoi(want) : 16u;
+    if (cl < 1 || cl > 16 || (cl & (cl - 1))) cl = 16;
+    for (; cl > 1; cl /= 2) {
+        int fit = 0;
+        const int rc = multi ? front_cluster_fit<true>(cl, &fit) : front_cluster_fit<false>(cl, &fit);
+        cudaGetLastError();
+        if (rc == 0 && fit >= 1) break;
+    }
+    *cluster_out = cl;
     return 0;
 }
 
-int front_launch(const KParams& K, bool multi, cudaStream_t st) {
-    const unsigned grid = K.warm_lines ? 1u + FRONT_WARM_CTAS : 1u;      // CTA 0 runs the query; the others only warm L2
-    if (multi) k_front<true><<<grid, BFS_THREADS, sizeof(FrontSmem), st>>>(K);
-    else k_front<false><<<grid, BFS_THREADS, sizeof(FrontSmem), st>>>(K);
-    BIBFS_KERNEL_CHECK();
+int front_launch(const KParams& K, bool multi, u32 cluster, cudaStream_t st) {
+    // the first cluster runs the query; the clusters behind it only warm L2 (graphs that fit it with room to spare)
+    const unsigned warm = K.warm_lines ? (FRONT_WARM_CTAS + cluster - 1) / cluster * cluster : 0u;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cluster + warm);
+    cfg.blockDim = dim3(BFS_THREADS);
+    cfg.dynamicSmemBytes = sizeof(FrontSmem);
+    cfg.stream = st;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = cluster > 1 ? 1 : 0;
+    if (multi) BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front<true>, K));
+    else BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front<false>, K));
+    count_launch();
     return 0;
 }
 

@@ -34,6 +34,11 @@ struct bibfs_ctx {
     bool hosts0 = false;         // this context hosts rank 0 (runs the front kernel, walks the path, delivers the result)
     bool hosts_all = false;      // ... and every other rank too (single rank, or virtual ranks)
     bool async_peers = false;    // peers live in other processes (attached through IPC): each rank resumes on its own verdict
+    u32 front_cluster = 1;       // thread-block cluster of the front kernel (wide rounds)
+    // the cluster launch costs ~1.5 us more than a single CTA: contexts whose queries never go wide drop it, and take it
+    // back when a single-CTA front kernel has to hand a search over
+    bool front_narrow = false;
+    int no_wide_streak = 0;
     int front_mode = 0;          // BIBFS_FRONT: 0 policy, 1 always, 2 never
     int front_score = 0;         // policy: rises when the front kernel hands over after a few levels (hub graphs), falls otherwise
     u64 qn = 0;                  // queries issued (identical on every rank of the group)
@@ -123,7 +128,7 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     c->hosts0 = desc->rank_lo == 0;
     c->hosts_all = desc->vranks == desc->nranks;
     for (u32 i = 0; i < desc->vranks; ++i) { c->col_all[desc->rank_lo + i] = desc->d_col[i]; c->vrec_all[desc->rank_lo + i] = desc->d_vrec[i]; }
-    if (c->hosts0 && front_prepare(c->multi)) { delete c; return 1; }
+    if (c->hosts0 && front_prepare(c->multi, &c->front_cluster)) { delete c; return 1; }
     for (u32 i = 0; i < desc->vranks; ++i)
         if (reinterpret_cast<uintptr_t>(desc->d_vrec[i]) & 31u) { delete c; return fail("d_vrec of hosted rank %u is not 32-byte aligned", desc->rank_lo + i); }
     for (u32 i = 0; i < desc->vranks; ++i) {
@@ -249,6 +254,7 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
         K.vrec[r] = reinterpret_cast<const uint4*>(c->vrec_all[r]);
     }
     K.qn = c->qn;
+    { static const u32 wm = getenv("BIBFS_WIDE_MIN") ? (u32)atoi(getenv("BIBFS_WIDE_MIN")) : 512u; K.wide_min = wm; }
     K.async_peers = c->async_peers ? 1u : 0u;
     // records + visited words of a small graph are streamed into L2 by the idle CTAs at query start (<= 24 MB: a fifth of L2)
     if (c->vrec_all[0] && c->hosts0) {
@@ -312,7 +318,7 @@ extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const u
             c->last_fused = true;
             K.fuse_path = want_path ? 2u : 1u;
             K.h_out = reinterpret_cast<u32*>(c->h_stage); K.h_out_words = HOST_PATH_WORDS; K.h_seq = c->h_seq;
-            if (front_launch(K, c->multi, st)) return 1;
+            if (front_launch(K, c->multi, c->front_narrow ? 1u : c->front_cluster, st)) return 1;
         } else if (c->async_peers) {
             c->last_fused = true;         // the wait kernel delivers the verdict to the pinned buffer itself
             K.fuse_path = 1u;
@@ -387,6 +393,13 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     }
     const bool was_front = c->stage == 1;
     if (wait_stage(c, st)) return 1;
+    if (was_front && c->hosts0) {
+        const bool wide = (hr->rounds_paired >> 31) != 0, handed0 = hr->status == ST_ESCALATED;
+        if (c->front_narrow) { if (handed0) { c->front_narrow = false; c->no_wide_streak = 0; } }
+        else if (wide) c->no_wide_streak = 0;
+        else if (++c->no_wide_streak >= 8 && !getenv("BIBFS_FRONT_CLUSTER")) c->front_narrow = true;
+    }
+    hr->rounds_paired &= 0x7FFFFFFFu;
     if (was_front) {
         const bool handed = hr->status == ST_ESCALATED;
         // policy input: a hand-over after a handful of levels means the front kernel only added a launch
@@ -412,7 +425,7 @@ extern "C" int bibfs_ctx_result(bibfs_ctx* c, bibfs_result* res, uint32_t* path,
     res->edges_scanned = hr->edges_scanned;
     res->vertices_visited = hr->vertices_visited;
     res->levels_grid = hr->levels_grid;
-    res->levels_paired = hr->rounds_paired;
+    res->levels_paired = hr->rounds_paired & 0x7FFFFFFFu;
     res->path_len = 0;
     float a = 0;
     if (c->last_lean) {

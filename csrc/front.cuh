@@ -24,6 +24,9 @@
 
 namespace {
 
+// wide rounds stage their discoveries in the record mirror of the narrow rounds: (vertex, parent) pairs, per side
+constexpr u32 WIDE_STAGE_CAP = sizeof(PairSmemT<PT_CAP_FRONT>::fr) / 16;
+
 struct FrontSmem {
     LevelState st;
     Acc acc;
@@ -158,15 +161,16 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
     FrontSmem& fs = *reinterpret_cast<FrontSmem*>(smem_raw);
     LevelState& st = fs.st;
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (blockIdx.x > 0) {
-        // helper CTAs (launched only for graphs that fit L2 with room to spare): stream rank 0's vertex records and its
+    const u32 cl_n = ptx::cluster_nctarank(), cl_rank = ptx::cluster_ctarank();
+    if (blockIdx.x >= cl_n) {
+        // warm-up CTAs, the clusters behind the first one (launched only for graphs that fit L2 with room to spare): stream rank 0's vertex records and its
         // visited words into L2 and leave — a cold record costs ~700 ns on the chain of a round, a hit 154 ns, and one
         // CTA could not issue the ~25,000 prefetches of a 100k-vertex graph without stalling its own rounds
         const char* rec = reinterpret_cast<const char*>(K.vrec[0]);
         const char* vw = reinterpret_cast<const char*>(vis_of(K, 0));
         const u32 vis_lines = (K.L.nw * 8u + 127u) / 128u;
-        const u32 stride = (gridDim.x - 1u) * BFS_THREADS;
-        for (u32 i = (blockIdx.x - 1u) * BFS_THREADS + tid; i < K.warm_lines + vis_lines; i += stride)
+        const u32 stride = (gridDim.x - cl_n) * BFS_THREADS;
+        for (u32 i = (blockIdx.x - cl_n) * BFS_THREADS + tid; i < K.warm_lines + vis_lines; i += stride)
             ptx::prefetch_l2(i < K.warm_lines ? rec + 128ull * i : vw + 128ull * (i - K.warm_lines));
         return;
     }
@@ -194,6 +198,29 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
     } else {
         io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
     }
+    if (cl_rank > 0) {
+        // the other CTAs of the working cluster: wait until the leader CTA has decided whether its rounds go wide (it pushes
+        // its state into this CTA's shared memory before it arrives at the barrier), take part if so, and leave
+        ptx::cluster_sync_all();
+        if (fs.ps.out.go_wide) pair_wide<MULTI>(K, E, io, fs.ps.out, cl_n, cl_rank, reinterpret_cast<u64*>(&fs.ps.fr[0][0][0][0]), WIDE_STAGE_CAP);
+        return;
+    }
+    bool cl_pending = cl_n > 1;       // the helpers are waiting at the start-up barrier
+    // leader CTA: hand `fs.ps.out` to the helpers and release them (all threads)
+    auto release_helpers = [&]() {
+        if (!cl_pending) return;
+        cl_pending = false;
+        if (fs.ps.out.go_wide && tid == 0) {
+            Ctrl::Wide& W = C->wide;
+            for (u32 z = 0; z < 3; ++z) { W.cnt[z][0] = 0; W.cnt[z][1] = 0; W.flag[z] = 0; W.meet[z] = NO_V; W.tr_edges[z][0] = 0; W.tr_edges[z][1] = 0; }
+            W.meet_old[0] = NO_V; W.meet_old[1] = NO_V; W.edges = 0;
+        }
+        if (tid < 16u * (cl_n - 1u)) {
+            const u32 c = 1u + tid / 16u, i = tid % 16u;
+            ptx::dsmem_st(ptx::dsmem_map(ptx::smem_addr(&fs.ps.out), c) + 4u * i, reinterpret_cast<const u32*>(&fs.ps.out)[i]);
+        }
+        ptx::cluster_sync_all();
+    };
     // ---- query start
     u32 src = K.src, dst = K.dst;
     if (K.h_query) {
@@ -248,8 +275,20 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
     KT_STAMP(2);
     if (st.phase != PH_DONE && !fs.fail && tier) {
         KT_STAMP(3);
-        pair_run<MULTI, PT_CAP_FRONT>(K, E, st, fs.acc, fs.qvalid, fs.ps, io, src, dst);
+        pair_run<MULTI, PT_CAP_FRONT>(K, E, fs.ps, io, src, dst, cl_n > 1);
+        u64 edges = fs.ps.edges;
+        if (fs.ps.out.go_wide) {
+            release_helpers();
+            edges += pair_wide<MULTI>(K, E, io, fs.ps.out, cl_n, 0u, reinterpret_cast<u64*>(&fs.ps.fr[0][0][0][0]), WIDE_STAGE_CAP);
+        }
+        if (tid == 0) pair_finish<MULTI>(K, E, st, fs.acc, fs.qvalid, fs.ps.out, edges);
+        __syncthreads();
         KT_STAMP(4);
+    }
+    if (cl_pending) {                 // the rounds never went wide (or there were none): let the helpers go
+        if (tid == 0) fs.ps.out.go_wide = 0;
+        __syncthreads();
+        release_helpers();
     }
     if (fs.fail) {
         if (tid == 0) { st.status = 1; st.length = -1; st.phase = PH_DONE; write_result(K, C, st); atomicExch(&C->abort_flag, 1u); }

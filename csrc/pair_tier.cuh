@@ -55,6 +55,21 @@ constexpr int PT_NB = 6;             // neighbours inlined in a vertex record
 constexpr int PT_W = 4;              // adjacency entries per lane per batch beyond the inlined ones
 enum : u32 { PT_HIT = 1u, PT_BIG = 2u, PT_OVF = 4u };
 
+// State of the tier when its rounds stop: written by thread 0 of pair_run, pushed to the other CTAs of the front kernel's
+// cluster when the rounds go WIDE (pair_wide), and finally turned into the LevelState by pair_finish.
+struct PairOut {
+    u32 n[2], base[2], d[2];         // frontier sizes, log cursors, depths per side
+    u32 levels, visited;
+    i32 length;                      // -2: still searching (hand over / go wide)
+    u32 meet, depth_s, depth_t;
+    u32 go_wide;                     // the rounds continue on the whole cluster
+    u32 went_wide;                   // ... and did
+    u32 pad[2];
+};
+static_assert(sizeof(PairOut) == 64, "pushed over DSMEM as 16 words");
+constexpr u32 PT_WIDE_MIN = 160;     // frontier positions of a round from which the whole cluster takes it
+constexpr u32 PT_WIDE_CAP = 1u << 16;  // ... and the frontier size per side at which even the cluster hands over
+
 template <u32 CAP>
 struct PairSmemT {
     u32 cnt[3][2];                   // vertices discovered in the round, per side (three rotating sets)
@@ -63,6 +78,7 @@ struct PairSmemT {
     u32 tr_edges[3][2];              // (tracing only) adjacency entries per side
     u32 meet_old[2];                 // old-hit test: smallest frontier vertex of side x that carries the other side's mark
     unsigned long long edges, visited;
+    PairOut out;                     // where the rounds stopped (pair_run / pair_wide -> pair_finish)
     alignas(16) u32 fv[2][2][CAP];               // frontier vertices [side][buffer]
     alignas(16) uint4 fr[2][2][CAP][2];          // ... and their records
 };
@@ -70,6 +86,12 @@ using PairSmem = PairSmemT<PT_CAP_SMALL>;
 
 __device__ __forceinline__ void reds_or(u32* p, u32 v) {
     asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(ptx::smem_addr(p)), "r"(v) : "memory");
+}
+
+// positions of a paired round (both sides when they are of comparable size, else the smaller one)
+__device__ __forceinline__ u32 both_span(u32 n0, u32 n1) {
+    const u32 mx = max(n0, n1), mn = min(n0, n1);
+    return (mx <= 4u * mn || mx <= 32u) ? n0 + n1 : mn;
 }
 
 // What the tier works on.  Single rank: the rank's own queue / parent arrays (so that the general tiers continue on
@@ -82,12 +104,13 @@ struct PairIO {
     u32* par[2];        // parent of a vertex per side, indexed by the vertex id
 };
 
-// Returns with st.phase == PH_DONE (result written) or with the level state handed over (decide_next done).
+// Narrow rounds: one CTA.  Leaves its state in ps.out (thread 0) and the adjacency entries it inspected in ps.edges;
+// pair_finish turns that into the LevelState.  allow_wide: the CTA leads a cluster (front kernel) and stops with
+// out.go_wide = 1 when a round is large enough for all of it (pair_wide).
 template <bool MULTI, u32 PT_CAP>
-__device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, Acc& acc, u32* qvalid, PairSmemT<PT_CAP>& ps, const PairIO io,
-                                      const u32 src, const u32 dst) {
+__device__ __noinline__ void pair_run(const KParams& K, Env E, PairSmemT<PT_CAP>& ps, const PairIO io,
+                                      const u32 src, const u32 dst, const bool allow_wide) {
     const u32 tid = threadIdx.x, lane = tid & 31;
-    Ctrl* const C = E.C;
     u64* const g_vis = E.vis;
     const bool tracing = (K.flags & BIBFS_F_TRACE) != 0;
     // Everything the round loop needs from the kernel parameters is copied into registers here: K is reached through a
@@ -95,6 +118,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
     // the chain of the round (owner_of's reciprocal alone cost two of them per round: +2 us per round, measured).
     const u64 div_b = K.div_B;
     const bool mark_on = (K.flags & 0x80000000u) != 0; (void)mark_on;      // never set (see PT_MARK)
+    const u32 wide_min = K.wide_min;
     const u32* const e_col = E.col;
     u32* const log0 = io.log[0]; u32* const log1 = io.log[1];
     u32* const par0 = io.par[0]; u32* const par1 = io.par[1];
@@ -129,12 +153,13 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
     if (tid < 2) ps.meet_old[tid] = NO_V;
     i32 length = -2;                 // -2: still searching
     u32 meet = NO_V, depth_s = 0, depth_t = 0;
-    u32 visited = 0;
+    u32 visited = 0, go_wide = 0;
 
     while (!leave) {
         // ---- which sides expand: both, unless one frontier dwarfs the other (then the smaller, ties -> source, like v1)
         const u32 mx = max(n0, n1), mn = min(n0, n1);
         if (mn > PT_CAP) break;
+        if (allow_wide && both_span(n0, n1) > wide_min) { go_wide = 1; break; }
         const u32 pad0 = (n0 + 31u) & ~31u;
         const bool both = (mx <= 4u * mn || mx <= 32u) && mx <= PT_CAP;
         const bool e0 = both || n0 <= n1, e1 = both || n1 < n0;
@@ -284,6 +309,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
             break;
         }
         if (n0 == 0 || n1 == 0) { length = -1; depth_s = d0; depth_t = d1; break; }      // a side is exhausted: no path
+        if (allow_wide && (f & PT_OVF) && !(f & PT_BIG)) { go_wide = 1; break; }     // the log holds what the mirror dropped
         if (f & (PT_BIG | PT_OVF)) break;
     }
     // ---- leave the tier: totals, then either the verdict or the hand-over to the general machinery
@@ -295,26 +321,261 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, LevelState& st, A
     }
     __syncthreads();
     if (tid == 0) {
-        st.nf[0] = n0; st.nf[1] = n1;
-        st.depth[0] = d0; st.depth[1] = d1;
-        st.levels = levels;
-        st.q_lo[0] = base0 - n0; st.q_hi[0] = base0;
-        st.q_lo[1] = base1 - n1; st.q_hi[1] = base1;
-        acc.q_tail[0] = base0; acc.q_tail[1] = base1;
-        acc.new_count = 0; acc.meet_local = NO_V; acc.edges = 0;
-        qvalid[0] = 0; qvalid[1] = 0;                   // the general tiers read the frontier from the queue
-        st.edges_total += ps.edges;
-        st.visited_total += visited;
-        st.rounds_paired = levels;
-        if (length != -2) {
-            st.length = length; st.meet = length >= 0 ? meet : NO_V;
-            st.depth[0] = depth_s; st.depth[1] = depth_t;
-            st.phase = PH_DONE;
-            write_result(K, C, st);
-        } else if (!MULTI) {
-            decide_next(K, st);
-            if (st.phase == PH_DONE) write_result(K, C, st);
-        }
+        PairOut& o = ps.out;
+        o.n[0] = n0; o.n[1] = n1; o.base[0] = base0; o.base[1] = base1; o.d[0] = d0; o.d[1] = d1;
+        o.levels = levels; o.visited = visited; o.length = length; o.meet = meet; o.depth_s = depth_s; o.depth_t = depth_t;
+        o.go_wide = go_wide; o.went_wide = 0;
     }
     __syncthreads();
+}
+
+// Turn the tier's final state into the LevelState the rest of the machinery uses (thread 0 of the leader CTA; callers
+// synchronise).  `edges`: adjacency entries the tier inspected.
+template <bool MULTI>
+__device__ __noinline__ void pair_finish(const KParams& K, const Env& E, LevelState& st, Acc& acc, u32* qvalid, const PairOut& o, u64 edges) {
+    st.nf[0] = o.n[0]; st.nf[1] = o.n[1];
+    st.depth[0] = o.d[0]; st.depth[1] = o.d[1];
+    st.levels = o.levels;
+    st.q_lo[0] = o.base[0] - o.n[0]; st.q_hi[0] = o.base[0];
+    st.q_lo[1] = o.base[1] - o.n[1]; st.q_hi[1] = o.base[1];
+    acc.q_tail[0] = o.base[0]; acc.q_tail[1] = o.base[1];
+    acc.new_count = 0; acc.meet_local = NO_V; acc.edges = 0;
+    qvalid[0] = 0; qvalid[1] = 0;                   // the general tiers read the frontier from the queue
+    st.edges_total += edges;
+    st.visited_total += o.visited;
+    st.rounds_paired = o.levels | (o.went_wide ? 0x80000000u : 0u);      // bit 31: wide rounds were used (launch policy of ctx.cu)
+    if (o.length != -2) {
+        st.length = o.length; st.meet = o.length >= 0 ? o.meet : NO_V;
+        st.depth[0] = o.depth_s; st.depth[1] = o.depth_t;
+        st.phase = PH_DONE;
+        write_result(K, E.C, st);
+    } else if (!MULTI) {
+        decide_next(K, st);
+        if (st.phase == PH_DONE) write_result(K, E.C, st);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// WIDE rounds: the whole thread-block cluster of the front kernel.
+//
+// One SM's load/store path is what limits a round of more than a couple of hundred frontier
+// vertices (a 512-thread narrow round takes ~5 us), so from PT_WIDE_MIN positions on the round is
+// dealt over all CTAs of the cluster.  Differences to the narrow round:
+//   * the frontier is read from the LOG in global memory (every reached vertex is appended there
+//     anyway) and the record of a frontier vertex is fetched by the thread that expands it — two
+//     more L2 trips per round, but no record fetch per CANDIDATE and no shared-memory mirror, so
+//     the frontier size is not bounded by one CTA's shared memory (a 4096 x 4096 grid stays here
+//     for all of its 8,190 levels);
+//   * cursors, flags and the meeting vertex live in Ctrl::wide (L2 atomics, one reservation per
+//     warp), the round ends at barrier.cluster, and every thread of every CTA derives the next
+//     round from those counters, exactly as in the narrow round;
+//   * rows of >= PT_MAXDEG entries — their length is only known when their record is read — are
+//     walked by their whole warp; the round after that the tier hands over (PT_BIG).
+// All CTAs call this together (the leader after pair_run, the others from the start-up barrier);
+// `o` is each CTA's own copy of the state and is updated in place.  Returns the adjacency entries
+// inspected by the whole cluster (valid in the leader CTA).
+// ------------------------------------------------------------------------------------------
+//   * discoveries are STAGED per CTA in shared memory ((vertex, parent) pairs in the space the narrow rounds use for
+//     their frontier mirror) and flushed with ONE reservation per CTA and side on the global cursor: 256 warps
+//     bumping the same L2 word serialise at ~40 ns apiece (10 us per round, measured on the 4096 x 4096 grid).
+template <bool MULTI>
+__device__ __noinline__ u64 pair_wide(const KParams& K, Env E, const PairIO io, PairOut& o, const u32 cl_n, const u32 cl_rank,
+                                      u64* const stage /* 2 x stage_cap entries of this CTA's shared memory */, const u32 stage_cap) {
+    const u32 tid = threadIdx.x, lane = tid & 31;
+    Ctrl::Wide& W = E.C->wide;
+    u64* const g_vis = E.vis;
+    const bool tracing = (K.flags & BIBFS_F_TRACE) != 0;
+    const u64 div_b = K.div_B;
+    const u32* const e_col = E.col;
+    u32* const log0 = io.log[0]; u32* const log1 = io.log[1];
+    u32* const par0 = io.par[0]; u32* const par1 = io.par[1];
+    auto owner = [div_b](u32 v) -> u32 { return (u32)__umul64hi(div_b, (u64)v); };
+    __shared__ const uint4* s_vrecb[MAXR];
+    __shared__ const u32* s_colb[MAXR];
+    if (MULTI && tid < K.P) { s_vrecb[tid] = K.vrec[tid] - 2 * (size_t)tid * K.B; s_colb[tid] = K.col[tid]; }
+    const uint4* const vrec0 = MULTI ? nullptr : K.vrec[E.me] - 2 * (size_t)E.lo;
+    auto rec_of = [&](u32 v) -> const uint4* { return (MULTI ? s_vrecb[owner(v)] : vrec0) + 2 * (size_t)v; };
+    __shared__ u32 s_cnt[2], s_gbase[2];
+    if (tid < 2) s_cnt[tid] = 0;
+    __syncthreads();
+    u32 n0 = o.n[0], n1 = o.n[1], base0 = o.base[0], base1 = o.base[1], d0 = o.d[0], d1 = o.d[1], levels = o.levels, visited = o.visited;
+    u32 par = 0;
+    u64 my_edges = 0;
+    i32 length = -2;
+    u32 meet = NO_V, depth_s = 0, depth_t = 0;
+    const u32 gthreads = cl_n * BFS_THREADS, gt0 = cl_rank * BFS_THREADS + tid;
+
+    while (true) {
+        const u32 mx = max(n0, n1), mn = min(n0, n1);
+        if (mn > PT_WIDE_CAP) break;
+        const u32 pad0 = (n0 + 31u) & ~31u;
+        const bool both = (mx <= 4u * mn || mx <= 32u) && mx <= PT_WIDE_CAP;
+        const bool e0 = both || n0 <= n1, e1 = both || n1 < n0;
+        const u32 off1 = e0 ? pad0 : 0u;
+        const u32 span = off1 + (e1 ? n1 : 0u);
+        const u32 flo0 = base0 - n0, flo1 = base1 - n1;          // the frontiers are the last n entries of the logs
+        u32 fl = 0;
+        for (u32 vt = gt0; (vt & ~31u) < span; vt += gthreads) {
+            const u32 side = (e0 && (!e1 || vt < off1)) ? 0u : 1u;      // warp-uniform
+            const u32 idx = side ? vt - off1 : vt;
+            const bool have = side ? (e1 && vt >= off1 && idx < n1) : (e0 && vt < n0);
+            const u32 sh = 32u * side, osh = 32u - sh;
+            const u32 base = side ? base1 : base0;
+            u32* const qs = side ? log1 : log0;
+            u32* const pp = side ? par1 : par0;
+            u32* const cursor = &W.cnt[par][side];
+            u64* const stg = stage + (size_t)side * stage_cap;
+            u32 u = 0;
+            if (have) u = ptx::ld_relaxed_gpu(qs + (side ? flo1 : flo0) + idx);
+            const uint4* rp = rec_of(u);
+            const uint4 ra = ptx::ld_v4_gpu_if(have, rp), rb = ptx::ld_v4_gpu_if(have, rp + 1);
+            const u32 deg = ra.x, r0 = ra.y;
+            my_edges += deg;
+            if (tracing && deg) atomicAdd(&W.tr_edges[par][side], deg);
+            const u32* const g_col = MULTI ? s_colb[owner(u)] : e_col;
+            // claims of one batch of W candidates of parent `pu`; reservation per warp on the global cursor
+            auto batch = [&](auto Wc, const u32* v, const u32 nact, const u32 pu) {
+                constexpr int Wn = decltype(Wc)::value;
+                u64 old[Wn];
+#pragma unroll
+                for (int k = 0; k < Wn; ++k) {
+                    const bool act = (u32)k < nact;
+                    old[k] = ptx::atom_or_gpu_if(act, &g_vis[(act ? v[k] : u) >> 5], 1ull << ((v[k] & 31u) + sh));
+                }
+                const u32 shz = sh + ptx::zero_after(old[Wn - 1]);
+                u32 newmask = 0, meetmask = 0;
+#pragma unroll
+                for (int k = 0; k < Wn; ++k) {
+                    const u32 isnew = (u32)k < nact ? (((u32)(old[k] >> ((v[k] & 31u) + shz)) & 1u) ^ 1u) : 0u;
+                    newmask |= isnew << k;
+                    meetmask |= (isnew & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
+                }
+                u32 slot = warp_reserve((u32)__popc(newmask), [&](u32 n) { return ptx::atoms_add(&s_cnt[side], n); });
+                if (newmask) {
+#pragma unroll
+                    for (int k = 0; k < Wn; ++k) {
+                        if ((newmask >> k) & 1u) {
+                            if (slot < stage_cap) stg[slot] = (u64)v[k] | ((u64)pu << 32);
+                            else { qs[base + atomicAdd(cursor, 1u)] = v[k]; pp[v[k]] = pu; }      // stage full: straight to the log
+                            ++slot;
+                        }
+                    }
+                    if (meetmask) {
+                        fl |= PT_HIT;
+#pragma unroll
+                        for (int k = 0; k < Wn; ++k)
+                            if ((meetmask >> k) & 1u) atomicMin(&W.meet[par], v[k]);
+                    }
+                }
+            };
+            if (__any_sync(FULL, have)) {
+                const u32 sdeg = deg < PT_MAXDEG ? deg : 0u;       // rows a lane walks alone
+                {
+                    const u32 c[PT_NB] = {ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
+                    batch(std::integral_constant<int, PT_NB>{}, c, min(sdeg, (u32)PT_NB), u);
+                }
+                for (u32 e = PT_NB; __any_sync(FULL, e < sdeg); e += PT_W) {
+                    u32 c[PT_W];
+                    const u32 left = sdeg > e ? sdeg - e : 0u;
+#pragma unroll
+                    for (int k = 0; k < PT_W; ++k) c[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((u32)k < left ? e + k : 0u));
+                    batch(std::integral_constant<int, PT_W>{}, c, min(left, (u32)PT_W), u);
+                }
+                // long rows: the whole warp walks one row at a time, 4 x 32 entries per step
+                u32 big = __ballot_sync(FULL, deg >= PT_MAXDEG);
+                if (big) fl |= PT_BIG;
+                while (big) {
+                    const u32 sl = __ffs(big) - 1;
+                    big &= big - 1;
+                    const u32 uu = __shfl_sync(FULL, u, sl), rr = __shfl_sync(FULL, r0, sl), dd = __shfl_sync(FULL, deg, sl);
+                    const u32* const cc = (MULTI ? s_colb[owner(uu)] : e_col) + rr;
+                    for (u32 e = 0; e < dd; e += 32u * PT_W) {
+                        u32 c[PT_W];
+                        u32 nact = 0;
+#pragma unroll
+                        for (int k = 0; k < PT_W; ++k) {
+                            const u32 i = e + 32u * k + lane;
+                            c[k] = ptx::ld_relaxed_gpu(cc + (i < dd ? i : 0u));
+                            nact += i < dd ? 1u : 0u;          // (entries of a lane are consecutive in k: i grows with k)
+                        }
+                        batch(std::integral_constant<int, PT_W>{}, c, nact, uu);
+                    }
+                }
+            }
+        }
+        if (fl) atomicOr(&W.flag[par], fl);
+        // ---- flush the CTA's stage: one reservation per side
+        __syncthreads();
+        if (tid < 2) { const u32 c = min(s_cnt[tid], stage_cap); s_gbase[tid] = c ? atomicAdd(&W.cnt[par][tid], c) : 0u; }
+        __syncthreads();
+        for (u32 side = 0; side < 2; ++side) {
+            const u32 c = min(s_cnt[side], stage_cap);
+            u32* const qs = side ? log1 : log0;
+            u32* const pp = side ? par1 : par0;
+            const u32 gb = (side ? base1 : base0) + s_gbase[side];
+            const u64* const stg = stage + (size_t)side * stage_cap;
+            for (u32 i = tid; i < c; i += BFS_THREADS) {
+                const u64 e = stg[i];
+                qs[gb + i] = (u32)e;
+                pp[(u32)e] = (u32)(e >> 32);
+            }
+        }
+        __syncthreads();
+        if (tid < 2) s_cnt[tid] = 0;
+        ptx::cluster_sync_all();
+        // ---- round end
+        const u32 c0 = ptx::ld_relaxed_gpu(&W.cnt[par][0]), c1 = ptx::ld_relaxed_gpu(&W.cnt[par][1]);
+        const u32 f = ptx::ld_relaxed_gpu(&W.flag[par]), mnew = ptx::ld_relaxed_gpu(&W.meet[par]);
+        if (cl_rank == 0 && tid == 0) {
+            const u32 z = (par + 2u) % 3u;       // last read before this barrier, next used after the next one
+            if (tracing) {
+                const u64 now = ptx::globaltimer_ns();
+                if (e0) trace_level(K, E, 0, PH_TD_SOLO | 16u | 32u, n0, c0, W.tr_edges[par][0], now);
+                if (e1) trace_level(K, E, 1, PH_TD_SOLO | 16u | 32u, n1, c1, W.tr_edges[par][1], now);
+            }
+            W.cnt[z][0] = 0; W.cnt[z][1] = 0; W.flag[z] = 0; W.meet[z] = NO_V; W.tr_edges[z][0] = 0; W.tr_edges[z][1] = 0;
+        }
+        const u32 p0 = n0, p1 = n1;
+        if (e0) { d0 += 1; levels += 1; base0 += c0; n0 = c0; visited += c0; }
+        if (e1) { d1 += 1; levels += 1; base1 += c1; n1 = c1; visited += c1; }
+        par = (par + 1u) % 3u;
+        if (f & PT_HIT) {
+            length = (i32)(d0 + d1); meet = mnew; depth_s = d0;
+            if (e0 && e1) {
+                // old-hit test: a vertex of an expanded frontier that carries the other side's mark now
+                for (u32 vt = gt0; vt < span; vt += gthreads) {
+                    const u32 side = vt < off1 ? 0u : 1u;
+                    const u32 idx = side ? vt - off1 : vt;
+                    if (idx < (side ? p1 : p0)) {
+                        const u32 u = ptx::ld_relaxed_gpu((side ? log1 + flo1 : log0 + flo0) + idx);
+                        const u64 w = ptx::ld_relaxed_gpu(&g_vis[u >> 5]);
+                        if ((w >> ((u & 31u) + 32u - 32u * side)) & 1ull) atomicMin(&W.meet_old[side], u);
+                    }
+                }
+                ptx::cluster_sync_all();
+                const u32 m0 = ptx::ld_relaxed_gpu(&W.meet_old[0]), m1 = ptx::ld_relaxed_gpu(&W.meet_old[1]);
+                if (m0 != NO_V) { length = (i32)(d0 + d1 - 1u); meet = m0; depth_s = d0 - 1u; }
+                else if (m1 != NO_V) { length = (i32)(d0 + d1 - 1u); meet = m1; depth_s = d0; }
+            }
+            depth_t = (u32)length - depth_s;
+            break;
+        }
+        if (n0 == 0 || n1 == 0) { length = -1; depth_s = d0; depth_t = d1; break; }
+        if (f & PT_BIG) break;
+    }
+    // ---- totals; every CTA leaves with the same state
+    {
+        u64 e = my_edges;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) e += __shfl_xor_sync(FULL, e, d);
+        if (lane == 0 && e) atomicAdd(&W.edges, (unsigned long long)e);
+    }
+    ptx::cluster_sync_all();
+    if (tid == 0) {
+        o.n[0] = n0; o.n[1] = n1; o.base[0] = base0; o.base[1] = base1; o.d[0] = d0; o.d[1] = d1;
+        o.levels = levels; o.visited = visited; o.length = length; o.meet = meet; o.depth_s = depth_s; o.depth_t = depth_t;
+        o.go_wide = 0; o.went_wide = 1;
+    }
+    __syncthreads();
+    return ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&W.edges));
 }

@@ -41,7 +41,8 @@ def test_front_kernel_answers_small_queries_alone(bb, nranks):
 def test_hand_over_to_the_fused_levels(bb, nranks):
     """Searches that outgrow the front kernel: a grid whose diagonal passes 512 vertices, R-MAT hubs after a level or two."""
     for spec, pairs in ((bb.grid_spec(1400, 1100), [(0, 1400 * 1100 - 1), (1399, 1400 * 1099), (5, 700 * 1400 + 9)]),
-                        (bb.rmat_spec(15, edgefactor=16, seed=3), None), (bb.er_spec(6000, 9.0 / 6000, seed=4), None)):
+                        (bb.rmat_spec(15, edgefactor=16, seed=3), None), (bb.er_spec(6000, 9.0 / 6000, seed=4), None),
+                        (bb.er_spec(300000, 40.0 / 300000, seed=5), None)):
         g_cpu = bb.Graph.generate(spec)
         oracle = bb.SerialSolver(g_cpu, policy=1)
         solver = bb.MultiGpuSolver(bb.Graph.generate(spec, device="cuda:0", nranks=nranks))
@@ -49,20 +50,40 @@ def test_hand_over_to_the_fused_levels(bb, nranks):
         for s, t in (pairs or query_pairs(spec.n, 40, nranks + 11)):
             r = _check(bb, g_cpu, oracle, solver, s, t)
             handed += int(r.length is not None and r.levels > r.levels_paired)
-        assert handed > 0 or spec.kind == 0       # (the dense ER graph is small enough for rank 0 to finish alone)
+        assert handed > 0 or spec.kind != 1       # (grids and ER graphs may well be finished by rank 0's cluster alone)
         solver.close()
 
 
 def test_single_rank_front_then_general_kernel(bb):
+    """A grid stays with the front kernel's cluster (wide rounds); a graph with rows of >= 32 entries next to a long
+    sparse approach is handed to the general kernel after some paired levels."""
     spec = bb.grid_spec(1500, 1300)
     g_cpu = bb.Graph.generate(spec)
     solver = bb.GpuSolver(bb.Graph.generate(spec, device="cuda:0"))
     for timing in ("device", "events"):
         r = solver.query(0, spec.n - 1, timing=timing)
-        assert r.length == 1499 + 1299 and 0 < r.levels_paired < r.levels
+        assert r.length == 1499 + 1299 and r.levels_paired == r.levels
         bb.validate_path(g_cpu, 0, spec.n - 1, r.path, r.length)
         r = solver.query(7, 7 + 1500 * 2 + 3, timing=timing)
         assert r.length == 5 and r.levels_paired == r.levels
+        tr_flags = 1
+        r = solver.query(0, spec.n - 1, flags=tr_flags, timing=timing)
+        tr = solver.ctx.trace()
+        assert len(tr) == r.levels and any(x["mode"] & 32 for x in tr), "no wide round in the trace"
+    solver.close()
+    # two paths of 40 vertices into a clique of 64: paired levels first, then rows of 63 entries -> general kernel
+    import numpy as np
+    k, L = 64, 40
+    edges = [(i, j) for i in range(k) for j in range(i + 1, k)]
+    a = list(range(k, k + L)); b = list(range(k + L, k + 2 * L))
+    edges += [(a[i], a[i + 1]) for i in range(L - 1)] + [(b[i], b[i + 1]) for i in range(L - 1)] + [(a[-1], 0), (b[-1], 1)]
+    n = k + 2 * L
+    e = np.array(edges, dtype=np.uint32)
+    g_cpu = bb.Graph.from_edges(n, e)
+    solver = bb.GpuSolver(bb.Graph.from_edges(n, e, device="cuda:0"))
+    r = solver.query(a[0], b[0])
+    assert r.length == 2 * L + 1 and 0 < r.levels_paired < r.levels
+    bb.validate_path(g_cpu, a[0], b[0], r.path, r.length)
     solver.close()
 
 

@@ -71,12 +71,12 @@ def test_pair_tier_special_graphs_and_grid(bb):
             if want is not None:
                 bb.validate_path(g_cpu, s, t, r.path, want)
         solver.close()
-    # a grid: the frontier outgrows the tier after a few hundred levels -> hand-over to the cluster / grid tiers
+    # a grid: the frontier outgrows one CTA after a few hundred levels -> wide rounds on the front kernel's cluster
     spec = bb.grid_spec(1500, 1300)
     g = bb.Graph.generate(spec, device="cuda:0")
     solver = bb.GpuSolver(g)
     r = solver.query(0, spec.n - 1)
-    assert r.length == 1499 + 1299 and r.levels_paired > 0 and r.levels > r.levels_paired
+    assert r.length == 1499 + 1299 and r.levels_paired > 0
     bb.validate_path(bb.Graph.generate(spec), 0, spec.n - 1, r.path, r.length)
     r = solver.query(5, 5 + 1500 * 3)
     assert r.length == 3
