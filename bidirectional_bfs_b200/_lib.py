@@ -50,7 +50,7 @@ class CtxDesc(C.Structure):
         ("n", C.c_uint32), ("nranks", C.c_uint32), ("rank_lo", C.c_uint32), ("vranks", C.c_uint32),
         ("d_row_ptr", C.c_void_p * MAX_RANKS), ("d_col", C.c_void_p * MAX_RANKS),
         ("max_path", C.c_uint32), ("solo_threshold", C.c_uint32), ("bottom_up_div", C.c_uint32),
-        ("max_ctas", C.c_uint32), ("watchdog_ms", C.c_uint32),
+        ("max_ctas", C.c_uint32), ("watchdog_ms", C.c_uint32), ("max_degree", C.c_uint32),
         ("d_vrec", C.c_void_p * MAX_RANKS),
     ]
 
@@ -105,7 +105,7 @@ def _declare(lib):
         "bibfs_validate_path": (C.c_int, [u32, vp, vp, u32, u32, vp, u32]),
         "bibfs_block_size": (u32, [u32, u32]),
         "bibfs_vrec_bytes": (C.c_size_t, [u32]),
-        "bibfs_vrec_build_device": (C.c_int, [vp, vp, u32, u64, vp, vp]),
+        "bibfs_vrec_build_device": (C.c_int, [vp, vp, u32, u64, vp, vp, vp]),
         "bibfs_ctx_create": (C.c_int, [P(vp), P(CtxDesc)]),
         "bibfs_ctx_destroy": (C.c_int, [vp]),
         "bibfs_ctx_ipc_handle": (C.c_int, [vp, u32, vp]),

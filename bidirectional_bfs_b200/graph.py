@@ -27,6 +27,7 @@ class Shard:
     row_ptr: torch.Tensor
     col: torch.Tensor
     vrec: torch.Tensor | None = None      # vertex records (csrc/vrec_dev.cu), built on first use by a search context
+    max_degree: int = 0                   # longest row of the shard (known once the records are built)
 
     @property
     def nnz(self) -> int:
@@ -43,8 +44,10 @@ class Shard:
             with torch.cuda.device(dev):
                 out = torch.empty(rows * 8, dtype=torch.int32, device=dev)
                 colp = self.col.data_ptr() if self.col.numel() else self.row_ptr.data_ptr()
-                check(lib().bibfs_vrec_build_device(self.row_ptr.data_ptr(), colp, rows, self.nnz, out.data_ptr(),
+                mx = torch.zeros(1, dtype=torch.int32, device=dev)
+                check(lib().bibfs_vrec_build_device(self.row_ptr.data_ptr(), colp, rows, self.nnz, out.data_ptr(), mx.data_ptr(),
                                                     torch.cuda.current_stream(dev).cuda_stream))
+                self.max_degree = int(mx.item())
             self.vrec = out
         return self.vrec
 

@@ -133,6 +133,12 @@ class MultiGpuSolver:
         self = cls.__new__(cls)
         self.graph = graphs[0]
         self.ctxs = []
+        degs = []
+        for g in graphs:
+            (sh,) = g.shards.values()
+            sh.vertex_records()
+            degs.append(sh.max_degree if (sh.vrec is not None or sh.hi == sh.lo) else None)
+        ctx_kw.setdefault("max_degree", 0 if None in degs else max(degs))
         for g in graphs:
             (rank,) = g.shards.keys()
             with torch.cuda.device(g.device):
@@ -231,6 +237,7 @@ class BatchSolver:
                 d.d_col[0] = s.col.data_ptr() if s.col.numel() else s.row_ptr.data_ptr()
                 vr = s.vertex_records()
                 d.d_vrec[0] = vr.data_ptr() if vr is not None else None
+                d.max_degree = s.max_degree if vr is not None else 0
                 free, _ = torch.cuda.mem_get_info(graph.device)
                 per_lane = 20 * graph.n + (1 << 22)            # parents + queues + bitmaps, roughly
                 lanes = max(1, min(lanes, int(free * 0.6 // per_lane)))

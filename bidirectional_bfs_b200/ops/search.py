@@ -57,7 +57,7 @@ _NVTX = bool(os.environ.get("BIBFS_NVTX"))
 
 class SearchContext:
     def __init__(self, graph, rank_lo=0, vranks=None, max_path=0, solo_threshold=0, bottom_up_div=0,
-                 max_ctas=0, watchdog_ms=0, pair_tier=True):
+                 max_ctas=0, watchdog_ms=0, pair_tier=True, max_degree=None):
         if graph.device.type != "cuda":
             raise ValueError("SearchContext needs a CUDA graph")
         self.graph = graph
@@ -74,6 +74,11 @@ class SearchContext:
             if pair_tier:
                 vr = s.vertex_records()
                 d.d_vrec[i] = vr.data_ptr() if vr is not None else None
+        # longest row of the whole graph: known when every shard is hosted here, else the caller passes it (0 = unknown)
+        if max_degree is None:
+            hosted_all = self.vranks == graph.nranks and all(graph.shards[r].vrec is not None or graph.shards[r].hi == graph.shards[r].lo for r in graph.shards)
+            max_degree = max((graph.shards[r].max_degree for r in graph.shards), default=0) if (pair_tier and hosted_all) else 0
+        d.max_degree = int(max_degree)
         d.max_path = max_path or min(graph.n + 1, 1 << 24)
         d.solo_threshold, d.bottom_up_div, d.max_ctas, d.watchdog_ms = solo_threshold, bottom_up_div, max_ctas, watchdog_ms
         self.max_path = d.max_path

@@ -52,6 +52,12 @@ class DistributedSolver:
             raise ValueError("graph must hold exactly this rank's shard of a world-sized partition")
         self.graph = graph
         with torch.cuda.device(graph.device):
+            # longest row of the whole graph (the search skips its long-row handling when there is none)
+            sh = graph.shards[self.rank]
+            sh.vertex_records()
+            mx = torch.tensor([sh.max_degree if (sh.vrec is not None or sh.hi == sh.lo) else 1 << 30], dtype=torch.int64, device=graph.device)
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            ctx_kw.setdefault("max_degree", int(mx.item()) if int(mx.item()) < (1 << 30) else 0)
             self.ctx = SearchContext(graph, self.rank, 1, **ctx_kw)
             handles = [None] * self.world
             dist.all_gather_object(handles, self.ctx.ipc_handle(0))

@@ -135,6 +135,7 @@ struct Ctrl {
         u32 tr_edges[3][2];
         u32 meet_old[2];
         unsigned long long edges;
+        unsigned long long long_packed[3];   // rows of >= PT_MAXDEG entries met in the round: (entries << 40) | chunks
     } wide;
     // front kernel (k_front) <-> peers: see "query flow" in bfs_dev.cu
     alignas(128) u64 arrive[MAXR];       // at rank 0: arrive[p] = queries rank p has entered (one process per GPU only)
@@ -187,6 +188,7 @@ struct KParams {
     u32 src, dst, query_in_ctrl;   // query by value, or (query_in_ctrl) read from Ctrl::q_src/q_dst
     u32 resume;                    // k_bibfs continues a search the front kernel handed over (no query start)
     u32 async_peers;               // the other ranks are driven by other processes: arrival words order the queries
+    u32 long_rows;                 // the graph has rows of >= 32 entries (or nobody knows): wide rounds deal them over the cluster
     u32 wide_min;                  // front kernel: frontier positions of a round from which its whole cluster takes the round
     u64 qn;                        // number of this query in the context group (host counter, identical on every rank)
     u64 div_B;                     // 2^64 / B rounded up: owner(v) = umulhi64(div_B, v), exact for 32-bit v

@@ -939,6 +939,8 @@ struct HubChunk {
     u32 bytes;         // size of the bulk copy
     const u32* src;    // 16-byte aligned start of the chunk in col
     bool valid;
+    u64 A;             // index of src in col
+    u32 nch_word;      // the entry's nchunks word (wide rounds of the front kernel keep the side in bit 31)
 };
 
 // whole warp, same c in every lane.  The entries are ordered by chunk_base (slot and base come from one atomic): a
@@ -972,6 +974,8 @@ __device__ __forceinline__ HubChunk hub_lookup(const HubEntry* H, u32 ne, const 
     h.hi = (u32)(Aend - A);
     h.bytes = ((h.hi * 4u) + 15u) & ~15u;
     h.src = col + A;
+    h.A = A;
+    h.nch_word = nch;
     return h;
 }
 

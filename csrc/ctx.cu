@@ -254,6 +254,7 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
         K.vrec[r] = reinterpret_cast<const uint4*>(c->vrec_all[r]);
     }
     K.qn = c->qn;
+    K.long_rows = (c->d.max_degree == 0 || c->d.max_degree >= 32) ? 1u : 0u;
     { static const u32 wm = getenv("BIBFS_WIDE_MIN") ? (u32)atoi(getenv("BIBFS_WIDE_MIN")) : 512u; K.wide_min = wm; }
     K.async_peers = c->async_peers ? 1u : 0u;
     // records + visited words of a small graph are streamed into L2 by the idle CTAs at query start (<= 24 MB: a fifth of L2)

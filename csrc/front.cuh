@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
         if (fs.ps.out.go_wide && tid == 0) {
             Ctrl::Wide& W = C->wide;
             for (u32 z = 0; z < 3; ++z) { W.cnt[z][0] = 0; W.cnt[z][1] = 0; W.flag[z] = 0; W.meet[z] = NO_V; W.tr_edges[z][0] = 0; W.tr_edges[z][1] = 0; }
-            W.meet_old[0] = NO_V; W.meet_old[1] = NO_V; W.edges = 0;
+            W.meet_old[0] = NO_V; W.meet_old[1] = NO_V; W.edges = 0; W.long_packed[0] = 0; W.long_packed[1] = 0; W.long_packed[2] = 0;
         }
         if (tid < 16u * (cl_n - 1u)) {
             const u32 c = 1u + tid / 16u, i = tid % 16u;

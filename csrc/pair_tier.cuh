@@ -154,6 +154,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, PairSmemT<PT_CAP>
     i32 length = -2;                 // -2: still searching
     u32 meet = NO_V, depth_s = 0, depth_t = 0;
     u32 visited = 0, go_wide = 0;
+    if (leave && allow_wide) go_wide = 1;          // a seed with a long row: straight to the cluster
 
     while (!leave) {
         // ---- which sides expand: both, unless one frontier dwarfs the other (then the smaller, ties -> source, like v1)
@@ -309,7 +310,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, PairSmemT<PT_CAP>
             break;
         }
         if (n0 == 0 || n1 == 0) { length = -1; depth_s = d0; depth_t = d1; break; }      // a side is exhausted: no path
-        if (allow_wide && (f & PT_OVF) && !(f & PT_BIG)) { go_wide = 1; break; }     // the log holds what the mirror dropped
+        if (allow_wide && (f & (PT_OVF | PT_BIG))) { go_wide = 1; break; }     // the cluster takes long rows and large frontiers (the log holds what the mirror dropped)
         if (f & (PT_BIG | PT_OVF)) break;
     }
     // ---- leave the tier: totals, then either the verdict or the hand-over to the general machinery
@@ -369,8 +370,9 @@ __device__ __noinline__ void pair_finish(const KParams& K, const Env& E, LevelSt
 //   * cursors, flags and the meeting vertex live in Ctrl::wide (L2 atomics, one reservation per
 //     warp), the round ends at barrier.cluster, and every thread of every CTA derives the next
 //     round from those counters, exactly as in the narrow round;
-//   * rows of >= PT_MAXDEG entries — their length is only known when their record is read — are
-//     walked by their whole warp; the round after that the tier hands over (PT_BIG).
+//   * rows of >= PT_MAXDEG entries (hubs of power-law graphs) are cut into 256-entry chunks that ALL warps of the
+//     cluster take in a second phase of the round, behind one more cluster barrier; graphs without such rows
+//     (KParams::long_rows, from the records' degree maximum) skip that barrier.
 // All CTAs call this together (the leader after pair_run, the others from the start-up barrier);
 // `o` is each CTA's own copy of the state and is updated in place.  Returns the adjacency entries
 // inspected by the whole cluster (valid in the leader CTA).
@@ -405,105 +407,157 @@ __device__ __noinline__ u64 pair_wide(const KParams& K, Env E, const PairIO io, 
     u32 meet = NO_V, depth_s = 0, depth_t = 0;
     const u32 gthreads = cl_n * BFS_THREADS, gt0 = cl_rank * BFS_THREADS + tid;
 
+    const bool long_rows = K.long_rows != 0;
+    HubEntry* const H = hub_of(K, E.me);
+    const u32 gwarp = gt0 >> 5, gwarps = gthreads >> 5;
+
     while (true) {
         const u32 mx = max(n0, n1), mn = min(n0, n1);
         if (mn > PT_WIDE_CAP) break;
         const u32 pad0 = (n0 + 31u) & ~31u;
-        const bool both = (mx <= 4u * mn || mx <= 32u) && mx <= PT_WIDE_CAP;
+        // both sides while they are of comparable size AND fit one pass of the cluster; beyond that only the smaller one
+        // (v1's policy: fewer entries to inspect), and such a round may stop as soon as any claim has hit the other side:
+        // with one side expanding every hit of the round gives the same length (what v1's `break` does, main-v1.cpp:61)
+        // (graphs with long rows: always one side - a hub row multiplies the work of a round by 10^5, and only a
+        //  single-side round may stop early)
+        const bool both = !long_rows && (mx <= 4u * mn || mx <= 32u) && ((n0 + 31u) & ~31u) + n1 <= gthreads;
         const bool e0 = both || n0 <= n1, e1 = both || n1 < n0;
+        auto hit_seen = [&]() -> bool {
+            u32 f = 0;
+            if (lane == 0) f = ptx::ld_relaxed_gpu(&W.flag[par]);
+            return (__shfl_sync(FULL, f, 0) & PT_HIT) != 0;
+        };
         const u32 off1 = e0 ? pad0 : 0u;
         const u32 span = off1 + (e1 ? n1 : 0u);
         const u32 flo0 = base0 - n0, flo1 = base1 - n1;          // the frontiers are the last n entries of the logs
         u32 fl = 0;
+        // claims of one batch of W candidates of parent `pu` (side `sd`); discoveries go to the CTA's stage
+        auto batch = [&](auto Wc, const u32* v, const u32 nact, const u32 pu, const u32 sd) {
+            constexpr int Wn = decltype(Wc)::value;
+            const u32 sh = 32u * sd, osh = 32u - sh;
+            u64 old[Wn];
+#pragma unroll
+            for (int k = 0; k < Wn; ++k) {
+                const bool act = (u32)k < nact;
+                old[k] = ptx::atom_or_gpu_if(act, &g_vis[(act ? v[k] : pu) >> 5], 1ull << ((v[k] & 31u) + sh));
+            }
+            const u32 shz = sh + ptx::zero_after(old[Wn - 1]);
+            u32 newmask = 0, meetmask = 0;
+#pragma unroll
+            for (int k = 0; k < Wn; ++k) {
+                const u32 isnew = (u32)k < nact ? (((u32)(old[k] >> ((v[k] & 31u) + shz)) & 1u) ^ 1u) : 0u;
+                newmask |= isnew << k;
+                meetmask |= (isnew & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
+            }
+            u32 slot = warp_reserve((u32)__popc(newmask), [&](u32 n) { return ptx::atoms_add(&s_cnt[sd], n); });
+            if (newmask) {
+                u64* const stg = stage + (size_t)sd * stage_cap;
+#pragma unroll
+                for (int k = 0; k < Wn; ++k) {
+                    if ((newmask >> k) & 1u) {
+                        if (slot < stage_cap) stg[slot] = (u64)v[k] | ((u64)pu << 32);
+                        else {      // stage full: straight to the log
+                            (sd ? log1 : log0)[(sd ? base1 : base0) + atomicAdd(&W.cnt[par][sd], 1u)] = v[k];
+                            (sd ? par1 : par0)[v[k]] = pu;
+                        }
+                        ++slot;
+                    }
+                }
+                if (meetmask) {
+#pragma unroll
+                    for (int k = 0; k < Wn; ++k)
+                        if ((meetmask >> k) & 1u) atomicMin(&W.meet[par], v[k]);
+                    if (!(fl & PT_HIT)) atomicOr(&W.flag[par], PT_HIT);      // at once: single-side rounds stop on it
+                    fl |= PT_HIT;
+                }
+            }
+        };
+        // ---- phase 1: every frontier position; rows shorter than PT_MAXDEG are walked by their lane, longer ones are
+        // cut into chunks for the whole cluster (phase 2)
         for (u32 vt = gt0; (vt & ~31u) < span; vt += gthreads) {
+            if (!both && vt >= gthreads && hit_seen()) break;
             const u32 side = (e0 && (!e1 || vt < off1)) ? 0u : 1u;      // warp-uniform
             const u32 idx = side ? vt - off1 : vt;
             const bool have = side ? (e1 && vt >= off1 && idx < n1) : (e0 && vt < n0);
-            const u32 sh = 32u * side, osh = 32u - sh;
-            const u32 base = side ? base1 : base0;
-            u32* const qs = side ? log1 : log0;
-            u32* const pp = side ? par1 : par0;
-            u32* const cursor = &W.cnt[par][side];
-            u64* const stg = stage + (size_t)side * stage_cap;
             u32 u = 0;
-            if (have) u = ptx::ld_relaxed_gpu(qs + (side ? flo1 : flo0) + idx);
+            if (have) u = ptx::ld_relaxed_gpu((side ? log1 + flo1 : log0 + flo0) + idx);
             const uint4* rp = rec_of(u);
             const uint4 ra = ptx::ld_v4_gpu_if(have, rp), rb = ptx::ld_v4_gpu_if(have, rp + 1);
             const u32 deg = ra.x, r0 = ra.y;
             my_edges += deg;
             if (tracing && deg) atomicAdd(&W.tr_edges[par][side], deg);
+            if (!__any_sync(FULL, have)) continue;
             const u32* const g_col = MULTI ? s_colb[owner(u)] : e_col;
-            // claims of one batch of W candidates of parent `pu`; reservation per warp on the global cursor
-            auto batch = [&](auto Wc, const u32* v, const u32 nact, const u32 pu) {
-                constexpr int Wn = decltype(Wc)::value;
-                u64 old[Wn];
-#pragma unroll
-                for (int k = 0; k < Wn; ++k) {
-                    const bool act = (u32)k < nact;
-                    old[k] = ptx::atom_or_gpu_if(act, &g_vis[(act ? v[k] : u) >> 5], 1ull << ((v[k] & 31u) + sh));
+            bool lng = deg >= PT_MAXDEG;
+            if (lng) {
+                const u32 nch = hub_nchunks(r0, (u64)r0 + deg);
+                const unsigned long long inc = (1ull << 40) | (unsigned long long)nch;
+                const unsigned long long was = atomicAdd(&W.long_packed[par], inc);
+                const u32 hs = (u32)(was >> 40);
+                if (hs < HUB_CAP) {
+                    HubEntry h;
+                    h.u = u; h.nchunks = nch | (side << 31); h.r0 = r0; h.r1 = (u64)r0 + deg; h.chunk_base = was & 0xFFFFFFFFFFull;
+                    H[hs] = h;
+                    lng = false;
+                } else {
+                    atomicAdd(&W.long_packed[par], 0ull - inc);       // list full: the warp walks the row below
                 }
-                const u32 shz = sh + ptx::zero_after(old[Wn - 1]);
-                u32 newmask = 0, meetmask = 0;
+            }
+            const u32 sdeg = deg < PT_MAXDEG ? deg : 0u;
+            {
+                const u32 c[PT_NB] = {ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
+                batch(std::integral_constant<int, PT_NB>{}, c, min(sdeg, (u32)PT_NB), u, side);
+            }
+            for (u32 e = PT_NB; __any_sync(FULL, e < sdeg); e += PT_W) {
+                u32 c[PT_W];
+                const u32 left = sdeg > e ? sdeg - e : 0u;
 #pragma unroll
-                for (int k = 0; k < Wn; ++k) {
-                    const u32 isnew = (u32)k < nact ? (((u32)(old[k] >> ((v[k] & 31u) + shz)) & 1u) ^ 1u) : 0u;
-                    newmask |= isnew << k;
-                    meetmask |= (isnew & (u32)(old[k] >> ((v[k] & 31u) + osh))) << k;
-                }
-                u32 slot = warp_reserve((u32)__popc(newmask), [&](u32 n) { return ptx::atoms_add(&s_cnt[side], n); });
-                if (newmask) {
-#pragma unroll
-                    for (int k = 0; k < Wn; ++k) {
-                        if ((newmask >> k) & 1u) {
-                            if (slot < stage_cap) stg[slot] = (u64)v[k] | ((u64)pu << 32);
-                            else { qs[base + atomicAdd(cursor, 1u)] = v[k]; pp[v[k]] = pu; }      // stage full: straight to the log
-                            ++slot;
-                        }
-                    }
-                    if (meetmask) {
-                        fl |= PT_HIT;
-#pragma unroll
-                        for (int k = 0; k < Wn; ++k)
-                            if ((meetmask >> k) & 1u) atomicMin(&W.meet[par], v[k]);
-                    }
-                }
-            };
-            if (__any_sync(FULL, have)) {
-                const u32 sdeg = deg < PT_MAXDEG ? deg : 0u;       // rows a lane walks alone
-                {
-                    const u32 c[PT_NB] = {ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
-                    batch(std::integral_constant<int, PT_NB>{}, c, min(sdeg, (u32)PT_NB), u);
-                }
-                for (u32 e = PT_NB; __any_sync(FULL, e < sdeg); e += PT_W) {
+                for (int k = 0; k < PT_W; ++k) c[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((u32)k < left ? e + k : 0u));
+                batch(std::integral_constant<int, PT_W>{}, c, min(left, (u32)PT_W), u, side);
+            }
+            u32 big = __ballot_sync(FULL, lng);          // (only when the chunk list overflowed)
+            while (big) {
+                const u32 sl = __ffs(big) - 1;
+                big &= big - 1;
+                const u32 uu = __shfl_sync(FULL, u, sl), rr = __shfl_sync(FULL, r0, sl), dd = __shfl_sync(FULL, deg, sl);
+                const u32* const cc = (MULTI ? s_colb[owner(uu)] : e_col) + rr;
+                for (u32 e = 0; e < dd; e += 32u * PT_W) {
                     u32 c[PT_W];
-                    const u32 left = sdeg > e ? sdeg - e : 0u;
+                    u32 nact = 0;
 #pragma unroll
-                    for (int k = 0; k < PT_W; ++k) c[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((u32)k < left ? e + k : 0u));
-                    batch(std::integral_constant<int, PT_W>{}, c, min(left, (u32)PT_W), u);
-                }
-                // long rows: the whole warp walks one row at a time, 4 x 32 entries per step
-                u32 big = __ballot_sync(FULL, deg >= PT_MAXDEG);
-                if (big) fl |= PT_BIG;
-                while (big) {
-                    const u32 sl = __ffs(big) - 1;
-                    big &= big - 1;
-                    const u32 uu = __shfl_sync(FULL, u, sl), rr = __shfl_sync(FULL, r0, sl), dd = __shfl_sync(FULL, deg, sl);
-                    const u32* const cc = (MULTI ? s_colb[owner(uu)] : e_col) + rr;
-                    for (u32 e = 0; e < dd; e += 32u * PT_W) {
-                        u32 c[PT_W];
-                        u32 nact = 0;
-#pragma unroll
-                        for (int k = 0; k < PT_W; ++k) {
-                            const u32 i = e + 32u * k + lane;
-                            c[k] = ptx::ld_relaxed_gpu(cc + (i < dd ? i : 0u));
-                            nact += i < dd ? 1u : 0u;          // (entries of a lane are consecutive in k: i grows with k)
-                        }
-                        batch(std::integral_constant<int, PT_W>{}, c, nact, uu);
+                    for (int k = 0; k < PT_W; ++k) {
+                        const u32 i = e + 32u * k + lane;
+                        c[k] = ptx::ld_relaxed_gpu(cc + (i < dd ? i : 0u));
+                        nact += i < dd ? 1u : 0u;
                     }
+                    batch(std::integral_constant<int, PT_W>{}, c, nact, uu, side);
                 }
             }
         }
-        if (fl) atomicOr(&W.flag[par], fl);
+        // ---- phase 2 (graphs with long rows): the chunks of the long rows, dealt over all warps of the cluster
+        if (long_rows) {
+            ptx::cluster_sync_all();
+            const u64 hp = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&W.long_packed[par]));
+            const u32 ne = min((u32)(hp >> 40), HUB_CAP), nchunks = (u32)(hp & 0xFFFFFFFFFFull);
+            for (u32 c = gwarp; c < nchunks; c += gwarps) {
+                if (!both && hit_seen()) break;
+                const HubChunk h = hub_lookup(H, ne, (const u32*)nullptr, c);
+                const u32 sd = h.nch_word >> 31;
+                const u32* const cc = (MULTI ? s_colb[owner(h.uu)] : e_col) + h.A;
+                for (u32 e = h.lo; e < h.hi; e += 32u * PT_W) {
+                    u32 cv[PT_W];
+                    u32 nact = 0;
+#pragma unroll
+                    for (int k = 0; k < PT_W; ++k) {
+                        const u32 i = e + 32u * k + lane;
+                        cv[k] = ptx::ld_relaxed_gpu(cc + (i < h.hi ? i : h.lo));
+                        nact += i < h.hi ? 1u : 0u;
+                    }
+                    batch(std::integral_constant<int, PT_W>{}, cv, nact, h.uu, sd);
+                }
+            }
+        }
+        if (fl & ~PT_HIT) atomicOr(&W.flag[par], fl & ~PT_HIT);
         // ---- flush the CTA's stage: one reservation per side
         __syncthreads();
         if (tid < 2) { const u32 c = min(s_cnt[tid], stage_cap); s_gbase[tid] = c ? atomicAdd(&W.cnt[par][tid], c) : 0u; }
@@ -534,6 +588,7 @@ __device__ __noinline__ u64 pair_wide(const KParams& K, Env E, const PairIO io, 
                 if (e1) trace_level(K, E, 1, PH_TD_SOLO | 16u | 32u, n1, c1, W.tr_edges[par][1], now);
             }
             W.cnt[z][0] = 0; W.cnt[z][1] = 0; W.flag[z] = 0; W.meet[z] = NO_V; W.tr_edges[z][0] = 0; W.tr_edges[z][1] = 0;
+            W.long_packed[z] = 0;
         }
         const u32 p0 = n0, p1 = n1;
         if (e0) { d0 += 1; levels += 1; base0 += c0; n0 = c0; visited += c0; }
@@ -561,7 +616,6 @@ __device__ __noinline__ u64 pair_wide(const KParams& K, Env E, const PairIO io, 
             break;
         }
         if (n0 == 0 || n1 == 0) { length = -1; depth_s = d0; depth_t = d1; break; }
-        if (f & PT_BIG) break;
     }
     // ---- totals; every CTA leaves with the same state
     {

@@ -11,7 +11,9 @@
 
 namespace bibfs {
 
-__global__ void __launch_bounds__(256) k_vrec_build(const u64* __restrict__ row_ptr, const u32* __restrict__ col, u32 rows, uint4* __restrict__ out) {
+__global__ void __launch_bounds__(256) k_vrec_build(const u64* __restrict__ row_ptr, const u32* __restrict__ col, u32 rows, uint4* __restrict__ out,
+                                                     u32* __restrict__ max_deg) {
+    u32 mx = 0;
     for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += gridDim.x * blockDim.x) {
         const u64 r0 = row_ptr[i], r1 = row_ptr[i + 1];
         const u64 d64 = r1 - r0;
@@ -21,6 +23,11 @@ __global__ void __launch_bounds__(256) k_vrec_build(const u64* __restrict__ row_
         for (int k = 0; k < 6; ++k) nb[k] = (u32)k < deg ? col[r0 + k] : 0u;
         out[2 * (size_t)i] = make_uint4(deg, (u32)r0, nb[0], nb[1]);
         out[2 * (size_t)i + 1] = make_uint4(nb[2], nb[3], nb[4], nb[5]);
+        mx = deg > mx ? deg : mx;
+    }
+    if (max_deg) {
+        mx = __reduce_max_sync(0xffffffffu, mx);
+        if ((threadIdx.x & 31) == 0 && mx) atomicMax(max_deg, mx);
     }
 }
 
@@ -31,13 +38,13 @@ using namespace bibfs;
 extern "C" size_t bibfs_vrec_bytes(uint32_t rows) { return (size_t)rows * 32; }
 
 extern "C" int bibfs_vrec_build_device(const uint64_t* d_row_ptr, const uint32_t* d_col, uint32_t rows, uint64_t nnz,
-                                       void* d_vrec, void* stream) {
+                                       void* d_vrec, uint32_t* d_max_degree, void* stream) {
     if (!d_row_ptr || !d_vrec) return fail("NULL argument");
     if (nnz >= (1ull << 32)) return fail("vertex records need < 2^32 stored entries per shard (have %llu)", (unsigned long long)nnz);
     if (reinterpret_cast<uintptr_t>(d_vrec) & 31u) return fail("d_vrec must be 32-byte aligned");
     if (rows == 0) return 0;
     const u32 blocks = (rows + 255u) / 256u;
-    k_vrec_build<<<blocks < 4096u ? blocks : 4096u, 256, 0, (cudaStream_t)stream>>>(d_row_ptr, d_col, rows, (uint4*)d_vrec);
+    k_vrec_build<<<blocks < 4096u ? blocks : 4096u, 256, 0, (cudaStream_t)stream>>>(d_row_ptr, d_col, rows, (uint4*)d_vrec, d_max_degree);
     BIBFS_KERNEL_CHECK();
     return 0;
 }

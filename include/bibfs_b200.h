@@ -186,6 +186,7 @@ typedef struct {
     uint32_t bottom_up_div;     /* go bottom-up when frontier > n/div (0 -> default, ~0u never) */
     uint32_t max_ctas;          /* cap on CTAs per rank (0 -> all SMs)                     */
     uint32_t watchdog_ms;       /* spin-loop timeout (0 -> default 4000)                   */
+    uint32_t max_degree;        /* longest row of the whole graph, 0 = unknown                */
     const void* d_vrec[BIBFS_MAX_RANKS];        /* per hosted rank: vertex records (bibfs_vrec_build_device) or NULL.
                                                    With records, small searches run on the pair tier: both directions
                                                    per round, one memory round trip per round                            */
@@ -195,10 +196,12 @@ uint32_t bibfs_block_size(uint32_t n, uint32_t nranks);
 
 /* Vertex records of a CSR shard: 32 bytes per row = {degree, row start (32 bits), first six neighbours}.
  * d_vrec: bibfs_vrec_bytes(rows) bytes, 32-byte aligned; nnz = stored entries of the shard (< 2^32).
+ * bibfs_ctx_desc::max_degree (largest row of the WHOLE graph, 0 = unknown) lets the search skip the handling of long
+ * rows on graphs that have none.
  * No counterpart in the reference. */
 size_t bibfs_vrec_bytes(uint32_t rows);
 int bibfs_vrec_build_device(const uint64_t* d_row_ptr, const uint32_t* d_col, uint32_t rows, uint64_t nnz,
-                            void* d_vrec, void* stream);
+                            void* d_vrec, uint32_t* d_max_degree /* device word, atomicMax'ed; may be NULL */, void* stream);
 
 int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc);
 int bibfs_ctx_destroy(bibfs_ctx* ctx);
