@@ -86,6 +86,9 @@ class SearchContext:
         with torch.cuda.device(self.device):
             check(lib().bibfs_ctx_create(C.byref(self._h), C.byref(d)))
         self._path = np.empty(self.max_path, dtype=np.uint32)
+        self._desc = d
+        # col / vertex-record pointers of every rank as mapped on this device (hosted shards now, peers when attached)
+        self.graph_ptrs = {rank_lo + i: (d.d_col[i], d.d_vrec[i]) for i in range(self.vranks) if d.d_vrec[i]}
         # per-query constants of the hot call (each of these lookups costs 0.3-1 us in CPython)
         self._path_ptr = self._path.ctypes.data
         self._fn_query_result = lib().bibfs_ctx_query_result
@@ -135,6 +138,7 @@ class SearchContext:
             col, vrec = self._import(shared)
             if col.value and vrec.value:
                 check(lib().bibfs_ctx_set_peer_graph(self._h, rank, col, vrec))
+                self.graph_ptrs[rank] = (col.value, vrec.value)
 
     def replicate_records(self, shared_by_rank: list) -> bool:
         """Keep a LOCAL, contiguous copy of every shard's vertex records (32 bytes per vertex: the index the front kernel
@@ -161,6 +165,7 @@ class SearchContext:
             self._record_replica = full
             for r in range(P):
                 check(lib().bibfs_ctx_set_peer_graph(self._h, r, C.c_void_p(cols[r]), C.c_void_p(full.data_ptr() + r * B * 32)))
+                self.graph_ptrs[r] = (cols[r], full.data_ptr() + r * B * 32)
         return True
 
     def resume(self) -> None:

@@ -95,12 +95,53 @@ class DistributedSolver:
         return self.ctx.query(src, dst, flags, want_path, pinned_query, self.variant)
 
     def query_many(self, srcs, dsts, want_path=False) -> list[PathResult]:
-        """A batch of queries on the partitioned graph, one fused launch per query and rank, back to back on the stream
-        (BASELINE config 5: 64 queries on a graph that only fits the 8 GPUs together; 0.12 ms per query on Kronecker
-        scale 26).  Every rank must pass the same lists.  For graphs that fit one GPU, `bibfs_batch` is the faster tool."""
+        """A batch of queries on the partitioned graph, one after the other (every rank passes the same lists)."""
         return [self.query(int(s), int(t), want_path=want_path) for s, t in zip(srcs, dsts)]
+
+    def query_batch(self, srcs, dsts, lanes: int = 32) -> list[int | None]:
+        """Lengths of a batch of queries (BASELINE config 5: 64 random queries on a graph that is partitioned over the
+        GPUs).  Rank 0 runs a pool of `lanes` front kernels side by side — each one rank 0 working ALONE on the whole
+        partitioned graph through the peer mappings (pair tier, wide rounds, long rows over its cluster), so the searches
+        overlap their latency chains instead of queueing behind one another; the few searches a lane cannot finish
+        (frontier beyond 65536 per side) are then answered by the whole group, one at a time.  The reference answers one
+        query per process (benchmark_test.sh:47-54).  Every rank calls this with the same lists; `last_batch_ms` holds
+        the device time of the pooled part on rank 0."""
+        import ctypes as C
+        import numpy as np
+        from .._lib import check, lib
+        srcs = np.ascontiguousarray(np.asarray(srcs, dtype=np.uint32))
+        dsts = np.ascontiguousarray(np.asarray(dsts, dtype=np.uint32))
+        nq = int(srcs.size)
+        lens = np.full(nq, -2, dtype=np.int32)
+        self.last_batch_ms = 0.0
+        if self.rank == 0 and len(self.ctx.graph_ptrs) == self.world:
+            with torch.cuda.device(self.graph.device):
+                if getattr(self, "_pool", None) is None:
+                    free, _ = torch.cuda.mem_get_info(self.graph.device)
+                    per_lane = self.ctx.arena_bytes + (1 << 22)
+                    self._lanes = max(1, min(lanes, int(free * 0.5 // per_lane)))
+                    self._pool = C.c_void_p()
+                    check(lib().bibfs_pool_create(C.byref(self._pool), C.byref(self.ctx._desc), self._lanes, 1))
+                    for r, (col, vrec) in self.ctx.graph_ptrs.items():
+                        check(lib().bibfs_pool_set_peer_graph(self._pool, r, C.c_void_p(col), C.c_void_p(vrec)))
+                ms = C.c_float(0)
+                check(lib().bibfs_pool_query(self._pool, srcs.ctypes.data, dsts.ctypes.data, nq, lens.ctypes.data, None, None, None, C.byref(ms)))
+                self.last_batch_ms = float(ms.value)
+        box = [lens.tolist()]
+        dist.broadcast_object_list(box, src=0)
+        out = []
+        for i, L in enumerate(box[0]):
+            if L == -2:                      # not answered by the pool: the whole group takes it
+                out.append(self.query(int(srcs[i]), int(dsts[i]), want_path=False).length)
+            else:
+                out.append(None if L < 0 else int(L))
+        return out
 
     def close(self):
         torch.cuda.synchronize(self.graph.device)
         dist.barrier()
+        if getattr(self, "_pool", None) is not None:
+            from .._lib import lib
+            lib().bibfs_pool_destroy(self._pool)
+            self._pool = None
         self.ctx.close()

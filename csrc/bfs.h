@@ -188,6 +188,8 @@ struct KParams {
     u32 src, dst, query_in_ctrl;   // query by value, or (query_in_ctrl) read from Ctrl::q_src/q_dst
     u32 resume;                    // k_bibfs continues a search the front kernel handed over (no query start)
     u32 async_peers;               // the other ranks are driven by other processes: arrival words order the queries
+    u32 lone;                      // front kernel of a query-pool lane: rank 0 works without its peers (no verdicts, no hand-over;
+                                   // a search it cannot finish is reported back as handed over and answered by the group)
     u32 long_rows;                 // the graph has rows of >= 32 entries (or nobody knows): wide rounds deal them over the cluster
     u32 wide_min;                  // front kernel: frontier positions of a round from which its whole cluster takes the round
     u64 qn;                        // number of this query in the context group (host counter, identical on every rank)

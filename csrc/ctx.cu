@@ -33,6 +33,7 @@ struct bibfs_ctx {
     const void* vrec_all[MAXR] = {};
     bool hosts0 = false;         // this context hosts rank 0 (runs the front kernel, walks the path, delivers the result)
     bool hosts_all = false;      // ... and every other rank too (single rank, or virtual ranks)
+    bool lone = false;           // lane of a query pool on a partitioned graph: rank 0 without its peers (front kernel only)
     bool async_peers = false;    // peers live in other processes (attached through IPC): each rank resumes on its own verdict
     u32 front_cluster = 1;       // thread-block cluster of the front kernel (wide rounds)
     // the cluster launch costs ~1.5 us more than a single CTA: contexts whose queries never go wide drop it, and take it
@@ -68,7 +69,7 @@ struct DeviceGuard {
 size_t zero_prefix(const Layout& L) { return L.off_parent; }   // Ctrl + vis + fbm
 }  // namespace
 
-extern "C" size_t bibfs_ctx_arena_bytes(const bibfs_ctx* ctx) { return ctx ? ctx->L.total : 0; }
+extern "C" size_t bibfs_ctx_arena_bytes(const bibfs_ctx* ctx) { return ctx ? (ctx->hosts0 ? ctx->L.total0 : ctx->L.total) : 0; }
 
 extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     if (!out || !desc) return fail("NULL argument");
@@ -257,6 +258,7 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     K.long_rows = (c->d.max_degree == 0 || c->d.max_degree >= 32) ? 1u : 0u;
     { static const u32 wm = getenv("BIBFS_WIDE_MIN") ? (u32)atoi(getenv("BIBFS_WIDE_MIN")) : 512u; K.wide_min = wm; }
     K.async_peers = c->async_peers ? 1u : 0u;
+    K.lone = c->lone ? 1u : 0u;
     // records + visited words of a small graph are streamed into L2 by the idle CTAs at query start (<= 24 MB: a fifth of L2)
     if (c->vrec_all[0] && c->hosts0) {
         // how many of the records are local and contiguous behind rank 0's (its own shard; every shard with a record replica)
@@ -502,6 +504,8 @@ extern "C" int bibfs_ctx_trace(bibfs_ctx* c, uint32_t i, bibfs_level_trace* out,
 // heavy and overlap.)  No counterpart in the reference (one query per process).
 // ------------------------------------------------------------------------------------------
 struct bibfs_pool {
+    u32 lane_cluster = 1;        // cluster size of a lane's front kernel
+    bool multi = false;
     std::vector<bibfs_ctx*> ctx;
     std::vector<cudaStream_t> st;
     std::vector<cudaEvent_t> done;
@@ -527,7 +531,7 @@ extern "C" int bibfs_pool_destroy(bibfs_pool* p) {
 
 extern "C" int bibfs_pool_create(bibfs_pool** out, const bibfs_ctx_desc* desc, uint32_t lanes, uint32_t ctas_per_lane) {
     if (!out || !desc) return fail("NULL argument");
-    if (desc->nranks != 1 || desc->vranks != 1) return fail("the query pool works on an unpartitioned graph (nranks = 1)");
+    if (desc->vranks != 1 || desc->rank_lo != 0) return fail("a query pool is created on the context that hosts rank 0 (vranks = 1)");
     if (lanes < 1 || lanes > 1024) return fail("lanes must be 1..1024");
     bibfs_pool* p = new bibfs_pool();
     cudaGetDevice(&p->device);
@@ -537,6 +541,7 @@ extern "C" int bibfs_pool_create(bibfs_pool** out, const bibfs_ctx_desc* desc, u
     for (uint32_t i = 0; i < lanes; ++i) {
         bibfs_ctx* c = nullptr;
         if (bibfs_ctx_create(&c, &d)) { std::string why = bibfs_last_error(); bibfs_pool_destroy(p); return fail("lane %u: %s", i, why.c_str()); }
+        c->lone = desc->nranks > 1;
         p->ctx.push_back(c);
         cudaStream_t s;
         cudaEvent_t e;
@@ -549,7 +554,18 @@ extern "C" int bibfs_pool_create(bibfs_pool** out, const bibfs_ctx_desc* desc, u
     }
     cudaEventCreate(&p->ev0);
     cudaEventCreate(&p->ev1);
+    p->multi = desc->nranks > 1;
+    // lanes run their front kernels side by side: small clusters (4 CTAs: long rows and wide rounds still work)
+    p->lane_cluster = p->ctx[0]->front_cluster >= 4 ? 4u : p->ctx[0]->front_cluster;
+    if (const char* e = getenv("BIBFS_POOL_CLUSTER")) { const u32 v = (u32)atoi(e); if (v >= 1 && v <= p->ctx[0]->front_cluster && !(v & (v - 1))) p->lane_cluster = v; }
     *out = p;
+    return 0;
+}
+
+extern "C" int bibfs_pool_set_peer_graph(bibfs_pool* p, uint32_t rank, const uint32_t* d_col, const void* d_vrec) {
+    if (!p) return fail("NULL pool");
+    for (auto c : p->ctx)
+        if (bibfs_ctx_set_peer_graph(c, rank, d_col, d_vrec)) return 1;
     return 0;
 }
 
@@ -566,15 +582,28 @@ extern "C" int bibfs_pool_query(bibfs_pool* p, const uint32_t* h_src, const uint
         p->h_cap = cap;
     }
     const size_t L = p->ctx.size();
+    // with vertex records for every rank a lane runs the FRONT kernel (pair tier, wide rounds, long rows) as a small
+    // cluster and delivers its 64-byte result straight into the pinned array; without them (or when the front kernel
+    // cannot finish a search) the general kernel of a single-rank lane answers
+    bool front = true;
+    for (u32 r = 0; r < p->ctx[0]->d.nranks; ++r) front = front && p->ctx[0]->vrec_all[r] && p->ctx[0]->col_all[r];
+    if (p->multi && !front) return fail("a pool on a partitioned graph needs every rank's vertex records (bibfs_pool_set_peer_graph)");
     BIBFS_CUDA_TRY(cudaEventRecord(p->ev0, p->st[0]));
     for (size_t i = 1; i < L; ++i) BIBFS_CUDA_TRY(cudaStreamWaitEvent(p->st[i], p->ev0, 0));
     for (uint32_t q = 0; q < nq; ++q) {
         const size_t lane = q % L;
         bibfs_ctx* c = p->ctx[lane];
         KParams K;
+        c->qn += 1;
         fill_params(c, K, h_src[q], h_dst[q], false, BIBFS_F_NO_PATH);
-        if (bfs_launch(K, false, p->st[lane])) return 1;
-        BIBFS_CUDA_TRY(cudaMemcpyAsync(&p->h_res[q], c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, p->st[lane]));
+        if (front) {
+            K.lone = 1u; K.warm_lines = 0; K.async_peers = 0;
+            K.fuse_path = 1u; K.h_out = reinterpret_cast<u32*>(&p->h_res[q]); K.h_out_words = 0; K.h_seq = nullptr;
+            if (front_launch(K, p->multi, p->lane_cluster, p->st[lane])) return 1;
+        } else {
+            if (bfs_launch(K, false, p->st[lane])) return 1;
+            BIBFS_CUDA_TRY(cudaMemcpyAsync(&p->h_res[q], c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, p->st[lane]));
+        }
     }
     for (size_t i = 1; i < L; ++i) {
         BIBFS_CUDA_TRY(cudaEventRecord(p->done[i], p->st[i]));
@@ -585,9 +614,18 @@ extern "C" int bibfs_pool_query(bibfs_pool* p, const uint32_t* h_src, const uint
     if (ms) BIBFS_CUDA_TRY(cudaEventElapsedTime(ms, p->ev0, p->ev1));
     int bad = 0;
     for (uint32_t q = 0; q < nq; ++q) {
+        if (front && p->h_res[q].status == ST_ESCALATED && !p->multi) {
+            // a search beyond the front kernel (frontier > 65536 per side): the general kernel, one at a time
+            bibfs_ctx* c = p->ctx[0];
+            KParams K;
+            fill_params(c, K, h_src[q], h_dst[q], false, BIBFS_F_NO_PATH);
+            if (bfs_launch(K, false, p->st[0])) return 1;
+            BIBFS_CUDA_TRY(cudaMemcpyAsync(&p->h_res[q], c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, p->st[0]));
+            BIBFS_CUDA_TRY(cudaStreamSynchronize(p->st[0]));
+        }
         const Result& r = p->h_res[q];
         if (r.status == 1) bad = 1;
-        if (h_len) h_len[q] = r.status == 0 ? r.length : -1;
+        if (h_len) h_len[q] = r.status == 0 ? r.length : (r.status == ST_ESCALATED ? -2 : -1);      // -2: left to the caller (partitioned graph)
         if (h_meet) h_meet[q] = r.meet;
         if (h_levels) h_levels[q] = r.levels;
         if (h_edges) h_edges[q] = r.edges_scanned;

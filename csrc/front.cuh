@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
         }
         if (G.phase == PH_DONE) write_result(K, C, G);
     }
-    if (MULTI && K.async_peers && warp == 1) {
+    if (MULTI && K.async_peers && !K.lone && warp == 1) {
         // never more than one verdict ahead of a peer (the verdict slots alternate by query parity)
         if (!wait_arrivals(K, C, qn - 1, deadline) && lane == 0) fs.fail = 1;
     }
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
     }
     if (st.phase == PH_DONE) {
         // ---- the query ended here: verdict to the peers, path, result, cleanup
-        if (MULTI && warp == 0 && !fs.fail) send_verdict(K, st, VK_DONE, qn, nullptr);
+        if (MULTI && !K.lone && warp == 0 && !fs.fail) send_verdict(K, st, VK_DONE, qn, nullptr);
         KT_STAMP(5);
         if (K.fuse_path == 2u) path_body_local(K, io.par[0], io.par[1]);
         else if (K.fuse_path) result_to_host(K);
@@ -308,6 +308,21 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
         return;
     }
     // ---- the search goes on in the general kernel
+    if (K.lone) {
+        // pool lane: nobody to hand over to.  Undo the marks, report "handed over"; the caller answers the query elsewhere
+        const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
+        for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
+        for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+        if (tid == 0) {
+            Result& R = C->res;
+            R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
+            R.depth_s = st.depth[0]; R.depth_t = st.depth[1]; R.levels_bu = 0; R.levels_grid = 0;
+            R.edges_scanned = st.edges_total; R.vertices_visited = st.visited_total; R.search_ns = 0; R.path_ns = 0;
+        }
+        __syncthreads();
+        if (K.fuse_path) result_to_host(K);
+        return;
+    }
     if (MULTI) {
         if (K.async_peers && warp == 0 && !wait_arrivals(K, C, qn, deadline) && lane == 0) fs.fail = 1;
         __syncthreads();

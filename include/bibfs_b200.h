@@ -284,6 +284,11 @@ int bibfs_batch_query_device(uint32_t n, const uint64_t* d_row_ptr, const uint32
  * queries report length -1.  No counterpart in the reference. */
 typedef struct bibfs_pool bibfs_pool;
 int bibfs_pool_create(bibfs_pool** out, const bibfs_ctx_desc* desc, uint32_t lanes, uint32_t ctas_per_lane);
+/* Pool on a PARTITIONED graph (desc->nranks > 1, created in the process that hosts rank 0): every lane is rank 0's front
+ * kernel working alone through the peer mappings, so the lanes need the other ranks' col / vertex records as mapped on
+ * this device.  h_len[q] = -2 marks a query the lanes could not finish (frontier beyond 65536 vertices per side): answer
+ * it with bibfs_ctx_query on the group. */
+int bibfs_pool_set_peer_graph(bibfs_pool* pool, uint32_t rank, const uint32_t* d_col, const void* d_vrec);
 int bibfs_pool_query(bibfs_pool* pool, const uint32_t* h_src, const uint32_t* h_dst, uint32_t nq,
                      int32_t* h_len, uint32_t* h_meet, uint32_t* h_levels, uint64_t* h_edges, float* ms);
 int bibfs_pool_destroy(bibfs_pool* pool);

@@ -138,3 +138,40 @@ def test_watchdog_abort_and_reset(bb):
         assert r.length == oracle.query(s, t, want_path=False).length
         bb.validate_path(g_cpu, s, t, r.path, r.length)
     c0.close(); c1.close()
+
+
+def test_query_pool_on_a_partitioned_graph(bb):
+    """Lanes of front kernels on rank 0's device answering a batch on a graph partitioned over 4 ranks (the other shards
+    are reached through their pointers, here on the same device); what a lane cannot finish comes back as -2."""
+    import ctypes as C
+    from bidirectional_bfs_b200._lib import CtxDesc, check, lib
+    for spec in (bb.er_spec(60000, 2.5 / 60000, seed=9), bb.rmat_spec(15, edgefactor=16, seed=4), bb.grid_spec(300, 200)):
+        g_cpu = bb.Graph.generate(spec)
+        oracle = bb.SerialSolver(g_cpu, policy=1)
+        g = bb.Graph.generate(spec, device="cuda:0", nranks=4)
+        d = CtxDesc()
+        d.n, d.nranks, d.rank_lo, d.vranks = g.n, 4, 0, 1
+        s0 = g.shards[0]
+        d.d_row_ptr[0], d.d_col[0], d.d_vrec[0] = s0.row_ptr.data_ptr(), s0.col.data_ptr(), s0.vertex_records().data_ptr()
+        for r in range(4):
+            g.shards[r].vertex_records()
+        d.max_degree = max(g.shards[r].max_degree for r in range(4))
+        pool = C.c_void_p()
+        check(lib().bibfs_pool_create(C.byref(pool), C.byref(d), 8, 1))
+        for r in range(1, 4):
+            check(lib().bibfs_pool_set_peer_graph(pool, r, C.c_void_p(g.shards[r].col.data_ptr()), C.c_void_p(g.shards[r].vrec.data_ptr())))
+        pairs = query_pairs(spec.n, 64, 21)
+        src = np.array([p[0] for p in pairs], dtype=np.uint32)
+        dst = np.array([p[1] for p in pairs], dtype=np.uint32)
+        lens = np.empty(64, dtype=np.int32)
+        ms = C.c_float(0)
+        for _ in range(2):
+            check(lib().bibfs_pool_query(pool, src.ctypes.data, dst.ctypes.data, 64, lens.ctypes.data, None, None, None, C.byref(ms)))
+        answered = 0
+        for (s, t), L in zip(pairs, lens):
+            want = oracle.query(s, t, want_path=False).length
+            if L != -2:
+                assert (None if L < 0 else int(L)) == want, (s, t, L, want)
+                answered += 1
+        assert answered >= 60
+        check(lib().bibfs_pool_destroy(pool))
