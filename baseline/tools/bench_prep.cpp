@@ -12,7 +12,7 @@
 //     (v1/main-v1.cpp:50-81: smaller frontier first, ties to the source side, stop at the first
 //     meeting vertex in the middle of a level) — the common numerator of BASELINE.md §3.
 //
-//   bench_prep er:<n>:<p>:<seed> | rmat:<scale>:<edgefactor>:<n>:<seed> | grid:<w>:<h>  [--bin FILE] < pairs
+//   bench_prep er:<n>:<p>:<seed> | rmat:<scale>:<edgefactor>:<n>:<seed> | grid:<w>:<h>  [--bin FILE] [--need K] < pairs
 #include "../../csrc/gen.h"
 #include <algorithm>
 #include <cstdlib>
@@ -38,7 +38,11 @@ static std::vector<std::string> split(const std::string& s, char c) {
 int main(int argc, char** argv) {
     if (argc < 2) { fprintf(stderr, "usage: bench_prep <spec> [--bin FILE] < pairs\n"); return 2; }
     const char* bin_path = nullptr;
-    for (int i = 2; i + 1 < argc; ++i) if (!strcmp(argv[i], "--bin")) bin_path = argv[i + 1];
+    unsigned long long need = ~0ull;       // stop after this many usable pairs (connected, >= 2 hops; the first pair always counts)
+    for (int i = 2; i + 1 < argc; ++i) {
+        if (!strcmp(argv[i], "--bin")) bin_path = argv[i + 1];
+        if (!strcmp(argv[i], "--need")) need = strtoull(argv[i + 1], 0, 10);
+    }
     auto f = split(argv[1], ':');
     bibfs_gen_spec s;
     memset(&s, 0, sizeof(s));
@@ -114,8 +118,9 @@ int main(int argc, char** argv) {
     // pass 2: replay the v1 schedule for every pair on stdin
     std::vector<unsigned char> mark(n, 0);          // bit 0: reached from src, bit 1: reached from dst
     std::vector<u32> touched, fr[2], nx;
-    unsigned long long a, b;
-    while (scanf("%llu %llu", &a, &b) == 2) {
+    unsigned long long a, b, usable = 0, seen = 0;
+    while (usable < need && scanf("%llu %llu", &a, &b) == 2) {
+        ++seen;
         const u32 src = (u32)a, dst = (u32)b;
         long long length = -1;
         u64 edges = 0;
@@ -148,6 +153,7 @@ int main(int argc, char** argv) {
         if (met) length = (long long)depth[0] + depth[1];
         for (u32 v : touched) mark[v] = 0;
         printf("%u %u %lld %llu %u\n", src, dst, length, (unsigned long long)edges, levels);
+        if (length >= 2 || (seen == 1 && length >= 0)) ++usable;
     }
     return 0;
 }

@@ -119,7 +119,7 @@ def prepare(config: str, seed: int, need: int, bin_path: Path | None = None, hos
         except (OSError, ValueError, KeyError):
             pass
     cand = candidate_pairs(n, 50 * need + 100, seed)
-    cmd = [str(prep_tool()), spec] + (["--bin", str(bin_path)] if bin_path else [])
+    cmd = [str(prep_tool()), spec, "--need", str(need)] + (["--bin", str(bin_path)] if bin_path else [])
     out = subprocess.run(cmd, input="".join(f"{s} {t}\n" for s, t in cand), capture_output=True, text=True, check=True).stdout.splitlines()
     _, n_s, rec, nnz = out[0].split()
     picked = []
@@ -243,9 +243,8 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
             d2h += 64 + 4 * (length + 1)
         barrier()
         e2e_s = time.perf_counter() - e0
-        t_end = time.perf_counter() + 0.3     # keep the GPU in the same state long enough for nvidia-smi to sample it under load
-        while time.perf_counter() < t_end:
-            solver.query(queries[W][0], queries[W][1], want_path=False)
+        for _ in range(3000):                 # keep the GPU in the same state long enough for nvidia-smi to sample it under load
+            solver.query(queries[W][0], queries[W][1], want_path=False)      # (a fixed count: every rank must issue the same queries)
         if world > 1:
             te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
@@ -266,6 +265,72 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
         "wall_dev_loop": wall_dev_loop, "l2": "256 MB write between steps" if flush is not None else "inputs larger than L2",
         "levels_mean": float(np.mean([q[4] for q in queries[W:W + K]])),
     }
+
+
+def measure_batch(bb, comm, dist, torch, dev, rank, world, config, seed, nq=64):
+    """BASELINE.json config 5: a batch of `nq` random src/dst queries on `config` (kron26), answered by the query pool
+    (lanes of front kernels; on several GPUs rank 0's lanes over the partitioned graph + the group for what is left).
+    Wall clock of the whole batch, barrier + synchronize on both sides, max over ranks; answers checked against the
+    one-query-at-a-time path."""
+    spec = make_spec(bb, config[:-8] if config.endswith("_batch64") else config, seed)
+    n = int(spec.n)
+    t0 = time.time()
+    if world == 1:
+        g = bb.Graph.generate(spec, device=dev)
+        single = bb.GpuSolver(g)
+        pool = bb.BatchSolver(g, lanes=32)
+        run = lambda a, b: pool.query_batch(a, b)
+    else:
+        g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
+        single = comm.DistributedSolver(g)
+        run = lambda a, b: single.query_batch(a, b, lanes=32)
+    torch.cuda.synchronize()
+    build_s = time.time() - t0
+    rng = np.random.default_rng(seed + 64)
+    src = rng.integers(0, n, nq); dst = rng.integers(0, n, nq)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    run(src, dst)
+    times = []
+    for _ in range(3):
+        barrier()
+        t1 = time.perf_counter()
+        lens = run(src, dst)
+        barrier()
+        times.append(time.perf_counter() - t1)
+    t_batch = min(times)
+    pool_ms = pool.last_ms if world == 1 else getattr(single, "last_batch_ms", 0.0)
+    barrier()
+    t1 = time.perf_counter()
+    seq = [single.query(int(a), int(b), want_path=False).length for a, b in zip(src, dst)]
+    barrier()
+    t_seq = time.perf_counter() - t1
+    if lens != seq:
+        raise SystemExit(f"{config}: the pool and the one-at-a-time path disagree")
+    if world > 1:
+        tt = torch.tensor([t_batch, t_seq], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_batch, t_seq = float(tt[0].item()), float(tt[1].item())
+    nnz = g.nnz
+    if world > 1:
+        t = torch.tensor([nnz], dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        nnz = int(t.item())
+    if world == 1:
+        pool.close()
+    single.close()
+    del single, g
+    torch.cuda.empty_cache()
+    return {"model": f"{nq} random queries at once on {spec_string(config[:-8] if config.endswith('_batch64') else config, seed)[1]}",
+            "n": n, "directed_edges": nnz, "queries": nq, "found": sum(x is not None for x in lens),
+            "batch_ms_wall": t_batch * 1e3, "pool_ms_device": pool_ms, "one_at_a_time_ms_wall": t_seq * 1e3,
+            "queries_per_s": nq / t_batch, "graph_build_s": build_s,
+            "what": "wall clock of the whole batch through the public API (barrier + synchronize on both sides, max over ranks, best of 3); "
+                    "pool_ms_device = CUDA events around the pooled launches on rank 0"}
 
 
 def run_ours(args):
@@ -292,6 +357,15 @@ def run_ours(args):
     others = {}
     for cfg in [c for c in args.others.split(",") if c and c != args.config]:
         t0 = time.time()
+        if cfg.endswith("_batch64"):
+            try:
+                ob = measure_batch(bb, comm, dist, torch, dev, rank, world, cfg, args.seed)
+                if rank == 0:
+                    others[cfg] = ob
+            except Exception as e:  # noqa: BLE001
+                if rank == 0:
+                    others[cfg] = {"error": str(e)[:200]}
+            continue
         try:
             o = measure_ours(bb, comm, dist, torch, dev, rank, world, cfg, args.seed, args.other_steps, 3, do_e2e=False)
         except Exception as e:  # noqa: BLE001
