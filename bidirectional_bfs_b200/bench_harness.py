@@ -31,7 +31,7 @@ def boxed_table(rows: list[list[str]]) -> str:
     return "\n".join(out)
 
 
-def run(graph_paths, variants, repeats=5, ranks=4, outdir=".", device="cuda:0", log_dir=None):
+def run(graph_paths, variants, repeats=5, ranks=4, outdir=".", device="cuda:0", log_dir=None, gpus=0):
     import torch
     import bidirectional_bfs_b200 as bb
     rows = []
@@ -48,9 +48,8 @@ def run(graph_paths, variants, repeats=5, ranks=4, outdir=".", device="cuda:0", 
                 solver = bb.make_solver(g, variant, **({"ranks": ranks} if variant == "cpu-ranks" else {}))
                 ngpu = 0
             elif variant == "multi-gpu":
-                g = bb.Graph.from_edges(n, edges, device=device, nranks=ranks)
-                solver = bb.MultiGpuSolver(g)
-                ngpu = 1
+                from .models.solvers import multi_gpu_solver
+                solver, ngpu = multi_gpu_solver(n, edges, ranks, gpus, device)      # real devices with --gpus N, else virtual ranks
             else:
                 g = bb.Graph.from_edges(n, edges, device=device)
                 solver = bb.make_solver(g, variant)
@@ -89,6 +88,7 @@ def main(argv=None) -> int:
     ap.add_argument("--variants", nargs="*", default=["serial", "cpu-ranks", "gpu", "multi-gpu"])
     ap.add_argument("--repeats", type=int, default=5)
     ap.add_argument("--ranks", type=int, default=4)                                                  # NP=4, benchmark_test.sh:9
+    ap.add_argument("--gpus", type=int, default=0, help="multi-gpu variant: one rank per GPU on this many devices (default: --ranks virtual ranks on one GPU)")
     ap.add_argument("--out", default=".")
     ap.add_argument("--logs", default=None)
     a = ap.parse_args(argv)
@@ -97,7 +97,7 @@ def main(argv=None) -> int:
     if missing:
         from .cli import cmd_make_graphs
         cmd_make_graphs(["--dir", a.graphs_dir])
-    rows, table = run(paths, a.variants, a.repeats, a.ranks, a.out, log_dir=a.logs)
+    rows, table = run(paths, a.variants, a.repeats, a.ranks, a.out, log_dir=a.logs, gpus=a.gpus)
     print("\nBenchmark complete.\nCSV   ->", os.path.join(a.out, "benchmark_results.csv"))
     print("Table ->", os.path.join(a.out, "benchmark_table.txt"), "\n")
     print(table)

@@ -33,6 +33,7 @@ def cmd_query(argv) -> int:
     ap.add_argument("dst", type=int)
     ap.add_argument("--variant", default=None, choices=["serial", "cpu-ranks", "gpu", "multi-gpu", "naive-gpu"])
     ap.add_argument("--ranks", type=int, default=4, help="cpu-ranks: worker threads; multi-gpu: ranks (virtual ranks on one GPU unless launched with torchrun)")
+    ap.add_argument("--gpus", type=int, default=0, help="multi-gpu: one rank per GPU on this many devices (0/1: --ranks virtual ranks on --device)")
     ap.add_argument("--device", default="cuda:0")
     ap.add_argument("--quiet-path", action="store_true")
     ap.add_argument("--trace", action="store_true", help="print one line per BFS level (gpu variants)")
@@ -55,8 +56,8 @@ def cmd_query(argv) -> int:
         g = bb.Graph.from_edges(n, edges)
         solver = bb.make_solver(g, variant, **({"ranks": a.ranks} if variant == "cpu-ranks" else {}))
     elif variant == "multi-gpu":
-        g = bb.Graph.from_edges(n, edges, device=a.device, nranks=a.ranks)
-        solver = bb.MultiGpuSolver(g)
+        from .models.solvers import multi_gpu_solver
+        solver, _ = multi_gpu_solver(n, edges, a.ranks, a.gpus, a.device)
     else:
         g = bb.Graph.from_edges(n, edges, device=a.device)
         solver = bb.make_solver(g, variant)

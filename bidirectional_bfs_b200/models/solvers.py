@@ -296,6 +296,18 @@ class BatchSolver:
             pass
 
 
+def multi_gpu_solver(n, edges, ranks: int = 4, gpus: int = 0, device="cuda:0", **ctx_kw):
+    """The multi-GPU variant for the CLI / bench harness (the reference: `mpirun -np 6 ./mpi_bibfs`, v4/Makefile:63-64).
+    gpus >= 2: `gpus` ranks, one per device of this process (peer access between the devices, fused exchange over
+    NVLink); else `ranks` virtual ranks on `device`.  Returns (solver, number of GPUs used)."""
+    if gpus and gpus >= 2:
+        if torch.cuda.device_count() < gpus:
+            raise ValueError(f"--gpus {gpus}: this machine has {torch.cuda.device_count()} CUDA device(s)")
+        graphs = [Graph.from_edges(n, edges, device=f"cuda:{i}", nranks=gpus, ranks=[i]) for i in range(gpus)]
+        return MultiGpuSolver.across_devices(graphs, **ctx_kw), gpus
+    return MultiGpuSolver(Graph.from_edges(n, edges, device=device, nranks=ranks), **ctx_kw), 1
+
+
 def make_solver(graph: Graph, variant: str = "gpu", **kw):
     if variant == "serial":
         return SerialSolver(graph, **kw)

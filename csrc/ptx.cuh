@@ -45,14 +45,6 @@ __device__ __forceinline__ u64 ld_relaxed_gpu(const u64* p) {
 }
 
 // ---- system scope (peer GPUs over NVLink) -----------------------------------------------
-__device__ __forceinline__ u64 ld_acquire_sys(const u64* p) {
-    u64 v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(u64* p, u64 v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
 __device__ __forceinline__ u64 ld_relaxed_sys(const u64* p) {
     u64 v;
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -103,18 +95,6 @@ __device__ __forceinline__ uint4 ld_v4_gpu_if(bool on, const uint4* p) {
         : "memory");
     return r;
 }
-__device__ __forceinline__ uint4 ld_v4_sys_if(bool on, const uint4* p) {
-    uint4 r;
-    asm volatile(
-        "{\n\t.reg .pred q;\n\t"
-        "setp.ne.u32 q, %5, 0;\n\t"
-        "mov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\tmov.u32 %2, 0;\n\tmov.u32 %3, 0;\n\t"
-        "@q ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
-        : "=&r"(r.x), "=&r"(r.y), "=&r"(r.z), "=&r"(r.w)
-        : "l"(p), "r"((u32)on)
-        : "memory");
-    return r;
-}
 __device__ __forceinline__ u32 ld_relaxed_sys(const u32* p) {
     u32 v;
     asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -129,9 +109,6 @@ __device__ __forceinline__ void st_peer(u32* p, u32 v) {
 }
 __device__ __forceinline__ void st_peer_v2(u32* p, u32 a, u32 b) {
     asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
-}
-__device__ __forceinline__ void st_peer_v4(u32* p, u32 a, u32 b, u32 c, u32 d) {
-    asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
 // Scheduling fence for batches of independent atomics.  ptxas likes to consume the result of the first
@@ -176,13 +153,6 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, u32 b
                  "l"(gsrc), "r"(bytes), "r"(smem_addr(bar))
                  : "memory");
 }
-// shared -> global (works on peer-mapped global addresses too), bulk_group completion
-__device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, u32 bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_addr(smem_src)), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // shared-memory atomics through the shared window (a generic-address atomic on a shared location

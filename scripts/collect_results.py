@@ -5,17 +5,17 @@ import numpy as np, torch
 sys.path.insert(0, ".")
 import bidirectional_bfs_b200 as bb
 sys.path.insert(0, ".")
-from bench import make_spec, pick_queries
+import bench
 
 out = {}
 configs = sys.argv[1:] or ["er1k", "er10k", "er50k", "er100k", "er1m", "rmat20", "rmat10m", "grid1024", "grid16m"]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 for cfg in configs:
-    spec, desc = make_spec(bb, cfg, 1)
+    spec, desc = bench.make_spec(bb, cfg, 1), bench.spec_string(cfg, 1)[1]
     n = int(spec.n)
     t0 = time.time(); g = bb.Graph.generate(spec, device="cuda:0"); torch.cuda.synchronize(); build_s = time.time() - t0
     solver = bb.GpuSolver(g)
-    qs = pick_queries(lambda s, t: solver.query(s, t, want_path=False).length, n, 12, 1)
+    qs = [(a, b, L) for a, b, L, _, _ in bench.prepare(cfg, 1, 12)["queries"]]
     rec = {"desc": desc, "n": n, "nnz": g.nnz, "build_s": build_s, "queries": len(qs)}
     ms, pms, lev, edges = [], [], [], []
     for s, t, L in qs:

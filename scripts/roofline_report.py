@@ -6,16 +6,16 @@ import json, sys
 import numpy as np, torch
 sys.path.insert(0, ".")
 import bidirectional_bfs_b200 as bb
-from bench import make_spec, pick_queries
+import bench
 cfg = sys.argv[1]; flags = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 try:
     hbm = json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"]; src = "measured"
 except Exception:
     hbm = 6650.0; src = "fallback"
-spec, desc = make_spec(bb, cfg, 1)
+spec, desc = bench.make_spec(bb, cfg, 1), bench.spec_string(cfg, 1)[1]
 g = bb.Graph.generate(spec, device="cuda:0")
 s = bb.GpuSolver(g)
-qs = pick_queries(lambda a, b: s.query(a, b, want_path=False).length, int(spec.n), 3, 1)
+qs = [(a, b, L) for a, b, L, _, _ in bench.prepare(cfg, 1, 3)["queries"]]
 print(f"# {cfg}: {desc}; HBM peak {hbm} GB/s ({src}); flags={flags}")
 for a, b, L in qs:
     for _ in range(2): r = s.query(a, b, flags=1 | flags)
