@@ -104,6 +104,10 @@ def _declare(lib):
         "bibfs_cpu_ranks": (C.c_int, [u32, vp, vp, u32, u32, C.c_int, P(Result), vp, u32]),
         "bibfs_validate_path": (C.c_int, [u32, vp, vp, u32, u32, vp, u32]),
         "bibfs_block_size": (u32, [u32, u32]),
+        "bibfs_gen_chunks": (u64, [P(GenSpec)]),
+        "bibfs_csr_route_degree_device": (C.c_int, [u32, u64, vp, P(GenSpec), u64, u64, u32, vp, vp, vp]),
+        "bibfs_csr_route_fill_device": (C.c_int, [u32, u64, vp, P(GenSpec), u64, u64, u32, vp, vp, vp]),
+        "bibfs_csr_sort_rows_device": (C.c_int, [vp, vp, u32, vp]),
         "bibfs_vrec_bytes": (C.c_size_t, [u32]),
         "bibfs_vrec_build_device": (C.c_int, [vp, vp, u32, u64, vp, vp, vp]),
         "bibfs_ctx_create": (C.c_int, [P(vp), P(CtxDesc)]),

@@ -69,6 +69,14 @@ class Graph:
         part = Partition(n, nranks)
         g = Graph(n=n, nranks=nranks, device=dev, spec=spec, name=name)
         hosted = list(range(nranks)) if ranks is None else list(ranks)
+        if _sharded_build_applies(dev, nranks, hosted) and (spec is not None or edges is None):
+            # one process per GPU: each rank walks 1/P of the generator's chunks and routes the half-edges to their owners
+            from .parallel.build import build_shard
+            (r,) = hosted
+            lo, hi = part.range(r)
+            rp, col, _ = build_shard(n, dev, spec=spec, sort_rows=sort_rows)
+            g.shards[r] = Shard(r, lo, hi, rp, col)
+            return g
         if edges is not None:
             if isinstance(edges, np.ndarray):
                 edges = torch.from_numpy(np.ascontiguousarray(edges.reshape(-1, 2)).view(np.int32))
@@ -86,6 +94,19 @@ class Graph:
 
     @staticmethod
     def from_bin(path, device="cpu", nranks=1, ranks=None, sort_rows=False) -> "Graph":
+        dev = torch.device(device)
+        hosted = list(range(nranks)) if ranks is None else list(ranks)
+        if _sharded_build_applies(dev, nranks, hosted):
+            # one process per GPU: this rank reads and uploads only its M/P slice of the records
+            from .parallel.build import build_shard, read_bin_slice
+            (r,) = hosted
+            n, rec = read_bin_slice(path, r, nranks)
+            part = Partition(n, nranks)
+            lo, hi = part.range(r)
+            rp, col, m_slice = build_shard(n, dev, edges=torch.from_numpy(rec), sort_rows=sort_rows)
+            g = Graph(n=n, nranks=nranks, device=dev, name=str(path), m_records=m_slice)
+            g.shards[r] = Shard(r, lo, hi, rp, col)
+            return g
         n, edges = _io.read_bin(path)
         return Graph._build(n, edges, None, device, nranks, ranks, sort_rows, str(path))
 
@@ -173,6 +194,16 @@ class Graph:
         for r, s in self.shards.items():
             g.shards[r] = Shard(r, s.lo, s.hi, s.row_ptr.to(dev), padded_col(s.col, dev))
         return g
+
+
+def _sharded_build_applies(dev: torch.device, nranks: int, hosted: list) -> bool:
+    """The routed, sharded construction (parallel/build.py) is used when this process is one rank of a torch.distributed
+    group of `nranks` processes and builds exactly its own shard on a GPU (BIBFS_SHARDED_BUILD=0 turns it off)."""
+    import os
+    import torch.distributed as dist
+    if dev.type != "cuda" or nranks < 2 or len(hosted) != 1 or os.environ.get("BIBFS_SHARDED_BUILD") == "0":
+        return False
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() == nranks and dist.get_rank() == hosted[0]
 
 
 def padded_col(col: torch.Tensor, device) -> torch.Tensor:

@@ -39,6 +39,41 @@ __global__ void __launch_bounds__(256) k_fill(const Gen g, u32 n, u32 lo, u32 hi
     }
 }
 
+// ---- sharded construction: a rank walks only ITS slice of the edge stream and routes every half-edge to the rank that
+// owns the row, straight into that rank's degree histogram / cursor array / column array through the peer mappings
+// (the reference broadcasts the whole edge list to every rank instead, v4/mpi_bas.cpp:39-42).
+struct RoutePtrs {
+    u32* deg[BIBFS_MAX_RANKS];                       // owner's degree histogram (u32 per owned row)
+    unsigned long long* cursor[BIBFS_MAX_RANKS];     // owner's fill cursors (u64 per owned row, start = row offset)
+    u32* col[BIBFS_MAX_RANKS];                       // owner's column array
+};
+
+__global__ void __launch_bounds__(256) k_degree_routed(const Gen g, u64 c_lo, u64 c_hi, u32 n, u32 B, u64 div_b, const RoutePtrs R, u32* __restrict__ bad) {
+    for (u64 c = c_lo + (u64)blockIdx.x * blockDim.x + threadIdx.x; c < c_hi; c += (u64)gridDim.x * blockDim.x) {
+        g.for_each(c, [&](u32 u, u32 v) {
+            if (u >= n || v >= n) { *bad = 1; return; }
+            if (u == v) return;
+            const u32 ou = (u32)__umul64hi(div_b, (u64)u), ov = (u32)__umul64hi(div_b, (u64)v);
+            atomicAdd_system(R.deg[ou] + (u - ou * B), 1u);
+            atomicAdd_system(R.deg[ov] + (v - ov * B), 1u);
+        });
+    }
+}
+
+__global__ void __launch_bounds__(256) k_fill_routed(const Gen g, u64 c_lo, u64 c_hi, u32 n, u32 B, u64 div_b, const RoutePtrs R) {
+    for (u64 c = c_lo + (u64)blockIdx.x * blockDim.x + threadIdx.x; c < c_hi; c += (u64)gridDim.x * blockDim.x) {
+        g.for_each(c, [&](u32 u, u32 v) {
+            if (u == v || u >= n || v >= n) return;
+            const u32 ou = (u32)__umul64hi(div_b, (u64)u), ov = (u32)__umul64hi(div_b, (u64)v);
+            // both reservations first (two NVLink round trips in flight), then the two stores
+            const unsigned long long su = atomicAdd_system(R.cursor[ou] + (u - ou * B), 1ull);
+            const unsigned long long sv = atomicAdd_system(R.cursor[ov] + (v - ov * B), 1ull);
+            R.col[ou][su] = v;
+            R.col[ov][sv] = u;
+        });
+    }
+}
+
 // rows with <= 32 entries: one warp per row, bitonic sort in registers
 __global__ void __launch_bounds__(256) k_sort_rows_warp(const u64* __restrict__ row_ptr, u32* __restrict__ col, u32 rows) {
     const u32 lane = threadIdx.x & 31;
@@ -195,5 +230,68 @@ extern "C" int bibfs_csr_fill_device(uint32_t n, uint64_t m, const uint32_t* d_e
         k_sort_rows_cta<<<grid_for((u64)rows * 512, 512), 512, 0, st>>>(d_row_ptr, d_col, rows);
         BIBFS_KERNEL_CHECK();
     }
+    return 0;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// sharded construction (one process per GPU): see k_degree_routed / k_fill_routed.
+//   1. every rank zeroes its degree histogram (u32[B]); all ranks exchange the pointers (IPC)
+//   2. route_degree on the rank's chunk slice            -> barrier
+//   3. every rank scans ITS histogram (bibfs_scan_u32_device) -> row offsets, allocates col, copies the offsets
+//      into its cursor array; pointers exchanged           -> barrier
+//   4. route_fill on the rank's chunk slice               -> barrier;  optional bibfs_csr_sort_rows_device
+// chunk_lo / chunk_hi: slice of the generator's chunk space (bibfs_gen_chunks), or of the edge records.
+// ------------------------------------------------------------------------------------------
+extern "C" uint64_t bibfs_gen_chunks(const bibfs_gen_spec* spec) {
+    Gen g;
+    std::string why;
+    if (!spec || !make_gen(*spec, g, why)) return 0;
+    return g.nchunks;
+}
+
+static int route_args(uint32_t n, uint32_t nranks, uint64_t chunk_lo, uint64_t chunk_hi, const Gen& g) {
+    if (nranks < 1 || nranks > BIBFS_MAX_RANKS) return fail("nranks must be 1..%d", BIBFS_MAX_RANKS);
+    if (chunk_lo > chunk_hi || chunk_hi > g.nchunks) return fail("bad chunk slice [%llu,%llu) of %llu", (unsigned long long)chunk_lo, (unsigned long long)chunk_hi, (unsigned long long)g.nchunks);
+    return 0;
+}
+
+extern "C" int bibfs_csr_route_degree_device(uint32_t n, uint64_t m, const uint32_t* d_edges, const bibfs_gen_spec* spec,
+                                             uint64_t chunk_lo, uint64_t chunk_hi, uint32_t nranks,
+                                             uint32_t* const* d_deg_of_rank, uint32_t* d_bad_flag, void* stream) {
+    Gen g;
+    if (resolve_gen_dev(n, m, d_edges, spec, g) || route_args(n, nranks, chunk_lo, chunk_hi, g)) return 1;
+    RoutePtrs R = {};
+    for (u32 r = 0; r < nranks; ++r) R.deg[r] = d_deg_of_rank[r];
+    const u32 B = bibfs_block_size(n, nranks);
+    if (chunk_hi > chunk_lo) {
+        k_degree_routed<<<grid_for(chunk_hi - chunk_lo, 256), 256, 0, (cudaStream_t)stream>>>(g, chunk_lo, chunk_hi, n, B, ~0ull / B + 1ull, R, d_bad_flag);
+        BIBFS_KERNEL_CHECK();
+    }
+    return 0;
+}
+
+extern "C" int bibfs_csr_route_fill_device(uint32_t n, uint64_t m, const uint32_t* d_edges, const bibfs_gen_spec* spec,
+                                           uint64_t chunk_lo, uint64_t chunk_hi, uint32_t nranks,
+                                           uint64_t* const* d_cursor_of_rank, uint32_t* const* d_col_of_rank, void* stream) {
+    Gen g;
+    if (resolve_gen_dev(n, m, d_edges, spec, g) || route_args(n, nranks, chunk_lo, chunk_hi, g)) return 1;
+    RoutePtrs R = {};
+    for (u32 r = 0; r < nranks; ++r) { R.cursor[r] = (unsigned long long*)d_cursor_of_rank[r]; R.col[r] = d_col_of_rank[r]; }
+    const u32 B = bibfs_block_size(n, nranks);
+    if (chunk_hi > chunk_lo) {
+        k_fill_routed<<<grid_for(chunk_hi - chunk_lo, 256), 256, 0, (cudaStream_t)stream>>>(g, chunk_lo, chunk_hi, n, B, ~0ull / B + 1ull, R);
+        BIBFS_KERNEL_CHECK();
+    }
+    return 0;
+}
+
+extern "C" int bibfs_csr_sort_rows_device(const uint64_t* d_row_ptr, uint32_t* d_col, uint32_t rows, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!rows) return 0;
+    k_sort_rows_warp<<<grid_for((u64)rows * 32, 256), 256, 0, st>>>(d_row_ptr, d_col, rows);
+    BIBFS_KERNEL_CHECK();
+    k_sort_rows_cta<<<grid_for((u64)rows * 512, 512), 512, 0, st>>>(d_row_ptr, d_col, rows);
+    BIBFS_KERNEL_CHECK();
     return 0;
 }

@@ -194,6 +194,21 @@ typedef struct {
 
 uint32_t bibfs_block_size(uint32_t n, uint32_t nranks);
 
+/* Sharded CSR construction (one rank per GPU): a rank walks only its slice [chunk_lo, chunk_hi) of the edge stream (the
+ * generator's chunk space, bibfs_gen_chunks, or its M/P slice of the edge records) and routes each half-edge into the
+ * OWNER's degree histogram / cursor / column arrays through peer mappings (pointer tables indexed by rank; entries of
+ * other processes come from bibfs_ipc_import).  Sequence: route_degree -> barrier -> every rank scans its histogram
+ * (bibfs_scan_u32_device), allocates col, copies the row offsets into its cursors -> barrier -> route_fill -> barrier.
+ * Replaces the reference's MPI_Bcast of the whole edge list (v4/mpi_bas.cpp:39-42). */
+uint64_t bibfs_gen_chunks(const bibfs_gen_spec* spec);
+int bibfs_csr_route_degree_device(uint32_t n, uint64_t m, const uint32_t* d_edges, const bibfs_gen_spec* spec,
+                                  uint64_t chunk_lo, uint64_t chunk_hi, uint32_t nranks,
+                                  uint32_t* const* d_deg_of_rank, uint32_t* d_bad_flag, void* stream);
+int bibfs_csr_route_fill_device(uint32_t n, uint64_t m, const uint32_t* d_edges, const bibfs_gen_spec* spec,
+                                uint64_t chunk_lo, uint64_t chunk_hi, uint32_t nranks,
+                                uint64_t* const* d_cursor_of_rank, uint32_t* const* d_col_of_rank, void* stream);
+int bibfs_csr_sort_rows_device(const uint64_t* d_row_ptr, uint32_t* d_col, uint32_t rows, void* stream);
+
 /* Vertex records of a CSR shard: 32 bytes per row = {degree, row start (32 bits), first six neighbours}.
  * d_vrec: bibfs_vrec_bytes(rows) bytes, 32-byte aligned; nnz = stored entries of the shard (< 2^32).
  * bibfs_ctx_desc::max_degree (largest row of the WHOLE graph, 0 = unknown) lets the search skip the handling of long

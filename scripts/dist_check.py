@@ -13,9 +13,35 @@ torch.cuda.set_device(dev)
 ok = True
 for name, spec in (("er", bb.er_spec(30000, 2.2 / 30000, seed=1)), ("rmat", bb.rmat_spec(15, edgefactor=16, seed=3)),
                    ("grid", bb.grid_spec(150, 100)), ("er_dense", bb.er_spec(5000, 10.0 / 5000, seed=2))):
-    g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
+    g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])     # sharded, routed construction (parallel/build.py)
+    g_host = bb.Graph.generate(spec)
+    # this rank's shard against the host builder, row by row (the order inside a row is not fixed: compare sorted)
+    sh = g.shards[rank]
+    rp_h = g_host.single().row_ptr.numpy(); col_h = g_host.single().col.numpy().view(np.uint32)
+    rp_d = sh.row_ptr.cpu().numpy(); col_d = sh.col.cpu().numpy().view(np.uint32)
+    same = np.array_equal(rp_d - rp_d[0], rp_h[sh.lo:sh.hi + 1] - rp_h[sh.lo])
+    if same:
+        seg_h = col_h[rp_h[sh.lo]:rp_h[sh.hi]]
+        key_h = np.repeat(np.arange(sh.hi - sh.lo, dtype=np.int64), np.diff(rp_h[sh.lo:sh.hi + 1])) << 32
+        key_d = np.repeat(np.arange(sh.hi - sh.lo, dtype=np.int64), np.diff(rp_d)) << 32
+        same = np.array_equal(np.sort(key_h | seg_h), np.sort(key_d | col_d))
+    if not same:
+        ok = False
+        print(f"[rank {rank}] SHARD MISMATCH {name}: the routed build differs from the host builder", flush=True)
+    if name == "er":
+        # the same graph from a .bin file: every rank reads and uploads only its M/P slice of the records
+        import os, tempfile
+        path = os.path.join(tempfile.gettempdir(), "bibfs_dist_check.bin")
+        if rank == 0:
+            bb.io.write_bin(path, spec.n, bb.graph.edge_list(spec))
+        dist.barrier()
+        gb = bb.Graph.from_bin(path, device=dev, nranks=world, ranks=[rank])
+        rb = gb.shards[rank].row_ptr.cpu().numpy()
+        if not np.array_equal(rb, rp_d) or gb.m_records > (g_host.nnz // 2) // world + 1:
+            ok = False
+            print(f"[rank {rank}] BIN SHARD MISMATCH (records read here: {gb.m_records})", flush=True)
     solver = comm.DistributedSolver(g)
-    oracle = bb.SerialSolver(bb.Graph.generate(spec), policy=1)
+    oracle = bb.SerialSolver(g_host, policy=1)
     rng = np.random.default_rng(5)
     pairs = [(0, spec.n - 1), (3, 3)] + [(int(rng.integers(spec.n)), int(rng.integers(spec.n))) for _ in range(25)]
     for flags in (0, 64, 2, 2 | 8):          # default flow (front kernel), fused levels from the start, forced grid, forced bottom-up
