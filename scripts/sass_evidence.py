@@ -12,6 +12,7 @@ PAT = [("UBLKCP", "TMA 1-D bulk copy (cp.async.bulk)"), ("SYNCS", "mbarrier arri
        (r"LDG\.E\.STRONG\.GPU", "strong column loads of a claim batch"), ("ATOMS", "shared-memory atomics (cursors, accumulators)"), (r"MAPA|\.CLUSTER|LDS\.E\.U|STS\.E", "DSMEM access (mapa / shared::cluster)"),
        ("CCTL.E.PF2", "prefetch.global.L2 of row offsets"), ("REDUX", "redux.sync"), ("MATCH", "match.any aggregation"), ("VOTE", "ballot / any / all"), ("SHFL", "shuffles"),
        ("NANOSLEEP", "back-off of parked CTAs"), (r"MEMBAR\.ALL\.SYS", "fence.acq_rel.sys (bottom-up pushes, final exchange only)"), (r"LDG\.E\.(64\.)?CONSTANT", "read-only CSR loads"),
+       (r"LDG\.E\.128\.STRONG\.GPU", "32-byte vertex records (two 128-bit loads) of the pair tier"), (r"RED\.E\.OR\.STRONG\.SYS|REDG\.E\.OR\.STRONG\.SYS", "hand-over: visited bits to the owners (red.or.sys)"),
        ("POPC", "popc (incl. the zero_after scheduling fence)"), (r"HMMA|UTCMMA|UTCHMMA|QGMMA", "tensor-core instructions")]
 out = ["# cuobjdump -sass bidirectional_bfs_b200/_native/libbibfs_b200.so (sm_100a): occurrences of the instructions that show what each",
        "# kernel is built from.  Regenerate with: python scripts/sass_evidence.py.  There are deliberately no tensor-core instructions:",
@@ -29,6 +30,20 @@ for f in funcs:
             out.append(f"  {len(hits):6d}  {what}")
             out.append("          e.g. " + re.sub(r"\s+", " ", hits[0].split("/* 0x")[0]).strip())
     out.append("")
+    # full listing of the kernel (encodings stripped): docs/sass/full/<kernel>.sass
+    short = re.sub(r"[^A-Za-z0-9_]+", "_", re.sub(r"\(.*", "", dem.replace("(anonymous namespace)::", "").replace("bibfs::", "").replace("void ", ""))).strip("_")
+    full = docs / "full"; full.mkdir(exist_ok=True)
+    (full / f"{short}.sass").write_text(f"// {dem}\n" + "\n".join(re.sub(r"\s+/\* 0x[0-9a-f]+ \*/", "", l) for l in lines) + "\n")
+    if "k_front" in dem and ("false" in dem or "(bool)0" in dem):
+        ld = [i for i, l in enumerate(lines) if "LDG.E.128.STRONG.GPU" in l]
+        runs = [i for k, i in enumerate(ld) if k + 11 < len(ld) and ld[k + 11] - i < 60]
+        if runs:
+            seg = lines[max(0, runs[0] - 30): runs[0] + 140]
+            (docs / "k_front_pair_batch.sass").write_text("\n".join(re.sub(r"\s+/\* 0x[0-9a-f]+ \*/", "", l) for l in seg) + "\n")
+        cb = [i for i, l in enumerate(lines) if "UCGABAR" in l]
+        if cb:
+            seg = lines[max(0, cb[-1] - 30): cb[-1] + 30]
+            (docs / "k_front_wide_round_cluster_barrier.sass").write_text("\n".join(re.sub(r"\s+/\* 0x[0-9a-f]+ \*/", "", l) for l in seg) + "\n")
     if "k_bibfs" in dem and "false" in dem or "k_bibfs<(bool)0>" in dem:
         # excerpts: first 8-atomic batch with its loads, first UBLKCP neighbourhood, first cluster barrier
         def excerpt(tag, idx, before, after):
