@@ -38,7 +38,7 @@ struct bibfs_ctx {
     u32 front_cluster = 1;       // thread-block cluster of the front kernel (wide rounds)
     // the cluster launch costs ~1.5 us more than a single CTA: contexts whose queries never go wide drop it, and take it
     // back when a single-CTA front kernel has to hand a search over
-    bool front_narrow = false;
+    bool front_narrow = true;        // start with the single CTA: the first search that outgrows it brings the cluster in
     int no_wide_streak = 0;
     int front_mode = 0;          // BIBFS_FRONT: 0 policy, 1 always, 2 never
     int front_score = 0;         // policy: rises when the front kernel hands over after a few levels (hub graphs), falls otherwise
@@ -130,6 +130,7 @@ extern "C" int bibfs_ctx_create(bibfs_ctx** out, const bibfs_ctx_desc* desc) {
     c->hosts_all = desc->vranks == desc->nranks;
     for (u32 i = 0; i < desc->vranks; ++i) { c->col_all[desc->rank_lo + i] = desc->d_col[i]; c->vrec_all[desc->rank_lo + i] = desc->d_vrec[i]; }
     if (c->hosts0 && front_prepare(c->multi, &c->front_cluster)) { delete c; return 1; }
+    if (getenv("BIBFS_FRONT_CLUSTER") || c->front_cluster == 1) c->front_narrow = false;
     for (u32 i = 0; i < desc->vranks; ++i)
         if (reinterpret_cast<uintptr_t>(desc->d_vrec[i]) & 31u) { delete c; return fail("d_vrec of hosted rank %u is not 32-byte aligned", desc->rank_lo + i); }
     for (u32 i = 0; i < desc->vranks; ++i) {

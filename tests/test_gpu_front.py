@@ -63,6 +63,8 @@ def test_single_rank_front_then_general_kernel(bb):
     spec = bb.grid_spec(1500, 1300)
     g_cpu = bb.Graph.generate(spec)
     solver = bb.GpuSolver(bb.Graph.generate(spec, device="cuda:0"))
+    r = solver.query(0, spec.n - 1)          # a context starts with the single-CTA front kernel: this search outgrows it,
+    assert r.length == 1499 + 1299 and 0 < r.levels_paired < r.levels       # is handed to the general kernel, and brings the cluster in
     for timing in ("device", "events"):
         r = solver.query(0, spec.n - 1, timing=timing)
         assert r.length == 1499 + 1299 and r.levels_paired == r.levels
