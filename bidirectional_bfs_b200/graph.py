@@ -34,7 +34,7 @@ class Shard:
         return int(self.col.numel())
 
     def vertex_records(self) -> torch.Tensor | None:
-        """32-byte record per owned vertex {degree, row start, first six neighbours} for the latency tier of the search
+        """64-byte record per owned vertex ({degree, row start, first six neighbours} + neighbours 7..14) for the latency tier of the search
         kernel (csrc/pair_tier.cuh); CUDA shards with < 2^32 stored entries only, else None."""
         if self.vrec is None and self.row_ptr.device.type == "cuda" and self.nnz < (1 << 32) and self.hi > self.lo:
             import ctypes as C
@@ -42,7 +42,7 @@ class Shard:
             rows = self.hi - self.lo
             dev = self.row_ptr.device
             with torch.cuda.device(dev):
-                out = torch.empty(rows * 8, dtype=torch.int32, device=dev)
+                out = torch.empty(rows * 16, dtype=torch.int32, device=dev)
                 colp = self.col.data_ptr() if self.col.numel() else self.row_ptr.data_ptr()
                 mx = torch.zeros(1, dtype=torch.int32, device=dev)
                 check(lib().bibfs_vrec_build_device(self.row_ptr.data_ptr(), colp, rows, self.nnz, out.data_ptr(), mx.data_ptr(),

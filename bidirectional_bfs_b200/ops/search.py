@@ -141,13 +141,13 @@ class SearchContext:
                 self.graph_ptrs[rank] = (col.value, vrec.value)
 
     def replicate_records(self, shared_by_rank: list) -> bool:
-        """Keep a LOCAL, contiguous copy of every shard's vertex records (32 bytes per vertex: the index the front kernel
+        """Keep a LOCAL, contiguous copy of every shard's vertex records (64 bytes per vertex: the index the front kernel
         walks) instead of reading the other shards' records over NVLink: a round of the front kernel then costs what it
         costs on one GPU, and the copy is streamed into L2 at query start like on one GPU.  The adjacency itself (col)
         stays with its owner; rows longer than six entries are still read from there."""
         B, P = self.graph.partition.B, self.nranks
         with torch.cuda.device(self.device):
-            full = torch.zeros(B * P * 8, dtype=torch.int32, device=self.device)
+            full = torch.zeros(B * P * 16, dtype=torch.int32, device=self.device)
             cols = {}
             for r in range(P):
                 lo, hi = self.graph.partition.range(r)
@@ -160,12 +160,12 @@ class SearchContext:
                 if hi > lo and not src:
                     return False
                 if hi > lo:
-                    check(lib().bibfs_copy_device(full.data_ptr() + r * B * 32, src, (hi - lo) * 32, self._stream()))
+                    check(lib().bibfs_copy_device(full.data_ptr() + r * B * 64, src, (hi - lo) * 64, self._stream()))
             torch.cuda.synchronize(self.device)
             self._record_replica = full
             for r in range(P):
-                check(lib().bibfs_ctx_set_peer_graph(self._h, r, C.c_void_p(cols[r]), C.c_void_p(full.data_ptr() + r * B * 32)))
-                self.graph_ptrs[r] = (cols[r], full.data_ptr() + r * B * 32)
+                check(lib().bibfs_ctx_set_peer_graph(self._h, r, C.c_void_p(cols[r]), C.c_void_p(full.data_ptr() + r * B * 64)))
+                self.graph_ptrs[r] = (cols[r], full.data_ptr() + r * B * 64)
         return True
 
     def resume(self) -> None:

@@ -42,7 +42,7 @@ class DistributedSolver:
     variant = "multi-gpu"
 
     def __init__(self, graph: Graph, record_replica_mb: int | None = None, **ctx_kw):
-        """record_replica_mb: rank 0 keeps a local copy of the other shards' vertex records (32 bytes per vertex, the index
+        """record_replica_mb: rank 0 keeps a local copy of the other shards' vertex records (64 bytes per vertex, the index
         its front kernel walks) when all of them fit this many MB; beyond that it reads them through the peer mappings.
         Default 1024 (BIBFS_RECORD_REPLICA_MB overrides; 0 = never).  The CSR itself is never replicated."""
         if not dist.is_initialized():
@@ -71,7 +71,7 @@ class DistributedSolver:
             if record_replica_mb is None:
                 record_replica_mb = int(os.environ.get("BIBFS_RECORD_REPLICA_MB", "1024"))
             self.records_replicated = False
-            if self.rank == 0 and graph.n * 32 <= record_replica_mb << 20:
+            if self.rank == 0 and graph.n * 64 <= record_replica_mb << 20:
                 self.records_replicated = self.ctx.replicate_records(shared)
             if not self.records_replicated:
                 for r, sh in enumerate(shared):

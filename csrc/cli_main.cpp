@@ -236,6 +236,9 @@ int main(int argc, char** argv) {
         std::vector<bibfs_ctx*> ctx(ngroups, nullptr);
         std::vector<u64*> d_rp(P, nullptr);
         std::vector<u32*> d_col(P, nullptr);
+        std::vector<void*> d_vrec(P, nullptr);        // 32-byte vertex records: the front kernel's index (csrc/vrec_dev.cu)
+        u32 max_degree = 0;
+        for (u32 v = 0; v < g.n; ++v) { const u64 dg = g.row_ptr[v + 1] - g.row_ptr[v]; if (dg > max_degree) max_degree = (u32)(dg > 0xFFFFFFFFull ? 0xFFFFFFFFull : dg); }
         for (u32 r = 0; r < P; ++r) {
             const int dev = (ngroups > 1) ? (int)r : 0;
             CU(cudaSetDevice(dev));
@@ -248,13 +251,19 @@ int main(int argc, char** argv) {
             CU(cudaMalloc(&d_rp[r], rp.size() * 8)); CU(cudaMalloc(&d_col[r], nnz * 4 + 16));
             CU(cudaMemcpy(d_rp[r], rp.data(), rp.size() * 8, cudaMemcpyHostToDevice));
             if (nnz) CU(cudaMemcpy(d_col[r], g.col.data() + base, nnz * 4, cudaMemcpyHostToDevice));
+            if (hi > lo && nnz < (1ull << 32)) {
+                CU(cudaMalloc(&d_vrec[r], (size_t)B * 64));
+                CU(cudaMemset(d_vrec[r], 0, (size_t)B * 64));
+                CK(bibfs_vrec_build_device(d_rp[r], d_col[r], hi - lo, nnz, d_vrec[r], nullptr, nullptr));
+            }
         }
         for (u32 gi = 0; gi < ngroups; ++gi) {
             CU(cudaSetDevice((int)gi));
             bibfs_ctx_desc d;
             memset(&d, 0, sizeof(d));
             d.n = g.n; d.nranks = P; d.rank_lo = gi * vr; d.vranks = vr;
-            for (u32 i = 0; i < vr; ++i) { d.d_row_ptr[i] = d_rp[gi * vr + i]; d.d_col[i] = d_col[gi * vr + i]; }
+            for (u32 i = 0; i < vr; ++i) { d.d_row_ptr[i] = d_rp[gi * vr + i]; d.d_col[i] = d_col[gi * vr + i]; d.d_vrec[i] = d_vrec[gi * vr + i]; }
+            d.max_degree = max_degree;
             d.max_path = g.n + 1 < (1u << 20) ? (1u << 20) : g.n + 1;
             CK(bibfs_ctx_create(&ctx[gi], &d));
         }
@@ -270,6 +279,13 @@ int main(int argc, char** argv) {
             for (u32 gi = 0; gi < ngroups; ++gi) {
                 bibfs_result rr;
                 CK(bibfs_ctx_result(ctx[gi], &rr, gi == 0 ? path.data() : nullptr, (u32)path.size(), nullptr));
+                if (gi == 0 && rr.status == BIBFS_STATUS_HANDED_OVER) {
+                    // several devices in this process: rank 0's front kernel handed the search over, every context continues it
+                    for (u32 gj = 0; gj < ngroups; ++gj) CK(bibfs_ctx_resume(ctx[gj], nullptr));
+                    CK(bibfs_ctx_result(ctx[0], &rr, path.data(), (u32)path.size(), nullptr));
+                } else if (gi > 0 && rr.status == BIBFS_STATUS_HANDED_OVER) {
+                    continue;           // rank 0 answered alone
+                }
                 if (gi == 0) res = rr;
                 if (rr.search_ms > worst_search) worst_search = rr.search_ms;   // max over ranks
                 if (rr.path_ms > worst_path) worst_path = rr.path_ms;

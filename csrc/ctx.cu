@@ -264,8 +264,8 @@ static void fill_params(bibfs_ctx* c, KParams& K, u32 src, u32 dst, bool in_ctrl
     if (c->vrec_all[0] && c->hosts0) {
         // how many of the records are local and contiguous behind rank 0's (its own shard; every shard with a record replica)
         u32 local = 1;
-        while (local < c->d.nranks && c->vrec_all[local] == (const char*)c->vrec_all[0] + (size_t)local * c->B * 32) ++local;
-        const u64 bytes = local == c->d.nranks ? (u64)c->d.n * 32ull : (u64)c->B * 32ull;
+        while (local < c->d.nranks && c->vrec_all[local] == (const char*)c->vrec_all[0] + (size_t)local * c->B * 64) ++local;
+        const u64 bytes = local == c->d.nranks ? (u64)c->d.n * 64ull : (u64)c->B * 64ull;
         if (bytes <= (24ull << 20)) K.warm_lines = (u32)((bytes + 127ull) / 128ull);
     }
 }

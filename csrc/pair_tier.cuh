@@ -6,13 +6,14 @@
 // (row offsets -> adjacency entries -> visited word) and runs one side per level.  This tier cuts
 // the chain to ONE round trip per round, and halves the number of rounds:
 //
-//   * vertex records ("vrec", built once per shard by k_vrec_build): 32 bytes per vertex =
-//     {degree, row start, first six neighbours}.  When v is a CANDIDATE (read from its parent's
+//   * vertex records ("vrec", built once per shard by k_vrec_build): two 32-byte sectors per vertex, the first =
+//     {degree, row start, first six neighbours}, the second = neighbours 7..14 (read only by rows that long).  When v is a CANDIDATE (read from its parent's
 //     record) its own record is fetched in the same instruction slot as the atomic that claims it:
 //     the claim (285 ns) and the fetch (154 ns, L2) overlap, and a newly discovered vertex enters
 //     the next frontier WITH its neighbours already in shared memory.  A round is
 //         shared memory -> { claim || record fetch } -> shared memory -> one __syncthreads.
-//     Rows longer than six entries read the rest from col[] (a second trip, for those rows only).
+//     Rows longer than six entries read the second sector, rows longer than 14 the rest from col[] (further trips,
+//     for those rows only).
 //   * both directions expand in the SAME round on disjoint warps (the reference's v2/v3 expand S
 //     and T in one iteration too, v2/second_try.cpp:70-105 — and print ceil(d/2)).
 //     Exact length rule used here: balls are disjoint when a round starts, so every vertex that
@@ -126,9 +127,9 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, PairSmemT<PT_CAP>
     // record / adjacency bases indexed by the GLOBAL vertex id resp. the owner's row start
     __shared__ const uint4* s_vrecb[MAXR];
     __shared__ const u32* s_colb[MAXR];
-    if (MULTI && tid < K.P) { s_vrecb[tid] = K.vrec[tid] - 2 * (size_t)tid * K.B; s_colb[tid] = K.col[tid]; }
-    const uint4* const vrec0 = MULTI ? nullptr : K.vrec[E.me] - 2 * (size_t)E.lo;
-    auto rec_of = [&](u32 v) -> const uint4* { return (MULTI ? s_vrecb[owner(v)] : vrec0) + 2 * (size_t)v; };
+    if (MULTI && tid < K.P) { s_vrecb[tid] = K.vrec[tid] - 4 * (size_t)tid * K.B; s_colb[tid] = K.col[tid]; }
+    const uint4* const vrec0 = MULTI ? nullptr : K.vrec[E.me] - 4 * (size_t)E.lo;
+    auto rec_of = [&](u32 v) -> const uint4* { return (MULTI ? s_vrecb[owner(v)] : vrec0) + 4 * (size_t)v; };
     // (records and adjacency never change: gpu-scope loads are enough also when they come from a peer's memory, and
     //  system-scope loads were measured 2 us per round slower even on local memory)
     auto ld_rec_if = [&](bool on, const uint4* p) -> uint4 { return ptx::ld_v4_gpu_if(on, p); };
@@ -252,7 +253,21 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, PairSmemT<PT_CAP>
                 const u32 c[PT_NB] = {ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
                 batch(std::integral_constant<int, PT_NB>{}, c, min(deg, (u32)PT_NB));
             }
-            for (u32 e = PT_NB; __any_sync(FULL, e < deg); e += PT_W) {
+            // entries 7..14 come from the record's second sector, the rest (rare) from col[]
+            if (__any_sync(FULL, deg > (u32)PT_NB)) {
+                const bool ext = deg > (u32)PT_NB;
+                const uint4* xp = rec_of(u) + 2;
+                const uint4 xa = ld_rec_if(ext, xp), xb = ld_rec_if(ext, xp + 1);
+                {
+                    const u32 c[PT_W] = {xa.x, xa.y, xa.z, xa.w};
+                    batch(std::integral_constant<int, PT_W>{}, c, min(ext ? deg - PT_NB : 0u, (u32)PT_W));
+                }
+                if (__any_sync(FULL, deg > (u32)PT_NB + PT_W)) {
+                    const u32 c[PT_W] = {xb.x, xb.y, xb.z, xb.w};
+                    batch(std::integral_constant<int, PT_W>{}, c, min(deg > (u32)PT_NB + PT_W ? deg - PT_NB - PT_W : 0u, (u32)PT_W));
+                }
+            }
+            for (u32 e = PT_NB + 2 * PT_W; __any_sync(FULL, e < deg); e += PT_W) {
                 u32 c[PT_W];
                 const u32 left = deg > e ? deg - e : 0u;
 #pragma unroll
@@ -394,9 +409,9 @@ __device__ __noinline__ u64 pair_wide(const KParams& K, Env E, const PairIO io, 
     auto owner = [div_b](u32 v) -> u32 { return (u32)__umul64hi(div_b, (u64)v); };
     __shared__ const uint4* s_vrecb[MAXR];
     __shared__ const u32* s_colb[MAXR];
-    if (MULTI && tid < K.P) { s_vrecb[tid] = K.vrec[tid] - 2 * (size_t)tid * K.B; s_colb[tid] = K.col[tid]; }
-    const uint4* const vrec0 = MULTI ? nullptr : K.vrec[E.me] - 2 * (size_t)E.lo;
-    auto rec_of = [&](u32 v) -> const uint4* { return (MULTI ? s_vrecb[owner(v)] : vrec0) + 2 * (size_t)v; };
+    if (MULTI && tid < K.P) { s_vrecb[tid] = K.vrec[tid] - 4 * (size_t)tid * K.B; s_colb[tid] = K.col[tid]; }
+    const uint4* const vrec0 = MULTI ? nullptr : K.vrec[E.me] - 4 * (size_t)E.lo;
+    auto rec_of = [&](u32 v) -> const uint4* { return (MULTI ? s_vrecb[owner(v)] : vrec0) + 4 * (size_t)v; };
     __shared__ u32 s_cnt[2], s_gbase[2];
     if (tid < 2) s_cnt[tid] = 0;
     __syncthreads();
@@ -508,7 +523,19 @@ __device__ __noinline__ u64 pair_wide(const KParams& K, Env E, const PairIO io, 
                 const u32 c[PT_NB] = {ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
                 batch(std::integral_constant<int, PT_NB>{}, c, min(sdeg, (u32)PT_NB), u, side);
             }
-            for (u32 e = PT_NB; __any_sync(FULL, e < sdeg); e += PT_W) {
+            if (__any_sync(FULL, sdeg > (u32)PT_NB)) {          // entries 7..14: the record's second sector
+                const bool ext = sdeg > (u32)PT_NB;
+                const uint4 xa = ptx::ld_v4_gpu_if(ext, rp + 2), xb = ptx::ld_v4_gpu_if(ext, rp + 3);
+                {
+                    const u32 c[PT_W] = {xa.x, xa.y, xa.z, xa.w};
+                    batch(std::integral_constant<int, PT_W>{}, c, min(ext ? sdeg - PT_NB : 0u, (u32)PT_W), u, side);
+                }
+                if (__any_sync(FULL, sdeg > (u32)PT_NB + PT_W)) {
+                    const u32 c[PT_W] = {xb.x, xb.y, xb.z, xb.w};
+                    batch(std::integral_constant<int, PT_W>{}, c, min(sdeg > (u32)PT_NB + PT_W ? sdeg - PT_NB - PT_W : 0u, (u32)PT_W), u, side);
+                }
+            }
+            for (u32 e = PT_NB + 2 * PT_W; __any_sync(FULL, e < sdeg); e += PT_W) {
                 u32 c[PT_W];
                 const u32 left = sdeg > e ? sdeg - e : 0u;
 #pragma unroll

@@ -209,7 +209,7 @@ int bibfs_csr_route_fill_device(uint32_t n, uint64_t m, const uint32_t* d_edges,
                                 uint64_t* const* d_cursor_of_rank, uint32_t* const* d_col_of_rank, void* stream);
 int bibfs_csr_sort_rows_device(const uint64_t* d_row_ptr, uint32_t* d_col, uint32_t rows, void* stream);
 
-/* Vertex records of a CSR shard: 32 bytes per row = {degree, row start (32 bits), first six neighbours}.
+/* Vertex records of a CSR shard: 64 bytes per row = {degree, row start (32 bits), first six neighbours} + {neighbours 7..14}.
  * d_vrec: bibfs_vrec_bytes(rows) bytes, 32-byte aligned; nnz = stored entries of the shard (< 2^32).
  * bibfs_ctx_desc::max_degree (largest row of the WHOLE graph, 0 = unknown) lets the search skip the handling of long
  * rows on graphs that have none.

@@ -177,3 +177,29 @@ def test_query_pool_on_a_partitioned_graph(bb):
                 answered += 1
         assert answered >= 60
         check(lib().bibfs_pool_destroy(pool))
+
+
+def test_native_cli_gpu_variants(bb, tmp_path):
+    """bin/bibfs (the reference's argv shape): front kernel on one GPU and on four virtual ranks."""
+    import re
+    import subprocess
+    from pathlib import Path
+    exe = Path(__file__).resolve().parent.parent / "bin" / "bibfs"
+    if not exe.exists():
+        pytest.skip("native CLI not built")
+    spec = bb.er_spec(20000, 2.4 / 20000, seed=6)
+    edges = bb.graph.edge_list(spec)
+    path = tmp_path / "g.bin"
+    bb.io.write_bin(path, spec.n, edges)
+    g_cpu = bb.Graph.from_edges(spec.n, edges)
+    oracle = bb.SerialSolver(g_cpu, policy=1)
+    s, t = next((a, b) for a, b in query_pairs(spec.n, 60, 5) if (oracle.query(a, b, want_path=False).length or 0) > 3)
+    want = oracle.query(s, t, want_path=False).length
+    for extra in (["--variant", "gpu"], ["--variant", "multi-gpu", "--vranks", "4"]):
+        out = subprocess.run([str(exe), str(path), str(s), str(t)] + extra, capture_output=True, text=True, timeout=120)
+        assert out.returncode == 0, out.stdout + out.stderr
+        m = re.search(r"Shortest path length = (\d+)", out.stdout)
+        assert m and int(m.group(1)) == want, out.stdout
+        p = re.search(r"Path: ([\d ]+)", out.stdout)
+        nodes = [int(x) for x in p.group(1).split()]
+        bb.validate_path(g_cpu, s, t, nodes, want)
