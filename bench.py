@@ -278,12 +278,12 @@ def measure_batch(bb, comm, dist, torch, dev, rank, world, config, seed, nq=64):
     if world == 1:
         g = bb.Graph.generate(spec, device=dev)
         single = bb.GpuSolver(g)
-        pool = bb.BatchSolver(g, lanes=32)
+        pool = bb.BatchSolver(g, lanes=64)
         run = lambda a, b: pool.query_batch(a, b)
     else:
         g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
         single = comm.DistributedSolver(g)
-        run = lambda a, b: single.query_batch(a, b, lanes=32)
+        run = lambda a, b: single.query_batch(a, b, lanes=64)
     torch.cuda.synchronize()
     build_s = time.time() - t0
     rng = np.random.default_rng(seed + 64)

@@ -100,9 +100,10 @@ class DistributedSolver:
 
     def query_batch(self, srcs, dsts, lanes: int = 32) -> list[int | None]:
         """Lengths of a batch of queries (BASELINE config 5: 64 random queries on a graph that is partitioned over the
-        GPUs).  Rank 0 runs a pool of `lanes` front kernels side by side — each one rank 0 working ALONE on the whole
-        partitioned graph through the peer mappings (pair tier, wide rounds, long rows over its cluster), so the searches
-        overlap their latency chains instead of queueing behind one another; the few searches a lane cannot finish
+        GPUs).  Rank 0 answers the batch with ONE launch whose thread-block clusters are `lanes` front kernels
+        side by side — each one rank 0 working ALONE on the whole partitioned graph through the peer mappings (pair tier,
+        wide rounds, long rows over its cluster), so the searches overlap their latency chains instead of queueing behind
+        one another; the few searches a lane cannot finish
         (frontier beyond 65536 per side) are then answered by the whole group, one at a time.  The reference answers one
         query per process (benchmark_test.sh:47-54).  Every rank calls this with the same lists; `last_batch_ms` holds
         the device time of the pooled part on rank 0."""
@@ -127,10 +128,15 @@ class DistributedSolver:
                 ms = C.c_float(0)
                 check(lib().bibfs_pool_query(self._pool, srcs.ctypes.data, dsts.ctypes.data, nq, lens.ctypes.data, None, None, None, C.byref(ms)))
                 self.last_batch_ms = float(ms.value)
-        box = [lens.tolist()]
-        dist.broadcast_object_list(box, src=0)
+        # the lengths go to the other ranks as ONE tensor broadcast (an object broadcast pickles and sends twice: 0.4 ms)
+        buf = getattr(self, "_batch_buf", None)
+        if buf is None or buf.numel() < nq:
+            buf = self._batch_buf = torch.empty(max(nq, 1024), dtype=torch.int32, device=self.graph.device)
+        if self.rank == 0:
+            buf[:nq].copy_(torch.from_numpy(lens))
+        dist.broadcast(buf[:nq], src=0)
         out = []
-        for i, L in enumerate(box[0]):
+        for i, L in enumerate(buf[:nq].tolist()):
             if L == -2:                      # not answered by the pool: the whole group takes it
                 out.append(self.query(int(srcs[i]), int(dsts[i]), want_path=False).length)
             else:

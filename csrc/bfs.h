@@ -213,6 +213,8 @@ int bfs_max_ctas_clustered(u32 cluster, int* out);
 int bfs_launch(const KParams& K, bool multi, cudaStream_t st);
 int front_launch(const KParams& K, bool multi, u32 cluster, cudaStream_t st);
 int wait_launch(const KParams& K, cudaStream_t st);
+int front_batch_prepare(bool multi);
+int front_batch_launch(const KParams* d_lane_K, unsigned long long* d_queries, Result* h_res, u32 nq, u32 lanes, bool multi, u32 cluster, cudaStream_t st);
 int front_prepare(bool multi, u32* cluster_out);
 #endif
 

@@ -2197,6 +2197,30 @@ int front_launch(const KParams& K, bool multi, u32 cluster, cudaStream_t st) {
     return 0;
 }
 
+// one launch for a batch of queries: `lanes` clusters of `cluster` CTAs, lane i works with d_lane_K[i]
+int front_batch_prepare(bool multi) {
+    if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_front_batch<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrontSmem)));
+    else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_front_batch<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrontSmem)));
+    return 0;
+}
+
+int front_batch_launch(const KParams* d_lane_K, unsigned long long* d_queries, Result* h_res, u32 nq, u32 lanes, bool multi, u32 cluster, cudaStream_t st) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(lanes * cluster);
+    cfg.blockDim = dim3(BFS_THREADS);
+    cfg.dynamicSmemBytes = sizeof(FrontSmem);
+    cfg.stream = st;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = cluster > 1 ? 1 : 0;
+    if (multi) BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front_batch<true>, d_lane_K, d_queries, h_res, nq));
+    else BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front_batch<false>, d_lane_K, d_queries, h_res, nq));
+    count_launch();
+    return 0;
+}
+
 int wait_launch(const KParams& K, cudaStream_t st) {
     k_wait<<<1, 32, 0, st>>>(K);
     BIBFS_KERNEL_CHECK();

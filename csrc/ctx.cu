@@ -498,9 +498,9 @@ extern "C" int bibfs_ctx_trace(bibfs_ctx* c, uint32_t i, bibfs_level_trace* out,
 //
 // A bidirectional search touches a sliver of the graph and is bound by the latency of its
 // level chain, not by bandwidth, so one query cannot use more than a few SMs — but 148 SMs can
-// chase 148 chains at once.  The pool owns `lanes` single-rank contexts, each launching a small
-// cooperative grid (default 1 CTA) on its own stream; queries are dealt round-robin and the
-// 64-byte results are copied into pinned memory in stream order.  (The bit-parallel MS-BFS engine
+// chase 148 chains at once.  The pool owns `lanes` single-rank contexts (one search arena each); a batch is ONE
+// launch in which every thread-block cluster is a lane that takes every lanes-th query (k_front_batch, front.cuh)
+// and writes its 64-byte results straight into pinned memory.  (The bit-parallel MS-BFS engine
 // of msbfs_dev.cu sweeps all N vertices per level instead: better only when the searches are
 // heavy and overlap.)  No counterpart in the reference (one query per process).
 // ------------------------------------------------------------------------------------------
@@ -513,6 +513,14 @@ struct bibfs_pool {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     Result* h_res = nullptr;
     size_t h_cap = 0;
+    // one launch per batch (k_front_batch): the lanes' kernel parameters on the device, uploaded when they change, and
+    // the queries of the batch behind a pinned staging copy
+    KParams* h_lane_K = nullptr;
+    KParams* d_lane_K = nullptr;
+    bool lanes_dirty = true;
+    unsigned long long* h_q = nullptr;
+    unsigned long long* d_q = nullptr;
+    int sms = 0;
     int device = 0;
 };
 
@@ -526,6 +534,10 @@ extern "C" int bibfs_pool_destroy(bibfs_pool* p) {
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
     if (p->h_res) cudaFreeHost(p->h_res);
+    if (p->h_lane_K) cudaFreeHost(p->h_lane_K);
+    if (p->d_lane_K) cudaFree(p->d_lane_K);
+    if (p->h_q) cudaFreeHost(p->h_q);
+    if (p->d_q) cudaFree(p->d_q);
     delete p;
     return 0;
 }
@@ -559,12 +571,19 @@ extern "C" int bibfs_pool_create(bibfs_pool** out, const bibfs_ctx_desc* desc, u
     // lanes run their front kernels side by side: small clusters (4 CTAs: long rows and wide rounds still work)
     p->lane_cluster = p->ctx[0]->front_cluster >= 4 ? 4u : p->ctx[0]->front_cluster;
     if (const char* e = getenv("BIBFS_POOL_CLUSTER")) { const u32 v = (u32)atoi(e); if (v >= 1 && v <= p->ctx[0]->front_cluster && !(v & (v - 1))) p->lane_cluster = v; }
+    cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, p->device);
+    if (cudaHostAlloc((void**)&p->h_lane_K, lanes * sizeof(KParams), cudaHostAllocDefault) != cudaSuccess ||
+        cudaMalloc((void**)&p->d_lane_K, lanes * sizeof(KParams)) != cudaSuccess || front_batch_prepare(p->multi)) {
+        bibfs_pool_destroy(p);
+        return fail("query pool: allocation of the lane parameters failed");
+    }
     *out = p;
     return 0;
 }
 
 extern "C" int bibfs_pool_set_peer_graph(bibfs_pool* p, uint32_t rank, const uint32_t* d_col, const void* d_vrec) {
     if (!p) return fail("NULL pool");
+    p->lanes_dirty = true;
     for (auto c : p->ctx)
         if (bibfs_ctx_set_peer_graph(c, rank, d_col, d_vrec)) return 1;
     return 0;
@@ -576,41 +595,64 @@ extern "C" int bibfs_pool_query(bibfs_pool* p, const uint32_t* h_src, const uint
     DeviceGuard g(p->device);
     if (nq > p->h_cap) {
         if (p->h_res) cudaFreeHost(p->h_res);
-        p->h_res = nullptr;
+        if (p->h_q) cudaFreeHost(p->h_q);
+        if (p->d_q) cudaFree(p->d_q);
+        p->h_res = nullptr; p->h_q = nullptr; p->d_q = nullptr;
         p->h_cap = 0;
         const size_t cap = nq < 1024 ? 1024 : nq;
         BIBFS_CUDA_TRY(cudaHostAlloc((void**)&p->h_res, cap * sizeof(Result), cudaHostAllocDefault));
+        BIBFS_CUDA_TRY(cudaHostAlloc((void**)&p->h_q, (cap + 1) * sizeof(unsigned long long), cudaHostAllocDefault));      // + the lanes' query counter
+        BIBFS_CUDA_TRY(cudaMalloc((void**)&p->d_q, (cap + 1) * sizeof(unsigned long long)));
         p->h_cap = cap;
     }
     const size_t L = p->ctx.size();
-    // with vertex records for every rank a lane runs the FRONT kernel (pair tier, wide rounds, long rows) as a small
-    // cluster and delivers its 64-byte result straight into the pinned array; without them (or when the front kernel
-    // cannot finish a search) the general kernel of a single-rank lane answers
+    // with vertex records for every rank the whole batch is ONE launch of k_front_batch: every cluster of its grid is a
+    // lane (pair tier, wide rounds, long rows) that takes every L-th query and delivers the 64-byte results straight
+    // into the pinned array; without records the general kernel of the single-rank lanes answers, one launch per query
     bool front = true;
     for (u32 r = 0; r < p->ctx[0]->d.nranks; ++r) front = front && p->ctx[0]->vrec_all[r] && p->ctx[0]->col_all[r];
     if (p->multi && !front) return fail("a pool on a partitioned graph needs every rank's vertex records (bibfs_pool_set_peer_graph)");
-    BIBFS_CUDA_TRY(cudaEventRecord(p->ev0, p->st[0]));
-    for (size_t i = 1; i < L; ++i) BIBFS_CUDA_TRY(cudaStreamWaitEvent(p->st[i], p->ev0, 0));
-    for (uint32_t q = 0; q < nq; ++q) {
-        const size_t lane = q % L;
-        bibfs_ctx* c = p->ctx[lane];
-        KParams K;
-        c->qn += 1;
-        fill_params(c, K, h_src[q], h_dst[q], false, BIBFS_F_NO_PATH);
-        if (front) {
-            K.lone = 1u; K.warm_lines = 0; K.async_peers = 0;
-            K.fuse_path = 1u; K.h_out = reinterpret_cast<u32*>(&p->h_res[q]); K.h_out_words = 0; K.h_seq = nullptr;
-            if (front_launch(K, p->multi, p->lane_cluster, p->st[lane])) return 1;
-        } else {
+    if (nq == 0) { if (ms) *ms = 0.f; return 0; }
+    if (front) {
+        cudaStream_t st = p->st[0];
+        if (p->lanes_dirty) {
+            for (size_t i = 0; i < L; ++i) {
+                KParams& K = p->h_lane_K[i];
+                fill_params(p->ctx[i], K, 0, 0, false, BIBFS_F_NO_PATH);
+                K.lone = 1u; K.warm_lines = 0; K.async_peers = 0;
+                K.fuse_path = 1u; K.h_out = nullptr; K.h_out_words = 0; K.h_seq = nullptr;
+            }
+            BIBFS_CUDA_TRY(cudaMemcpyAsync(p->d_lane_K, p->h_lane_K, L * sizeof(KParams), cudaMemcpyHostToDevice, st));
+            p->lanes_dirty = false;
+        }
+        for (uint32_t q = 0; q < nq; ++q) p->h_q[q] = (unsigned long long)h_src[q] | ((unsigned long long)h_dst[q] << 32);
+        p->h_q[nq] = 0ull;         // the counter the lanes draw their queries from
+        const u32 lanes = (u32)(nq < L ? nq : L);
+        // cluster per lane: the pool's size while every lane is resident at once, smaller (down to 2) when that buys residency
+        u32 cl = p->lane_cluster;
+        if (!getenv("BIBFS_POOL_CLUSTER")) while (cl > 2 && lanes * cl > (u32)p->sms) cl /= 2;
+        BIBFS_CUDA_TRY(cudaEventRecord(p->ev0, st));
+        BIBFS_CUDA_TRY(cudaMemcpyAsync(p->d_q, p->h_q, ((size_t)nq + 1) * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
+        if (front_batch_launch(p->d_lane_K, p->d_q, p->h_res, nq, lanes, p->multi, cl, st)) return 1;
+        BIBFS_CUDA_TRY(cudaEventRecord(p->ev1, st));
+    } else {
+        BIBFS_CUDA_TRY(cudaEventRecord(p->ev0, p->st[0]));
+        for (size_t i = 1; i < L; ++i) BIBFS_CUDA_TRY(cudaStreamWaitEvent(p->st[i], p->ev0, 0));
+        for (uint32_t q = 0; q < nq; ++q) {
+            const size_t lane = q % L;
+            bibfs_ctx* c = p->ctx[lane];
+            KParams K;
+            c->qn += 1;
+            fill_params(c, K, h_src[q], h_dst[q], false, BIBFS_F_NO_PATH);
             if (bfs_launch(K, false, p->st[lane])) return 1;
             BIBFS_CUDA_TRY(cudaMemcpyAsync(&p->h_res[q], c->arena_local[0] + offsetof(Ctrl, res), sizeof(Result), cudaMemcpyDeviceToHost, p->st[lane]));
         }
+        for (size_t i = 1; i < L; ++i) {
+            BIBFS_CUDA_TRY(cudaEventRecord(p->done[i], p->st[i]));
+            BIBFS_CUDA_TRY(cudaStreamWaitEvent(p->st[0], p->done[i], 0));
+        }
+        BIBFS_CUDA_TRY(cudaEventRecord(p->ev1, p->st[0]));
     }
-    for (size_t i = 1; i < L; ++i) {
-        BIBFS_CUDA_TRY(cudaEventRecord(p->done[i], p->st[i]));
-        BIBFS_CUDA_TRY(cudaStreamWaitEvent(p->st[0], p->done[i], 0));
-    }
-    BIBFS_CUDA_TRY(cudaEventRecord(p->ev1, p->st[0]));
     BIBFS_CUDA_TRY(cudaEventSynchronize(p->ev1));
     if (ms) BIBFS_CUDA_TRY(cudaEventElapsedTime(ms, p->ev0, p->ev1));
     int bad = 0;

@@ -356,6 +356,171 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
 }
 
 // ------------------------------------------------------------------------------------------
+// k_front_batch: MANY queries in one launch (the query pool of ctx.cu).
+//
+// 64 front kernels on 64 streams are bound by the launch rate (~5 us apiece: 0.32 ms of a 0.35 ms batch, measured).
+// Here every cluster of the grid is a LANE: it owns one search arena (lane_K[lane], uploaded once per pool), draws the
+// next query from a counter behind the query list (queries[nq], zero at launch; {src, dst} packed into 64 bits per
+// query) until the list is used up, and delivers each 64-byte result into h_res[q] (pinned host memory).  A lane runs the query the way a `lone` front kernel does: pair tier, wide rounds on
+// its own cluster, no peers; a search it cannot finish is reported as ST_ESCALATED and left to the caller.  Lanes never
+// talk to one another, so the grid may be larger than what is resident at once.
+// ------------------------------------------------------------------------------------------
+template <bool MULTI>
+__global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* __restrict__ lane_K, unsigned long long* queries,
+                                                                Result* h_res, const u32 nq) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ KParams sK;
+    __shared__ u32 s_query[3];
+    const u32 tid = threadIdx.x;
+    const u32 cl_n = ptx::cluster_nctarank(), cl_rank = ptx::cluster_ctarank();
+    constexpr u32 LANE_EXIT = 0xFFFFFFFFu;      // PairOut::go_wide value that sends the helpers home
+    const u32 lane_id = blockIdx.x / cl_n;
+    {
+        const u32* src = reinterpret_cast<const u32*>(lane_K + lane_id);
+        u32* dst = reinterpret_cast<u32*>(&sK);
+        for (u32 i = tid; i < sizeof(KParams) / 4; i += BFS_THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    const KParams& K = sK;
+    FrontSmem& fs = *reinterpret_cast<FrontSmem*>(smem_raw);
+    LevelState& st = fs.st;
+    Env E;
+    E.cta = 0; E.cpr = 1; E.me = 0; E.lo = 0;
+    E.P = K.P; E.B = K.B; E.n = K.n; E.nw = K.L.nw;
+    E.C = ctrl_of(K, 0);
+    E.A = &fs.acc; E.sA = &fs.acc;
+    E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = false; E.solo = true; E.tag = 0; E.smem_src = false;
+    E.stage = nullptr; E.stage_cnt = nullptr; E.cta_new = nullptr; E.cta_edges = nullptr; E.s_sent = nullptr; E.s_rnew = nullptr;
+    E.vis = vis_of(K, 0);
+    E.parent[0] = parent_of(K, 0, 0); E.parent[1] = parent_of(K, 0, 1);
+    E.q[0] = q_of(K, 0, 0); E.q[1] = q_of(K, 0, 1);
+    E.row_ptr = K.row_ptr[0];
+    E.col = K.col[0];
+    Ctrl* const C = E.C;
+    PairIO io;
+    if (MULTI) {
+        u32* lg = reinterpret_cast<u32*>(K.arena[0] + K.L.off_log);
+        u32* pa = reinterpret_cast<u32*>(K.arena[0] + K.L.off_pall);
+        const size_t nv = (size_t)K.B * K.P;
+        io.log[0] = lg; io.log[1] = lg + nv; io.par[0] = pa; io.par[1] = pa + nv;
+    } else {
+        io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
+    }
+    u64* const wide_stage = reinterpret_cast<u64*>(&fs.ps.fr[0][0][0][0]);
+    bool tier_ok = true;
+    if (MULTI) for (u32 p = 0; p < K.P; ++p) tier_ok = tier_ok && K.vrec[p] != nullptr;
+    else tier_ok = K.vrec[0] != nullptr;
+
+    auto push_out = [&]() {          // leader CTA: fs.ps.out into every helper's shared memory, then the barrier they wait at
+        if (tid < 16u * (cl_n - 1u)) {
+            const u32 c = 1u + tid / 16u, i = tid % 16u;
+            ptx::dsmem_st(ptx::dsmem_map(ptx::smem_addr(&fs.ps.out), c) + 4u * i, reinterpret_cast<const u32*>(&fs.ps.out)[i]);
+        }
+        ptx::cluster_sync_all();
+    };
+    while (true) {
+        if (cl_rank > 0) {
+            // helpers: the leader pushes its state into fs.ps.out before it arrives at this barrier
+            ptx::cluster_sync_all();
+            const u32 go = fs.ps.out.go_wide;
+            if (go == LANE_EXIT) break;
+            if (go) {
+                pair_wide<MULTI>(K, E, io, fs.ps.out, cl_n, cl_rank, wide_stage, WIDE_STAGE_CAP);
+                ptx::cluster_sync_all();        // nobody still reads its copy of the state when the leader pushes the next one
+            }
+            continue;
+        }
+        if (tid == 0) {
+            const u32 q = (u32)atomicAdd(queries + nq, 1ull);
+            s_query[2] = q;
+            if (q < nq) {
+                const u64 w = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(queries + q));
+                s_query[0] = (u32)w; s_query[1] = (u32)(w >> 32);
+                sK.h_out = reinterpret_cast<u32*>(h_res + q);
+            }
+        }
+        __syncthreads();
+        if (s_query[2] >= nq) {
+            if (cl_n > 1) {
+                if (tid == 0) fs.ps.out.go_wide = LANE_EXIT;
+                __syncthreads();
+                push_out();
+            }
+            break;
+        }
+        const u32 src = s_query[0], dst = s_query[1];
+        const bool bad = src >= K.n || dst >= K.n;
+        const bool tier = tier_ok && !bad && src != dst;
+        if (tid == 0) {
+            LevelState& G = st;
+            C->q_src = src; C->q_dst = dst;
+            C->trace_count = 0;
+            C->t_begin_ns = ptx::globaltimer_ns();
+            fs.acc.q_tail[0] = 1; fs.acc.q_tail[1] = 1; fs.acc.new_count = 0; fs.acc.meet_local = NO_V; fs.acc.edges = 0;
+            fs.fail = 0;
+            G.phase = PH_TD_SOLO; G.side = 0; G.levels = 0; G.levels_bu = 0;
+            G.depth[0] = G.depth[1] = 0; G.nf[0] = G.nf[1] = 1;
+            for (u32 s = 0; s < 2; ++s) {
+                G.q_lo[s] = 0; G.q_hi[s] = 1; G.fbm_cur[s] = 0; G.fbm_valid[s] = 0; G.rq_tag[s] = 0;
+                for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
+            }
+            G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 1; G.pad = 0; G.rounds_paired = 0; G.levels_grid = 0;
+            G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
+            G.edges_total = 0; G.visited_total = 2;
+            G.xepoch = C->xepoch;
+            if (bad) { G.status = 2; G.phase = PH_DONE; fs.acc.q_tail[0] = 0; fs.acc.q_tail[1] = 0; }
+            else if (src == dst) { G.length = 0; G.meet = src; G.phase = PH_DONE; G.visited_total = 1; fs.acc.q_tail[0] = 0; fs.acc.q_tail[1] = 0; }
+            else {
+                atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[src >> 5]), 1ull << (src & 31));
+                atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[dst >> 5]), 1ull << ((dst & 31) + 32));
+                io.log[0][0] = src; io.par[0][src] = NO_V;
+                io.log[1][0] = dst; io.par[1][dst] = NO_V;
+            }
+            if (G.phase == PH_DONE) write_result(K, C, G);
+            fs.ps.out.go_wide = 0;
+        }
+        __syncthreads();
+        bool wide = false;
+        if (tier) {
+            pair_run<MULTI, PT_CAP_FRONT>(K, E, fs.ps, io, src, dst, cl_n > 1);
+            wide = fs.ps.out.go_wide != 0;
+        }
+        if (cl_n > 1) {
+            // hand fs.ps.out to the helpers and release them
+            if (wide && tid == 0) {
+                Ctrl::Wide& W = C->wide;
+                for (u32 z = 0; z < 3; ++z) { W.cnt[z][0] = 0; W.cnt[z][1] = 0; W.flag[z] = 0; W.meet[z] = NO_V; W.tr_edges[z][0] = 0; W.tr_edges[z][1] = 0; }
+                W.meet_old[0] = NO_V; W.meet_old[1] = NO_V; W.edges = 0; W.long_packed[0] = 0; W.long_packed[1] = 0; W.long_packed[2] = 0;
+            }
+            __syncthreads();
+            push_out();
+        }
+        if (tier) {
+            u64 edges = fs.ps.edges;
+            if (wide) {
+                edges += pair_wide<MULTI>(K, E, io, fs.ps.out, cl_n, 0u, wide_stage, WIDE_STAGE_CAP);
+                ptx::cluster_sync_all();
+            }
+            if (tid == 0) pair_finish<MULTI>(K, E, st, fs.acc, fs.qvalid, fs.ps.out, edges);
+            __syncthreads();
+        }
+        // ---- undo the marks; result (or "not finished here") to the host
+        const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
+        for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
+        for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+        if (st.phase != PH_DONE && tid == 0) {
+            Result& R = C->res;
+            R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
+            R.depth_s = st.depth[0]; R.depth_t = st.depth[1]; R.levels_bu = 0; R.levels_grid = 0;
+            R.edges_scanned = st.edges_total; R.vertices_visited = st.visited_total; R.search_ns = 0; R.path_ns = 0;
+        }
+        __syncthreads();
+        result_to_host(K);
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // k_wait: a peer (rank > 0) in the one-process-per-GPU deployment; one warp
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(32) k_wait(const __grid_constant__ KParams K) {

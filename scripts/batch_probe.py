@@ -14,9 +14,14 @@ for a, c in zip(src[:4], dst[:4]): s.query(int(a), int(c), want_path=False)
 torch.cuda.synchronize(); t0 = time.perf_counter()
 seq = [s.query(int(a), int(c), want_path=False).length for a, c in zip(src, dst)]
 torch.cuda.synchronize(); t_seq = (time.perf_counter() - t0) * 1e3
-for lanes in (16, 32, 64):
-    b = bb.BatchSolver(g, lanes=lanes)
-    for _ in range(3): lens = b.query_batch(src, dst)
-    assert lens == seq, "pool and sequential answers differ"
-    print(f"  lanes={b.lanes}: 64 queries in {b.last_ms:.3f} ms (device, pool) vs {t_seq:.3f} ms one after the other (wall); found {sum(x is not None for x in lens)}")
-    b.close()
+import os
+for cl in ("", "2", "4"):
+    if cl: os.environ["BIBFS_POOL_CLUSTER"] = cl
+    else: os.environ.pop("BIBFS_POOL_CLUSTER", None)
+    for lanes in (24, 32, 37, 48, 64, 74):
+        b = bb.BatchSolver(g, lanes=lanes)
+        for _ in range(3): lens = b.query_batch(src, dst)
+        assert lens == seq, "pool and sequential answers differ"
+        t0 = time.perf_counter(); b.query_batch(src, dst); wall = (time.perf_counter() - t0) * 1e3
+        print(f"  cluster={cl or 'auto'} lanes={b.lanes}: 64 queries in {b.last_ms:.3f} ms (device, one launch), {wall:.3f} ms wall, vs {t_seq:.3f} ms one after the other (wall); found {sum(x is not None for x in lens)}")
+        b.close()

@@ -193,6 +193,23 @@ def test_batch_pool_many_queries_and_lanes(bb):
         b.close()
 
 
+def test_batch_pool_wide_rounds_back_to_back(bb, monkeypatch):
+    """Lanes of the one-launch batch kernel that go WIDE several queries in a row (grid: frontiers outgrow one CTA;
+    R-MAT: long rows dealt over the lane's cluster), for every cluster size a lane may have."""
+    for spec in (bb.grid_spec(700, 500), bb.rmat_spec(15, edgefactor=16, seed=2)):
+        g_cpu = bb.Graph.generate(spec)
+        oracle = bb.SerialSolver(g_cpu, policy=1)
+        rng = np.random.default_rng(5)
+        pairs = rng.integers(0, spec.n, size=(48, 2))
+        want = [oracle.query(int(s), int(t), want_path=False).length for s, t in pairs]
+        g = bb.Graph.generate(spec, device="cuda:0")
+        for cl, lanes in (("2", 3), ("4", 5), ("8", 2)):
+            monkeypatch.setenv("BIBFS_POOL_CLUSTER", cl)
+            b = bb.BatchSolver(g, lanes=lanes)
+            assert b.query_batch(pairs[:, 0], pairs[:, 1]) == want, (spec.kind, cl, lanes)
+            b.close()
+
+
 def test_naive_baseline_agrees(bb):
     spec = bb.er_spec(5000, 2.5 / 5000, seed=6)
     g_cpu = bb.Graph.generate(spec)
