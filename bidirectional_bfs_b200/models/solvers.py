@@ -207,14 +207,15 @@ class NaiveGpuSolver:
 class BatchSolver:
     """Many queries at once.
 
-    engine="concurrent" (default): a pool of `lanes` single-CTA search contexts on their own streams
-        (csrc/ctx.cu, bibfs_pool_*): independent latency-bound searches run side by side on the 148 SMs.
+    engine="concurrent" (default): ONE launch per batch whose thread-block clusters are `lanes` front kernels side by
+        side, each with its own search arena, drawing queries from a shared counter (csrc/front.cuh k_front_batch,
+        csrc/ctx.cu bibfs_pool_*): independent latency-bound searches overlap on the 148 SMs.
     engine="bitparallel": bit-parallel bidirectional MS-BFS, 64 queries per sweep (csrc/msbfs_dev.cu);
         pays off only when the searches are heavy and overlap, because every level sweeps all N vertices.
     """
     variant = "batch"
 
-    def __init__(self, graph: Graph, device=None, engine: str = "concurrent", lanes: int = 32, ctas_per_lane: int = 1):
+    def __init__(self, graph: Graph, device=None, engine: str = "concurrent", lanes: int = 64, ctas_per_lane: int = 1):
         if graph.device.type != "cuda" or graph.nranks != 1:
             graph = _as_single(graph, device or "cuda:0")
         self.graph = graph

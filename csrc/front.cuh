@@ -36,6 +36,10 @@ struct FrontSmem {
     u32 fail, pad;
     alignas(16) PairSmemT<PT_CAP_FRONT> ps;
 };
+// The kernel must stay within the 132 KB shared-memory configuration of the SM (dynamic + ~1 KB static + 1 KB reserved):
+// what shared memory does not take is L1, and with the 228 KB configuration (28 KB of L1 left) every round of the front
+// kernel was 15 % (narrow) to 45 % (wide, grid 4096 x 4096: 13.9 -> 20.3 ms) slower, measured; 164 KB and below are alike.
+static_assert(sizeof(FrontSmem) + 2048 <= 132 * 1024, "front kernel: shared memory beyond the 132 KB configuration");
 
 // leader warp: lane p waits until word `w` of rank 0 holds a value >= want
 __device__ bool wait_arrivals(const KParams& K, Ctrl* C, u64 want, u64 deadline) {
@@ -140,6 +144,59 @@ __device__ void front_handover(const KParams& K, const Env& E, FrontSmem& fs, co
         }
     }
     __syncthreads();
+}
+
+// Path of a search that ended inside the narrow rounds (whole CTA): both parent chains are walked in the shared-memory
+// log (a few cycles per hop), the path goes to the arena and, when it fits, with the result straight into the caller's
+// pinned buffer.  t0 / t1: log entries per side (<= PT_LOG_CAP); s_path: PT_CAP_FRONT words of scratch; s_idx: 2 words.
+__device__ __noinline__ void path_from_log(const KParams& K, const unsigned long long (*slog)[PT_LOG_CAP], const u32 t0, const u32 t1,
+                                           u32* s_path, u32* s_idx) {
+    Ctrl* C = ctrl_of(K, K.rank_lo);
+    Result& R = C->res;
+    u32* hdr = reinterpret_cast<u32*>(K.arena[K.rank_lo] + K.L.off_path);   // [copy of Result | path]
+    u32* path = hdr + PATH_HDR_WORDS;
+    const u32 tid = threadIdx.x;
+    const u64 tb = ptx::globaltimer_ns();
+    const u32 L = (u32)R.length, ds = R.depth_s, meet = R.meet;
+    const bool ok = L + 1u <= K.max_path;
+    for (u32 i = tid; i < t0; i += BFS_THREADS) if ((u32)slog[0][i] == meet) s_idx[0] = i;
+    for (u32 i = tid; i < t1; i += BFS_THREADS) if ((u32)slog[1][i] == meet) s_idx[1] = i;
+    __syncthreads();
+    if (ok && tid == 0) {
+        u32 idx = s_idx[0];
+        for (u32 pos = ds;; --pos) {
+            const unsigned long long e = slog[0][idx];
+            path[pos] = (u32)e;
+            if (pos < PT_CAP_FRONT) s_path[pos] = (u32)e;
+            if (pos == 0) break;
+            idx = (u32)(e >> 32);
+        }
+    } else if (ok && tid == 32) {
+        unsigned long long e = slog[1][s_idx[1]];
+        for (u32 pos = ds; pos < L; ++pos) {
+            e = slog[1][(u32)(e >> 32)];
+            path[pos + 1] = (u32)e;
+            if (pos + 1 < PT_CAP_FRONT) s_path[pos + 1] = (u32)e;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        R.path_len = ok ? L + 1u : 0u;
+        const u64 dt = ptx::globaltimer_ns() - tb;
+        R.path_ns = dt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)dt;
+    }
+    __syncthreads();
+    const u32 plen = ok ? L + 1u : 0u;
+    const u32 words = PATH_HDR_WORDS + ((K.h_out && plen <= K.h_out_words && plen <= PT_CAP_FRONT) ? plen : 0u);
+    for (u32 i = tid; i < words; i += BFS_THREADS) {
+        const u32 w = i < PATH_HDR_WORDS ? reinterpret_cast<const u32*>(&R)[i] : s_path[i - PATH_HDR_WORDS];
+        if (i < PATH_HDR_WORDS) hdr[i] = w;
+        if (K.h_out) { K.h_out[i] = w; __threadfence_system(); }
+    }
+    if (K.h_out && K.h_seq) {
+        __syncthreads();
+        if (tid == 0) *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq;
+    }
 }
 
 }  // namespace
@@ -273,7 +330,8 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
     }
     __syncthreads();
     KT_STAMP(2);
-    if (st.phase != PH_DONE && !fs.fail && tier) {
+    const bool ran_tier = st.phase != PH_DONE && !fs.fail && tier;
+    if (ran_tier) {
         KT_STAMP(3);
         pair_run<MULTI, PT_CAP_FRONT>(K, E, fs.ps, io, src, dst, cl_n > 1);
         u64 edges = fs.ps.edges;
@@ -298,12 +356,22 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
         // ---- the query ended here: verdict to the peers, path, result, cleanup
         if (MULTI && !K.lone && warp == 0 && !fs.fail) send_verdict(K, st, VK_DONE, qn, nullptr);
         KT_STAMP(5);
-        if (K.fuse_path == 2u) path_body_local(K, io.par[0], io.par[1]);
-        else if (K.fuse_path) result_to_host(K);
-        KT_STAMP(6);
         const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
-        for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
-        for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+        // a search that never left the narrow rounds has its whole log in shared memory: walk the path and clear the
+        // marks from there (no L2 round trip per hop / per entry)
+        const bool in_smem = ran_tier && !fs.ps.out.went_wide && t0 <= PT_LOG_CAP && t1 <= PT_LOG_CAP;
+        if (K.fuse_path == 2u) {
+            if (in_smem && st.status == 0 && st.length > 0) path_from_log(K, fs.ps.slog, t0, t1, &fs.ps.fv[0][0][0], fs.own);
+            else path_body_local(K, io.par[0], io.par[1]);
+        } else if (K.fuse_path) result_to_host(K);
+        KT_STAMP(6);
+        if (in_smem) {
+            for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[0][i] >> 5] = 0ull;
+            for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[1][i] >> 5] = 0ull;
+        } else {
+            for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
+            for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+        }
         KT_STAMP(7);
         return;
     }
@@ -504,10 +572,16 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
             if (tid == 0) pair_finish<MULTI>(K, E, st, fs.acc, fs.qvalid, fs.ps.out, edges);
             __syncthreads();
         }
-        // ---- undo the marks; result (or "not finished here") to the host
+        // ---- undo the marks (from the shared-memory log when the search never left the narrow rounds); result (or
+        // "not finished here") to the host
         const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
-        for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
-        for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+        if (tier && !fs.ps.out.went_wide && t0 <= PT_LOG_CAP && t1 <= PT_LOG_CAP) {
+            for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[0][i] >> 5] = 0ull;
+            for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[1][i] >> 5] = 0ull;
+        } else {
+            for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
+            for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+        }
         if (st.phase != PH_DONE && tid == 0) {
             Result& R = C->res;
             R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;

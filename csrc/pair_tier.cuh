@@ -50,7 +50,8 @@
 #endif
 
 constexpr u32 PT_CAP_SMALL = 512;    // frontier entries per side: inside the general kernel (shares its shared memory) ...
-constexpr u32 PT_CAP_FRONT = 1024;   // ... and in the front kernel (frontiers beyond the CTA's 512 threads are walked in passes)
+constexpr u32 PT_LOG_CAP = 1280;     // front kernel: (vertex, log index of its parent) pairs per side kept in shared memory for the path walk
+constexpr u32 PT_CAP_FRONT = 768;    // ... and in the front kernel (frontiers beyond the CTA's 512 threads are walked in passes)
 constexpr u32 PT_MAXDEG = 32;        // a discovered row at least this long ends the tier
 constexpr int PT_NB = 6;             // neighbours inlined in a vertex record
 constexpr int PT_W = 4;              // adjacency entries per lane per batch beyond the inlined ones
@@ -82,6 +83,11 @@ struct PairSmemT {
     PairOut out;                     // where the rounds stopped (pair_run / pair_wide -> pair_finish)
     alignas(16) u32 fv[2][2][CAP];               // frontier vertices [side][buffer]
     alignas(16) uint4 fr[2][2][CAP][2];          // ... and their records
+    // front kernel only: the first PT_LOG_CAP entries of each side's log, vertex | (log index of its parent) << 32.  A
+    // search that ends inside the narrow rounds walks its path and clears its marks from here instead of chasing
+    // par[] through L2 (a dependent load of a partially written sector per hop: ~550 ns each, measured)
+    static constexpr bool HAS_LOG = CAP == PT_CAP_FRONT;
+    alignas(16) unsigned long long slog[2][HAS_LOG ? PT_LOG_CAP : 1];
 };
 using PairSmem = PairSmemT<PT_CAP_SMALL>;
 
@@ -142,6 +148,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, PairSmemT<PT_CAP>
         const uint4* p = rec_of(v);
         const uint4 a = ld_rec_if(true, p), b = ld_rec_if(true, p + 1);
         ps.fv[tid][0][0] = v;
+        if (PairSmemT<PT_CAP>::HAS_LOG) ps.slog[tid][0] = (unsigned long long)v;
         ps.fr[tid][0][0][0] = a;
         ps.fr[tid][0][0][1] = b;
         ps.meet_old[tid] = a.x >= PT_MAXDEG ? 0u : NO_V;       // (borrowed until the first barrier: "seed row too long")
@@ -177,6 +184,8 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, PairSmemT<PT_CAP>
         const u32 sh = 32u * side, osh = 32u - sh;
         const u32 buf = side ? buf1 : buf0;
         const u32 base = side ? base1 : base0;
+        const unsigned long long plog = (unsigned long long)(base - (side ? n1 : n0) + idx) << 32;      // where u sits in the log
+        unsigned long long* const slog = ps.slog[side];
         u32 u = 0, deg = 0, r0 = 0;
         uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
         if (have) {
@@ -234,6 +243,7 @@ __device__ __noinline__ void pair_run(const KParams& K, Env E, PairSmemT<PT_CAP>
                     if ((newmask >> k) & 1u) {
                         qs[base + slot] = v[k];
                         pp[v[k]] = u;
+                        if (PairSmemT<PT_CAP>::HAS_LOG && base + slot < PT_LOG_CAP) slog[base + slot] = plog | v[k];
                         if (slot < PT_CAP) { out_v[slot] = v[k]; out_r[slot][0] = qa[k]; out_r[slot][1] = qb[k]; }
                         else fl |= PT_OVF;
                         if (qa[k].x >= PT_MAXDEG) fl |= PT_BIG;
