@@ -106,6 +106,8 @@ constexpr u32 BAR_WAYS = 16;
 enum : u32 { VD_KIND = 0, VD_LENGTH, VD_MEET, VD_D0, VD_D1, VD_LEVELS, VD_NF0, VD_NF1, VD_SENT0, VD_SENT1, VD_EDGES_LO, VD_EDGES_HI,
              VD_VIS_LO, VD_VIS_HI, VD_PAIRED, VD_STATUS, VD_WORDS };
 enum : u32 { VK_DONE = 1, VK_HANDOVER = 2 };
+constexpr u32 KF_HOST_SYNCS = 0x40000000u;   // KParams::flags (internal): the host waits for the STREAM before it reads the pinned result, so the
+                                             // kernel's writes to it need no fence of their own (a fence.sys is a PCIe round trip on the query's chain)
 constexpr i32 ST_ESCALATED = 100;    // Result::status of a front kernel that handed the search over (never reaches the caller)
 constexpr u32 PATH_HDR_WORDS = 16;   // sizeof(Result) / 4
 constexpr u32 HUB_CAP = 16384;          // hub entries per level per rank (overflow: expanded in place)

@@ -2040,7 +2040,7 @@ static __device__ __forceinline__ void path_body_impl(const KParams& K, const u3
     for (u32 i = threadIdx.x; i < words; i += blockDim.x) {
         const u32 w = i < PATH_HDR_WORDS ? reinterpret_cast<const u32*>(&R)[i] : __ldcg(hdr + i);
         if (i < PATH_HDR_WORDS) hdr[i] = w;
-        if (K.h_out) { K.h_out[i] = w; __threadfence_system(); }
+        if (K.h_out) { K.h_out[i] = w; if (!(K.flags & KF_HOST_SYNCS)) __threadfence_system(); }
     }
     if (K.h_out && K.h_seq) {
         __syncthreads();
@@ -2055,7 +2055,7 @@ __device__ __noinline__ void path_body_local(const KParams& K, const u32* par0, 
 __device__ __noinline__ void result_to_host(const KParams& K) {
     const Result& R = ctrl_of(K, K.rank_lo)->res;
     if (!K.h_out) return;
-    if (threadIdx.x < PATH_HDR_WORDS) { K.h_out[threadIdx.x] = reinterpret_cast<const u32*>(&R)[threadIdx.x]; __threadfence_system(); }
+    if (threadIdx.x < PATH_HDR_WORDS) { K.h_out[threadIdx.x] = reinterpret_cast<const u32*>(&R)[threadIdx.x]; if (!(K.flags & KF_HOST_SYNCS)) __threadfence_system(); }
     __syncthreads();
     if (threadIdx.x == 0 && K.h_seq) *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq;
 }

@@ -311,6 +311,7 @@ extern "C" int bibfs_ctx_query(bibfs_ctx* c, uint32_t src, uint32_t dst, const u
     K.h_query = h_query_pinned;          // read by the kernel itself: pinned memory is device-visible under UVA
     const bool want_path = !(flags & BIBFS_F_NO_PATH);
     c->last_lean = (flags & BIBFS_F_DEVICE_CLOCK) != 0;
+    if (!c->last_lean) K.flags |= KF_HOST_SYNCS;
     c->last_flags = flags;
     c->pend_src = src; c->pend_dst = dst; c->pend_flags = flags; c->pend_hq = h_query_pinned;
     if (!c->last_lean) BIBFS_CUDA_TRY(cudaEventRecord(c->ev[0], st));
@@ -349,6 +350,7 @@ extern "C" int bibfs_ctx_resume(bibfs_ctx* c, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     KParams K;
     fill_params(c, K, c->pend_src, c->pend_dst, false, c->pend_flags);
+    if (!c->last_lean) K.flags |= KF_HOST_SYNCS;
     c->stage = 0;
     return launch_general(c, K, !(c->pend_flags & BIBFS_F_NO_PATH), true, st);
 }

@@ -191,7 +191,7 @@ __device__ __noinline__ void path_from_log(const KParams& K, const unsigned long
     for (u32 i = tid; i < words; i += BFS_THREADS) {
         const u32 w = i < PATH_HDR_WORDS ? reinterpret_cast<const u32*>(&R)[i] : s_path[i - PATH_HDR_WORDS];
         if (i < PATH_HDR_WORDS) hdr[i] = w;
-        if (K.h_out) { K.h_out[i] = w; __threadfence_system(); }
+        if (K.h_out) { K.h_out[i] = w; if (!(K.flags & KF_HOST_SYNCS)) __threadfence_system(); }
     }
     if (K.h_out && K.h_seq) {
         __syncthreads();
@@ -622,7 +622,7 @@ __global__ void __launch_bounds__(32) k_wait(const __grid_constant__ KParams K) 
     }
     __syncwarp();
     if (K.h_out) {      // the verdict goes straight to the host's pinned buffer, then the completion word it may be polling
-        if (lane < PATH_HDR_WORDS) { K.h_out[lane] = reinterpret_cast<const u32*>(&C->res)[lane]; __threadfence_system(); }
+        if (lane < PATH_HDR_WORDS) { K.h_out[lane] = reinterpret_cast<const u32*>(&C->res)[lane]; if (!(K.flags & KF_HOST_SYNCS)) __threadfence_system(); }
         __syncwarp();
         if (lane == 0 && K.h_seq) *reinterpret_cast<volatile u32*>(K.h_seq) = K.seq;
     }
