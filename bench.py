@@ -211,6 +211,9 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
     wall0 = time.perf_counter()
     ms, ms_path, own_edges, lengths = np.zeros(K), np.zeros(K), np.zeros(K), []
     for i, (s, t, length, _, _) in enumerate(queries[W:W + K]):
+        if world > 1:
+            barrier()                                  # every rank starts the step together: a peer's events bracket its wait
+                                                       # kernel, which would otherwise also count rank 0's host work (path copy)
         if flush is not None:
             flush.fill_(i & 0xFF)                      # evict the graph from L2 between steps
         r = solver.query(s, t, want_path=True, timing="events")      # CUDA events on the launching stream

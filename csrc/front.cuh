@@ -146,6 +146,23 @@ __device__ void front_handover(const KParams& K, const Env& E, FrontSmem& fs, co
     __syncthreads();
 }
 
+// Undo the marks of a finished search: share `part` of `parts` (the CTAs of the cluster after wide rounds; 0 of 1: the
+// leader CTA alone).  A search that reached a sizeable part of the graph (a grid: millions of vertices) sweeps the visited
+// words instead of looking every logged vertex up: one CTA clearing 6 M entries one by one took 5 of the 13.6 ms of a
+// 4096 x 4096 grid query (measured: the peers' wait kernels saw the verdict that much earlier).
+__device__ __forceinline__ void clear_marks(const Env& E, const PairIO& io, const u32 t0, const u32 t1, const u32 part, const u32 parts) {
+    const u32 gt = part * BFS_THREADS + threadIdx.x, gn = parts * BFS_THREADS;
+    if ((u64)(t0 + t1) * 8ull >= (u64)E.nw) {
+        ulonglong2* p = reinterpret_cast<ulonglong2*>(E.vis);
+        const u32 n2 = E.nw / 2;
+        for (u32 i = gt; i < n2; i += gn) p[i] = make_ulonglong2(0ull, 0ull);
+        if ((E.nw & 1u) && gt == 0) E.vis[E.nw - 1] = 0ull;
+    } else {
+        for (u32 i = gt; i < t0; i += gn) E.vis[io.log[0][i] >> 5] = 0ull;
+        for (u32 i = gt; i < t1; i += gn) E.vis[io.log[1][i] >> 5] = 0ull;
+    }
+}
+
 // Path of a search that ended inside the narrow rounds (whole CTA): both parent chains are walked in the shared-memory
 // log (a few cycles per hop), the path goes to the arena and, when it fits, with the result straight into the caller's
 // pinned buffer.  t0 / t1: log entries per side (<= PT_LOG_CAP); s_path: PT_CAP_FRONT words of scratch; s_idx: 2 words.
@@ -259,7 +276,11 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
         // the other CTAs of the working cluster: wait until the leader CTA has decided whether its rounds go wide (it pushes
         // its state into this CTA's shared memory before it arrives at the barrier), take part if so, and leave
         ptx::cluster_sync_all();
-        if (fs.ps.out.go_wide) pair_wide<MULTI>(K, E, io, fs.ps.out, cl_n, cl_rank, reinterpret_cast<u64*>(&fs.ps.fr[0][0][0][0]), WIDE_STAGE_CAP);
+        if (fs.ps.out.go_wide) {
+            pair_wide<MULTI>(K, E, io, fs.ps.out, cl_n, cl_rank, reinterpret_cast<u64*>(&fs.ps.fr[0][0][0][0]), WIDE_STAGE_CAP);
+            // the search ended in the wide rounds (or the lane gives up): every CTA clears its share of the marks
+            if (fs.ps.out.length != -2 || K.lone) clear_marks(E, io, fs.ps.out.base[0], fs.ps.out.base[1], cl_rank, cl_n);
+        }
         return;
     }
     bool cl_pending = cl_n > 1;       // the helpers are waiting at the start-up barrier
@@ -369,8 +390,8 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
             for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[0][i] >> 5] = 0ull;
             for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[1][i] >> 5] = 0ull;
         } else {
-            for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
-            for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+            const bool shared = ran_tier && fs.ps.out.went_wide && fs.ps.out.length != -2;      // the helpers take part (see there)
+            clear_marks(E, io, t0, t1, 0u, shared ? cl_n : 1u);
         }
         KT_STAMP(7);
         return;
@@ -378,9 +399,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
     // ---- the search goes on in the general kernel
     if (K.lone) {
         // pool lane: nobody to hand over to.  Undo the marks, report "handed over"; the caller answers the query elsewhere
-        const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
-        for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
-        for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
+        clear_marks(E, io, fs.acc.q_tail[0], fs.acc.q_tail[1], 0u, (ran_tier && fs.ps.out.went_wide) ? cl_n : 1u);
         if (tid == 0) {
             Result& R = C->res;
             R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
@@ -494,7 +513,10 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
             if (go == LANE_EXIT) break;
             if (go) {
                 pair_wide<MULTI>(K, E, io, fs.ps.out, cl_n, cl_rank, wide_stage, WIDE_STAGE_CAP);
+                const u32 t0 = fs.ps.out.base[0], t1 = fs.ps.out.base[1];
                 ptx::cluster_sync_all();        // nobody still reads its copy of the state when the leader pushes the next one
+                clear_marks(E, io, t0, t1, cl_rank, cl_n);
+                ptx::cluster_sync_all();        // ... and no stale clear lands in the marks of the lane's next query
             }
             continue;
         }
@@ -578,10 +600,8 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
         if (tier && !fs.ps.out.went_wide && t0 <= PT_LOG_CAP && t1 <= PT_LOG_CAP) {
             for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[0][i] >> 5] = 0ull;
             for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[1][i] >> 5] = 0ull;
-        } else {
-            for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[io.log[0][i] >> 5] = 0ull;
-            for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[io.log[1][i] >> 5] = 0ull;
-        }
+        } else clear_marks(E, io, t0, t1, 0u, wide ? cl_n : 1u);
+        if (wide) ptx::cluster_sync_all();
         if (st.phase != PH_DONE && tid == 0) {
             Result& R = C->res;
             R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
