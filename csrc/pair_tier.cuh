@@ -69,6 +69,7 @@ struct PairOut {
     u32 pad[2];
 };
 static_assert(sizeof(PairOut) == 64, "pushed over DSMEM as 16 words");
+constexpr u32 PT_REC_ENTRIES = PT_NB + 2 * PT_W;      // neighbours held by a vertex record (both sectors): 14
 constexpr u32 PT_WIDE_MIN = 160;     // frontier positions of a round from which the whole cluster takes it
 constexpr u32 PT_WIDE_CAP = 1u << 16;  // ... and the frontier size per side at which even the cluster hands over
 
@@ -545,12 +546,18 @@ __device__ __noinline__ u64 pair_wide(const KParams& K, Env E, const PairIO io, 
                     batch(std::integral_constant<int, PT_W>{}, c, min(sdeg > (u32)PT_NB + PT_W ? sdeg - PT_NB - PT_W : 0u, (u32)PT_W), u, side);
                 }
             }
-            for (u32 e = PT_NB + 2 * PT_W; __any_sync(FULL, e < sdeg); e += PT_W) {
-                u32 c[PT_W];
-                const u32 left = sdeg > e ? sdeg - e : 0u;
+            // entries 15..31 live in col[] (another GPU's memory when rank 0 works alone on a partitioned graph): ALL of a
+            // lane's loads are issued before the first claim, so that the row costs one trip to col[] instead of five
+            if (__any_sync(FULL, sdeg > PT_REC_ENTRIES)) {
+                constexpr int TAIL = (int)(PT_MAXDEG - 1u - PT_REC_ENTRIES);       // 17
+                const u32 rem = sdeg > PT_REC_ENTRIES ? sdeg - PT_REC_ENTRIES : 0u;
+                const u32* const tp = g_col + r0 + PT_REC_ENTRIES;
+                u32 c[TAIL + 3] = {};
 #pragma unroll
-                for (int k = 0; k < PT_W; ++k) c[k] = ptx::ld_relaxed_gpu(g_col + r0 + ((u32)k < left ? e + k : 0u));
-                batch(std::integral_constant<int, PT_W>{}, c, min(left, (u32)PT_W), u, side);
+                for (int k = 0; k < TAIL; ++k) c[k] = ptx::ld_u32_gpu_if((u32)k < rem, tp + k);
+#pragma unroll
+                for (int j = 0; j < TAIL; j += PT_W)
+                    if (__any_sync(FULL, rem > (u32)j)) batch(std::integral_constant<int, PT_W>{}, c + j, min(rem > (u32)j ? rem - j : 0u, (u32)PT_W), u, side);
             }
             u32 big = __ballot_sync(FULL, lng);          // (only when the chunk list overflowed)
             while (big) {
@@ -581,16 +588,21 @@ __device__ __noinline__ u64 pair_wide(const KParams& K, Env E, const PairIO io, 
                 const HubChunk h = hub_lookup(H, ne, (const u32*)nullptr, c);
                 const u32 sd = h.nch_word >> 31;
                 const u32* const cc = (MULTI ? s_colb[owner(h.uu)] : e_col) + h.A;
-                for (u32 e = h.lo; e < h.hi; e += 32u * PT_W) {
-                    u32 cv[PT_W];
-                    u32 nact = 0;
+                // a chunk (256 entries) is fetched in ONE go: 8 loads per lane in flight, then the claims
+                for (u32 e = h.lo; e < h.hi; e += 64u * PT_W) {
+                    u32 cv[2 * PT_W];
 #pragma unroll
-                    for (int k = 0; k < PT_W; ++k) {
+                    for (int k = 0; k < 2 * PT_W; ++k) {
                         const u32 i = e + 32u * k + lane;
-                        cv[k] = ptx::ld_relaxed_gpu(cc + (i < h.hi ? i : h.lo));
-                        nact += i < h.hi ? 1u : 0u;
+                        cv[k] = ptx::ld_u32_gpu_if(i < h.hi, cc + i);
                     }
-                    batch(std::integral_constant<int, PT_W>{}, cv, nact, h.uu, sd);
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        u32 nact = 0;
+#pragma unroll
+                        for (int k = 0; k < PT_W; ++k) nact += e + 32u * (PT_W * j + k) + lane < h.hi ? 1u : 0u;
+                        if (__any_sync(FULL, nact != 0)) batch(std::integral_constant<int, PT_W>{}, cv + PT_W * j, nact, h.uu, sd);
+                    }
                 }
             }
         }

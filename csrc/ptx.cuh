@@ -95,6 +95,18 @@ __device__ __forceinline__ uint4 ld_v4_gpu_if(bool on, const uint4* p) {
         : "memory");
     return r;
 }
+__device__ __forceinline__ u32 ld_u32_gpu_if(bool on, const u32* p) {
+    u32 r;
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.u32 q, %2, 0;\n\t"
+        "mov.u32 %0, 0;\n\t"
+        "@q ld.relaxed.gpu.global.u32 %0, [%1];\n\t}"
+        : "=&r"(r)
+        : "l"(p), "r"((u32)on)
+        : "memory");
+    return r;
+}
 __device__ __forceinline__ u32 ld_relaxed_sys(const u32* p) {
     u32 v;
     asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
