@@ -150,6 +150,29 @@ def emit(obj):
 # --------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------
+def timed_build(bb, spec, dev, world, rank):
+    """Partitioned CSR + vertex records of this rank's shard on its GPU; seconds = max over ranks, barrier on both sides."""
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    if world == 1:
+        g = bb.Graph.generate(spec, device=dev)
+        g.single().vertex_records()
+    else:
+        g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
+        g.shards[rank].vertex_records()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    return g, dt
+
+
 def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do_e2e=True):
     """Build `config` on the GPUs, run W + K queries, return the measurement dict (rank 0) or None."""
     info = [None]
@@ -160,15 +183,11 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
     info = info[0]
     spec = make_spec(bb, config, seed)
     n = int(spec.n)
+    g, build_s = timed_build(bb, spec, dev, world, rank)
     t0 = time.time()
-    if world == 1:
-        g = bb.Graph.generate(spec, device=dev)
-        solver = bb.GpuSolver(g)
-    else:
-        g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
-        solver = comm.DistributedSolver(g)
+    solver = bb.GpuSolver(g) if world == 1 else comm.DistributedSolver(g)
     torch.cuda.synchronize()
-    build_s = time.time() - t0
+    setup_s = time.time() - t0
     nnz = g.nnz
     if world > 1:
         t = torch.tensor([nnz], dtype=torch.int64, device=dev)
@@ -264,7 +283,7 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
         "gteps": float(num.sum() / (total_ms * 1e-3) / 1e9) if total_ms > 0 else 0.0,
         "ms_per_step": total_ms / K, "ms": ms, "ms_path": ms_path, "lengths": lengths,
         "own_gteps": float(own_edges.sum() / (total_ms * 1e-3) / 1e9) if total_ms > 0 else 0.0,
-        "num_sum": float(num.sum()), "e2e_s": e2e_s, "d2h": d2h, "launches": int(launches), "build_s": build_s,
+        "num_sum": float(num.sum()), "e2e_s": e2e_s, "d2h": d2h, "launches": int(launches), "build_s": build_s, "setup_s": setup_s,
         "wall_dev_loop": wall_dev_loop, "l2": "256 MB write between steps" if flush is not None else "inputs larger than L2",
         "levels_mean": float(np.mean([q[4] for q in queries[W:W + K]])),
     }
@@ -277,18 +296,17 @@ def measure_batch(bb, comm, dist, torch, dev, rank, world, config, seed, nq=64):
     one-query-at-a-time path."""
     spec = make_spec(bb, config[:-8] if config.endswith("_batch64") else config, seed)
     n = int(spec.n)
+    g, build_s = timed_build(bb, spec, dev, world, rank)
     t0 = time.time()
     if world == 1:
-        g = bb.Graph.generate(spec, device=dev)
         single = bb.GpuSolver(g)
         pool = bb.BatchSolver(g, lanes=64)
         run = lambda a, b: pool.query_batch(a, b)
     else:
-        g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
         single = comm.DistributedSolver(g)
         run = lambda a, b: single.query_batch(a, b, lanes=64)
     torch.cuda.synchronize()
-    build_s = time.time() - t0
+    setup_s = time.time() - t0
     rng = np.random.default_rng(seed + 64)
     src = rng.integers(0, n, nq); dst = rng.integers(0, n, nq)
 
@@ -331,7 +349,7 @@ def measure_batch(bb, comm, dist, torch, dev, rank, world, config, seed, nq=64):
     return {"model": f"{nq} random queries at once on {spec_string(config[:-8] if config.endswith('_batch64') else config, seed)[1]}",
             "n": n, "directed_edges": nnz, "queries": nq, "found": sum(x is not None for x in lens),
             "batch_ms_wall": t_batch * 1e3, "pool_ms_device": pool_ms, "one_at_a_time_ms_wall": t_seq * 1e3,
-            "queries_per_s": nq / t_batch, "graph_build_s": build_s,
+            "queries_per_s": nq / t_batch, "graph_build_s": build_s, "solver_setup_s": setup_s,
             "what": "wall clock of the whole batch through the public API (barrier + synchronize on both sides, max over ranks, best of 3); "
                     "pool_ms_device = CUDA events around the pooled launches on rank 0"}
 
@@ -381,7 +399,7 @@ def run_ours(args):
                            "own_edges_gteps": o["own_gteps"], "levels_mean": o["levels_mean"],
                            "path_length": {"min": int(min(o["lengths"])), "max": int(max(o["lengths"]))},
                            "us_per_level": 1e3 * o["ms_per_step"] / max(1.0, o["levels_mean"]), "l2": o["l2"],
-                           "graph_build_s": o["build_s"], "wall_s": time.time() - t0}
+                           "graph_build_s": o["build_s"], "solver_setup_s": o["setup_s"], "wall_s": time.time() - t0}
 
     if rank == 0:
         ms_per_step = m["ms_per_step"]
@@ -415,7 +433,7 @@ def run_ours(args):
                     "d2h_bytes_per_step": m["d2h"] / K,
                     "what": "solver.query(): (src,dst) in pinned host memory read by the kernel -> search + path walk in one launch -> [result | path] written to pinned host memory and read by the caller, wall clock"},
             "gpu_launches": m["launches"], "launches_per_step": m["launches"] / K,
-            "graph_build_s": m["build_s"], "wall_s_device_loop": m["wall_dev_loop"],
+            "graph_build_s": m["build_s"], "solver_setup_s": m["setup_s"], "wall_s_device_loop": m["wall_dev_loop"],
             "other_configs": others,
         })
     if world > 1:

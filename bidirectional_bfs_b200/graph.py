@@ -69,7 +69,7 @@ class Graph:
         part = Partition(n, nranks)
         g = Graph(n=n, nranks=nranks, device=dev, spec=spec, name=name)
         hosted = list(range(nranks)) if ranks is None else list(ranks)
-        if _sharded_build_applies(dev, nranks, hosted) and (spec is not None or edges is None):
+        if (spec is not None or edges is None) and _sharded_build_applies(dev, nranks, hosted, from_generator=True):
             # one process per GPU: each rank walks 1/P of the generator's chunks and routes the half-edges to their owners
             from .parallel.build import build_shard
             (r,) = hosted
@@ -196,12 +196,19 @@ class Graph:
         return g
 
 
-def _sharded_build_applies(dev: torch.device, nranks: int, hosted: list) -> bool:
+def _sharded_build_applies(dev: torch.device, nranks: int, hosted: list, from_generator: bool = False) -> bool:
     """The routed, sharded construction (parallel/build.py) is used when this process is one rank of a torch.distributed
-    group of `nranks` processes and builds exactly its own shard on a GPU (BIBFS_SHARDED_BUILD=0 turns it off)."""
+    group of `nranks` processes and builds exactly its own shard on a GPU.  Edge lists that exist only once (a .bin file)
+    are always routed.  A GENERATOR can also be replayed by every rank (each keeps the rows it owns): the Philox stream
+    costs ALU time only, the routed build costs two remote atomics and a remote store per half-edge — measured on
+    Kronecker scale 26 over 4 GPUs: 0.060 s replayed, 0.12 s routed — so up to 8 ranks a generator is replayed, beyond
+    that (1/P of the stream per rank vs all of it) routed.  BIBFS_SHARDED_BUILD=0 / 1 forces never / always."""
     import os
     import torch.distributed as dist
-    if dev.type != "cuda" or nranks < 2 or len(hosted) != 1 or os.environ.get("BIBFS_SHARDED_BUILD") == "0":
+    mode = os.environ.get("BIBFS_SHARDED_BUILD")
+    if dev.type != "cuda" or nranks < 2 or len(hosted) != 1 or mode == "0":
+        return False
+    if from_generator and mode != "1" and nranks <= 8:
         return False
     return dist.is_available() and dist.is_initialized() and dist.get_world_size() == nranks and dist.get_rank() == hosted[0]
 

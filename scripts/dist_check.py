@@ -13,7 +13,12 @@ torch.cuda.set_device(dev)
 ok = True
 for name, spec in (("er", bb.er_spec(30000, 2.2 / 30000, seed=1)), ("rmat", bb.rmat_spec(15, edgefactor=16, seed=3)),
                    ("grid", bb.grid_spec(150, 100)), ("er_dense", bb.er_spec(5000, 10.0 / 5000, seed=2))):
-    g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])     # sharded, routed construction (parallel/build.py)
+    # two ways to a shard: routed (every rank walks 1/P of the generator and sends half-edges to their owners,
+    # parallel/build.py) and replayed (every rank walks the whole stream and keeps its rows: the default up to 8 ranks)
+    import os
+    if name in ("er", "rmat"): os.environ["BIBFS_SHARDED_BUILD"] = "1"
+    else: os.environ.pop("BIBFS_SHARDED_BUILD", None)
+    g = bb.Graph.generate(spec, device=dev, nranks=world, ranks=[rank])
     g_host = bb.Graph.generate(spec)
     # this rank's shard against the host builder, row by row (the order inside a row is not fixed: compare sorted)
     sh = g.shards[rank]
@@ -27,7 +32,7 @@ for name, spec in (("er", bb.er_spec(30000, 2.2 / 30000, seed=1)), ("rmat", bb.r
         same = np.array_equal(np.sort(key_h | seg_h), np.sort(key_d | col_d))
     if not same:
         ok = False
-        print(f"[rank {rank}] SHARD MISMATCH {name}: the routed build differs from the host builder", flush=True)
+        print(f"[rank {rank}] SHARD MISMATCH {name}: the device build differs from the host builder", flush=True)
     if name == "er":
         # the same graph from a .bin file: every rank reads and uploads only its M/P slice of the records
         import os, tempfile
