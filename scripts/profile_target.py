@@ -1,5 +1,8 @@
 """Short workload for Nsight Compute: every kernel family of the library, a handful of launches each.
-   python scripts/profile_target.py [search|build|all] [scale]
+   python scripts/profile_target.py [search|build|all|final] [scale]
+final:  one or two launches each of the kernels of the final tree, picked without probing queries on the GPU (ncu -c counts
+        every launch): k_front<false> single CTA (ER 100k) and as a cluster (R-MAT, grid), k_front<true> + k_bibfs<true>
+        (4 virtual ranks), k_front_batch (one launch for 24 queries).
 search: k_front<false/true> (pair tier, wide rounds, long rows), k_bibfs<false/true> (general kernel, fused multi-rank
         levels with 4 virtual ranks), the query pool;  build: generators, CSR builder, scans, row sort, vertex records,
         bit-parallel batch kernel, reference-style level-synchronous baseline."""
@@ -50,3 +53,36 @@ if what in ("search", "all"):
     b = bb.BatchSolver(g, lanes=8)
     b.query_batch([p[0] for p in pairs] * 3, [p[1] for p in pairs] * 3); print("pool ms", b.last_ms)    # lanes of k_front
     b.close()
+
+if what == "final":
+    host = bb.Graph.generate(spec)
+    oracle = bb.SerialSolver(host, policy=1)
+    rng = np.random.default_rng(3)
+    pairs = []
+    while len(pairs) < 24:
+        a, c = int(rng.integers(spec.n)), int(rng.integers(spec.n))
+        if (oracle.query(a, c, want_path=False).length or 0) >= 3:
+            pairs.append((a, c))
+    eg = bb.Graph.generate(bb.preset_spec("100k", seed=1), device="cuda:0")
+    se = bb.GpuSolver(eg)
+    for q in ((0, 99999), (17, 4242)):
+        r = se.query(*q); print("er100k front (single CTA + warm-up CTAs)", r.length, r.levels_paired)       # k_front<false>
+    se.close()
+    m = bb.MultiGpuSolver(bb.Graph.generate(spec, device="cuda:0", nranks=4))
+    r = m.query(*pairs[0]); print("front, 4 virtual ranks", r.length, r.levels_paired)                        # k_front<true>
+    for a, c in pairs[:2]:
+        r = m.query(a, c, flags=F_NO_FRONT); print("fused levels, 4 virtual ranks", r.length, r.levels)        # k_bibfs<true>
+    m.close()
+    g = bb.Graph.generate(spec, device="cuda:0")
+    b = bb.BatchSolver(g, lanes=8)
+    b.query_batch([p[0] for p in pairs], [p[1] for p in pairs]); print("batch of 24, one launch, ms", b.last_ms)   # k_front_batch
+    b.close()
+    s = bb.GpuSolver(g)
+    for a, c in pairs[:3]:
+        r = s.query(a, c); print("front", a, c, r.length, r.levels, r.levels_paired)                          # k_front<false>, cluster from the 2nd on
+    s.close()
+    gr = bb.Graph.generate(bb.grid_spec(512, 512), device="cuda:0")
+    sg = bb.GpuSolver(gr)
+    for q in ((0, 512 * 512 - 1), (5, 512 * 300)):
+        r = sg.query(*q); print("grid front (wide rounds)", r.length, r.levels_paired)
+    sg.close()
