@@ -20,7 +20,10 @@ work is never rewarded and the GTEPS ratio of two implementations equals their t
 Timing (ours): W warm-up queries, then K queries, each device-timed with CUDA events around the
 search on the launching stream, max over ranks per step; L2 is flushed (256 MB write) between
 steps when the graph fits in L2.  "e2e" repeats the K queries through the public API with the
-query read from pinned host memory and the result + path copied back, wall clock.
+query read from pinned host memory and the result + path copied back, wall clock per step with the
+same L2 flush before every step: on one GPU through the resident solver (a front kernel that stays
+on the GPU and polls a pinned mailbox; the launch-per-query path is reported beside it), on several
+GPUs through DistributedSolver.query.
 """
 from __future__ import annotations
 
@@ -253,18 +256,57 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
         ms = tms.cpu().numpy()
 
     e2e_s, d2h = None, 0
+    e2e_one_launch_s, e2e_what = None, ""
     if do_e2e:
         pinned = torch.empty(2, dtype=torch.int32).pin_memory()
         pinned_np = pinned.numpy()            # same memory; numpy item stores cost ~0.1 us, torch ones ~10 us
-        barrier()
-        e0 = time.perf_counter()
-        for s, t, length, _, _ in queries[W:W + K]:
+        side = torch.cuda.Stream(device=dev)
+
+        def e2e_loop(fn, count_bytes):
+            """K queries through a public call; every step: L2 flush (outside the timed region, waited for on its own stream
+            - never a device-wide synchronisation, a resident kernel would hold it up), then wall clock around
+            [query into pinned memory -> call -> result + path back in host memory]."""
+            nonlocal d2h
+            total = 0.0
+            for i, (s, t, length, _, _) in enumerate(queries[W:W + K]):
+                if world > 1:
+                    dist.barrier()
+                if flush is not None:
+                    with torch.cuda.stream(side):
+                        flush.fill_(i & 0xFF)
+                    side.synchronize()
+                t0 = time.perf_counter()
+                r = fn(s, t)
+                total += time.perf_counter() - t0
+                assert r.length == length
+                if count_bytes:
+                    d2h += 64 + 4 * (length + 1)
+            return total
+
+        def one_launch(s, t):
             pinned_np[0], pinned_np[1] = s, t
-            r = solver.query(-1 & 0x7FFFFFFF, -1 & 0x7FFFFFFF, want_path=True, pinned_query=pinned, timing="device")
-            assert r.length == length
-            d2h += 64 + 4 * (length + 1)
+            return solver.query(-1 & 0x7FFFFFFF, -1 & 0x7FFFFFFF, want_path=True, pinned_query=pinned, timing="device")
+
         barrier()
-        e2e_s = time.perf_counter() - e0
+        if world == 1:
+            # one GPU: the resident solver (a front kernel that stays on the GPU and is fed through a pinned mailbox);
+            # the launch-per-query path is reported next to it
+            e2e_one_launch_s = e2e_loop(one_launch, False)
+            torch.cuda.synchronize()
+            resident = bb.ResidentSolver(g, cluster=1, idle_ms=200)
+            for s, t, _, _, _ in queries[:W]:
+                resident.query(s, t)
+            e2e_s = e2e_loop(lambda s, t: resident.query(s, t, want_path=True), True)
+            resident_launches = resident.launches
+            resident.close()
+            e2e_what = ("ResidentSolver.query(): (src,dst) written into a pinned mailbox that a resident front kernel polls -> search + path walk -> "
+                        "[result | path] written to pinned host memory and read by the caller; wall clock per step, L2 flushed before every step; "
+                        f"kernel launches during the K steps: {resident_launches - 1}")
+        else:
+            e2e_s = e2e_loop(one_launch, True)
+            e2e_what = ("solver.query(): (src,dst) in pinned host memory read by the kernel -> search + path walk in one launch -> [result | path] "
+                        "written to pinned host memory and read by the caller; wall clock per step (max over ranks of the sums), L2 flushed before every step")
+        barrier()
         for _ in range(3000):                 # keep the GPU in the same state long enough for nvidia-smi to sample it under load
             solver.query(queries[W][0], queries[W][1], want_path=False)      # (a fixed count: every rank must issue the same queries)
         if world > 1:
@@ -283,7 +325,7 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
         "gteps": float(num.sum() / (total_ms * 1e-3) / 1e9) if total_ms > 0 else 0.0,
         "ms_per_step": total_ms / K, "ms": ms, "ms_path": ms_path, "lengths": lengths,
         "own_gteps": float(own_edges.sum() / (total_ms * 1e-3) / 1e9) if total_ms > 0 else 0.0,
-        "num_sum": float(num.sum()), "e2e_s": e2e_s, "d2h": d2h, "launches": int(launches), "build_s": build_s, "setup_s": setup_s,
+        "num_sum": float(num.sum()), "e2e_s": e2e_s, "e2e_one_launch_s": e2e_one_launch_s, "e2e_what": e2e_what, "d2h": d2h, "launches": int(launches), "build_s": build_s, "setup_s": setup_s,
         "wall_dev_loop": wall_dev_loop, "l2": "256 MB write between steps" if flush is not None else "inputs larger than L2",
         "levels_mean": float(np.mean([q[4] for q in queries[W:W + K]])),
     }
@@ -431,7 +473,8 @@ def run_ours(args):
             "clocks": {"sm_mhz": clocks["sm_mhz"], "sm_max_mhz": clocks["sm_max_mhz"], "reasons": clocks["reasons"], "samples": clocks["samples"]},
             "e2e": {"value": e2e_gteps, "unit": UNIT, "ms_per_step": m["e2e_s"] * 1e3 / K, "h2d_bytes_per_step": 8,
                     "d2h_bytes_per_step": m["d2h"] / K,
-                    "what": "solver.query(): (src,dst) in pinned host memory read by the kernel -> search + path walk in one launch -> [result | path] written to pinned host memory and read by the caller, wall clock"},
+                    "what": m["e2e_what"],
+                    "one_launch_per_query_ms_per_step": (m["e2e_one_launch_s"] * 1e3 / K) if m["e2e_one_launch_s"] is not None else None},
             "gpu_launches": m["launches"], "launches_per_step": m["launches"] / K,
             "graph_build_s": m["build_s"], "solver_setup_s": m["setup_s"], "wall_s_device_loop": m["wall_dev_loop"],
             "other_configs": others,

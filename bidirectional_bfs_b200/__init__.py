@@ -9,7 +9,7 @@ from .graph import Graph, Shard  # noqa: F401
 from .ops.gen import er_spec, grid_spec, preset_spec, rmat_spec, generate_edges  # noqa: F401
 from .ops.search import PathResult, SearchContext  # noqa: F401
 from .models import (BatchSolver, CpuRanksSolver, GpuSolver, MultiGpuSolver, NaiveGpuSolver,  # noqa: F401
-                     SerialSolver, make_solver)
+                     ResidentSolver, SerialSolver, make_solver)
 from .api import bibfs, bibfs_batch  # noqa: F401
 from .utils.validate import validate_path  # noqa: F401
 from . import io  # noqa: F401

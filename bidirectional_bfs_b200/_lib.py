@@ -133,6 +133,10 @@ def _declare(lib):
         "bibfs_pool_query": (C.c_int, [vp, vp, vp, u32, vp, vp, vp, vp, P(C.c_float)]),
         "bibfs_pool_destroy": (C.c_int, [vp]),
         "bibfs_pool_set_peer_graph": (C.c_int, [vp, u32, vp, vp]),
+        "bibfs_resident_start": (C.c_int, [P(vp), P(CtxDesc), u32, u32]),
+        "bibfs_resident_query": (C.c_int, [vp, u32, u32, u32, P(Result), vp, u32]),
+        "bibfs_resident_launches": (C.c_int, [vp, P(C.c_uint64)]),
+        "bibfs_resident_stop": (C.c_int, [vp]),
         "bibfs_naive_levelsync_device": (C.c_int, [u32, vp, vp, u32, u32, P(i32), P(C.c_float), vp]),
     }
     for name, (res, args) in sig.items():

@@ -4,8 +4,9 @@
   cpu-ranks   CpuRanksSolver   v2 equivalent       (v2/second_try.cpp)
   gpu         GpuSolver        v3 replacement      (v3/bibfs_cuda_only.cu)
   multi-gpu   MultiGpuSolver   v4 replacement      (v4/mpi_bas.cpp + v4/comp.cu)
-  batch       BatchSolver      64 queries per pass (no counterpart in the reference)
+  gpu-resident ResidentSolver  one resident kernel fed through a pinned mailbox: no launch per query (no counterpart)
+  batch       BatchSolver      many queries in one launch (no counterpart in the reference)
   naive-gpu   NaiveGpuSolver   reference-style level-synchronous baseline, for comparisons only
 """
 from .solvers import (BatchSolver, CpuRanksSolver, GpuSolver, MultiGpuSolver, NaiveGpuSolver,  # noqa: F401
-                      SerialSolver, make_solver, VARIANTS)
+                      ResidentSolver, SerialSolver, make_solver, VARIANTS)

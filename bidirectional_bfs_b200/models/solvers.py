@@ -107,6 +107,71 @@ class GpuSolver:
         self.ctx.close()
 
 
+class ResidentSolver:
+    """Single GPU, NO launch per query: one front kernel stays on the GPU (``cluster`` SMs: 1, 2, 4, 8 or 16) and takes its
+    queries from a mailbox in pinned host memory (csrc/front.cuh k_front_batch in resident mode, csrc/ctx.cu
+    bibfs_resident_*).  ``query`` writes {src, dst} into the mailbox, the kernel runs the search and the path walk and
+    writes [result | path] back, the call returns when the completion word arrives: the search plus three PCIe trips
+    instead of a launch and a teardown.  The kernel leaves by itself after ``idle_ms`` without a query (the next query
+    launches it again), so a device-wide synchronisation elsewhere in the process waits at most that long; ``close()``
+    sends it home at once.  Searches beyond the front kernel are answered by the general kernel (the resident kernel is
+    sent home first).  The reference starts a process per query (benchmark_test.sh:47-54)."""
+    variant = "gpu-resident"
+
+    def __init__(self, graph: Graph, device=None, cluster: int = 1, idle_ms: int = 50, max_path: int = 0, watchdog_ms: int = 0):
+        if graph.device.type != "cuda" or graph.nranks != 1:
+            dev = device or (graph.device if graph.device.type == "cuda" else "cuda:0")
+            graph = _as_single(graph, dev)
+        self.graph = graph
+        from .._lib import CtxDesc
+        s = graph.single()
+        vr = s.vertex_records()
+        if vr is None:
+            raise ValueError("the resident solver needs vertex records (graph without vertices?)")
+        d = CtxDesc()
+        d.n, d.nranks, d.rank_lo, d.vranks = graph.n, 1, 0, 1
+        d.d_row_ptr[0] = s.row_ptr.data_ptr()
+        d.d_col[0] = s.col.data_ptr() if s.col.numel() else s.row_ptr.data_ptr()
+        d.d_vrec[0] = vr.data_ptr()
+        d.max_degree = s.max_degree
+        d.max_path = max_path or min(graph.n + 1, 1 << 24)
+        d.watchdog_ms = watchdog_ms
+        self.max_path = d.max_path
+        self._desc = d
+        self._path = np.empty(self.max_path, dtype=np.uint32)
+        self._path_ptr = self._path.ctypes.data
+        self._res = Result()
+        self._res_ref = C.byref(self._res)
+        self._h = C.c_void_p()
+        with torch.cuda.device(graph.device):
+            check(lib().bibfs_resident_start(C.byref(self._h), C.byref(d), cluster, idle_ms))
+        self._fn = lib().bibfs_resident_query
+
+    def query(self, src, dst, want_path=True) -> PathResult:
+        if self._fn(self._h, int(src), int(dst), 0 if want_path else F_NO_PATH, self._res_ref,
+                    self._path_ptr if want_path else None, self.max_path if want_path else 0):
+            check(1)
+        return result_from_c(src, dst, self._res, self._path, self.variant)
+
+    @property
+    def launches(self) -> int:
+        """How often the kernel had to be (re)launched so far (1 under a steady stream of queries)."""
+        n = C.c_uint64(0)
+        check(lib().bibfs_resident_launches(self._h, C.byref(n)))
+        return int(n.value)
+
+    def close(self):
+        if self._h:
+            h, self._h = self._h, C.c_void_p()
+            check(lib().bibfs_resident_stop(h))
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class MultiGpuSolver:
     """P ranks over 1-D partitioned shards.
 

@@ -208,6 +208,20 @@ struct KParams {
     u32 warm_lines;                // > 0: the graph is small enough for L2 — idle CTAs prefetch this many 128-byte lines of vrec at query start
 };
 
+// Mailbox of a resident front kernel (pinned host memory, mapped into the device's address space).
+struct alignas(64) Mailbox {
+    // host -> device: one 16-byte word group, `seq` written last (x86 stores stay in order; the device reads all 16 bytes
+    // with one load)
+    u32 src, dst, seq, op;                 // op: MB_QUERY | flags, or MB_EXIT
+    u32 pad0[12];
+    // device -> host
+    alignas(64) u32 alive;                 // 1 while the kernel polls; 0 once it has left (idle or told to)
+    u32 out_seq;                           // == seq of the query whose [result | path] is complete in `out`
+    u32 pad1[14];
+    alignas(64) u32 out[PATH_HDR_WORDS + 240];
+};
+constexpr u32 MB_EXIT = 0x80000000u;
+
 // implemented in bfs_dev.cu
 int bfs_max_ctas_per_device(bool multi, int* out);
 int bfs_max_ctas_clustered(u32 cluster, int* out);
@@ -217,6 +231,7 @@ int front_launch(const KParams& K, bool multi, u32 cluster, cudaStream_t st);
 int wait_launch(const KParams& K, cudaStream_t st);
 int front_batch_prepare(bool multi);
 int front_batch_launch(const KParams* d_lane_K, unsigned long long* d_queries, Result* h_res, u32 nq, u32 lanes, bool multi, u32 cluster, cudaStream_t st);
+int front_resident_launch(const KParams* d_lane_K, Mailbox* mb, u32 start_seq, u32 idle_us, u32 cluster, cudaStream_t st);
 int front_prepare(bool multi, u32* cluster_out);
 #endif
 

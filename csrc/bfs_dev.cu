@@ -2201,6 +2201,9 @@ int front_launch(const KParams& K, bool multi, u32 cluster, cudaStream_t st) {
 int front_batch_prepare(bool multi) {
     if (multi) BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_front_batch<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrontSmem)));
     else BIBFS_CUDA_TRY(cudaFuncSetAttribute(k_front_batch<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrontSmem)));
+    if (multi) cudaFuncSetAttribute(k_front_batch<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    else cudaFuncSetAttribute(k_front_batch<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    cudaGetLastError();
     return 0;
 }
 
@@ -2215,8 +2218,25 @@ int front_batch_launch(const KParams* d_lane_K, unsigned long long* d_queries, R
     attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
     cfg.attrs = &attr;
     cfg.numAttrs = cluster > 1 ? 1 : 0;
-    if (multi) BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front_batch<true>, d_lane_K, d_queries, h_res, nq));
-    else BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front_batch<false>, d_lane_K, d_queries, h_res, nq));
+    if (multi) BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front_batch<true>, d_lane_K, d_queries, h_res, nq, (Mailbox*)nullptr, 0u, 0u));
+    else BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front_batch<false>, d_lane_K, d_queries, h_res, nq, (Mailbox*)nullptr, 0u, 0u));
+    count_launch();
+    return 0;
+}
+
+// the resident front kernel: one lane that takes its queries from the mailbox until it is told to leave or idles out
+int front_resident_launch(const KParams* d_lane_K, Mailbox* mb, u32 start_seq, u32 idle_us, u32 cluster, cudaStream_t st) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cluster);
+    cfg.blockDim = dim3(BFS_THREADS);
+    cfg.dynamicSmemBytes = sizeof(FrontSmem);
+    cfg.stream = st;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = cluster > 1 ? 1 : 0;
+    BIBFS_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_front_batch<false>, d_lane_K, (unsigned long long*)nullptr, (Result*)nullptr, 0u, mb, start_seq, idle_us));
     count_launch();
     return 0;
 }

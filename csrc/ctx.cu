@@ -9,6 +9,7 @@
 // bibfs_ctx_query enqueues the whole search.
 #include "bfs.h"
 #include <atomic>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -676,6 +677,167 @@ extern "C" int bibfs_pool_query(bibfs_pool* p, const uint32_t* h_src, const uint
         if (h_edges) h_edges[q] = r.edges_scanned;
     }
     if (bad) return fail("a pooled query was aborted by the device watchdog");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// resident solver: one front kernel that stays on the GPU and is fed through a mailbox in pinned host memory
+// (k_front_batch in resident mode, front.cuh).  The host side is three stores and a poll.
+// ------------------------------------------------------------------------------------------
+struct bibfs_resident {
+    bibfs_ctx* ctx = nullptr;          // owns the arena; also answers what the front kernel cannot finish
+    Mailbox* mb = nullptr;             // pinned, device-visible (UVA)
+    KParams* d_K = nullptr;
+    cudaStream_t st = nullptr, st2 = nullptr;      // st: the resident kernel; st2: copies beside it
+    u32 cluster = 1, idle_us = 50000;
+    u32 seq = 0;                       // sequence number of the last query posted
+    bool running = false;              // a kernel has been launched and has not been seen leaving
+    uint64_t launches = 0;
+    int device = 0;
+};
+
+static int resident_launch(bibfs_resident* r) {
+    // the new kernel treats everything up to the last COMPLETED query as old: a query posted while the previous kernel was
+    // leaving is still in the mailbox and is taken at once
+    const u32 done = *reinterpret_cast<volatile u32*>(&r->mb->out_seq);
+    *reinterpret_cast<volatile u32*>(&r->mb->alive) = 1u;
+    std::atomic_thread_fence(std::memory_order_seq_cst);
+    if (front_resident_launch(r->d_K, r->mb, done, r->idle_us, r->cluster, r->st)) return 1;
+    r->running = true;
+    r->launches += 1;
+    return 0;
+}
+
+// tell the kernel to leave (if it is there) and wait until it has
+static int resident_send_home(bibfs_resident* r) {
+    if (!r->running) return 0;
+    Mailbox* mb = r->mb;
+    if (*reinterpret_cast<volatile u32*>(&mb->alive)) {
+        mb->op = MB_EXIT;
+        std::atomic_thread_fence(std::memory_order_release);
+        *reinterpret_cast<volatile u32*>(&mb->seq) = ++r->seq;
+    }
+    BIBFS_CUDA_TRY(cudaStreamSynchronize(r->st));
+    // (an EXIT is never answered: bring out_seq up to date so that the next kernel does not take it for a query)
+    mb->out_seq = r->seq;
+    r->running = false;
+    return 0;
+}
+
+extern "C" int bibfs_resident_stop(bibfs_resident* r) {
+    if (!r) return 0;
+    DeviceGuard g(r->device);
+    int rc = resident_send_home(r);
+    if (r->st) { cudaStreamSynchronize(r->st); cudaStreamDestroy(r->st); }
+    if (r->st2) cudaStreamDestroy(r->st2);
+    if (r->ctx) bibfs_ctx_destroy(r->ctx);
+    if (r->d_K) cudaFree(r->d_K);
+    if (r->mb) cudaFreeHost(r->mb);
+    delete r;
+    return rc;
+}
+
+extern "C" int bibfs_resident_start(bibfs_resident** out, const bibfs_ctx_desc* desc, uint32_t cluster, uint32_t idle_ms) {
+    if (!out || !desc) return fail("NULL argument");
+    if (desc->nranks != 1 || desc->vranks != 1 || desc->rank_lo != 0) return fail("the resident solver works on a single-rank graph");
+    if (!desc->d_vrec[0]) return fail("the resident solver needs the graph's vertex records (bibfs_vrec_build_device)");
+    if (cluster == 0) cluster = 1;
+    if (cluster > 16 || (cluster & (cluster - 1))) return fail("cluster must be 1, 2, 4, 8 or 16");
+    bibfs_resident* r = new bibfs_resident();
+    cudaGetDevice(&r->device);
+    r->idle_us = (idle_ms ? idle_ms : 50u) * 1000u;
+    if (bibfs_ctx_create(&r->ctx, desc)) { delete r; return 1; }
+    if (cluster > r->ctx->front_cluster) cluster = r->ctx->front_cluster;
+    r->cluster = cluster;
+    if (cudaHostAlloc((void**)&r->mb, sizeof(Mailbox), cudaHostAllocDefault) != cudaSuccess ||
+        cudaMalloc((void**)&r->d_K, sizeof(KParams)) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&r->st, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&r->st2, cudaStreamNonBlocking) != cudaSuccess || front_batch_prepare(false)) {
+        bibfs_resident_stop(r);
+        return fail("resident solver: allocation failed");
+    }
+    memset(r->mb, 0, sizeof(Mailbox));
+    KParams K;
+    fill_params(r->ctx, K, 0, 0, false, 0);
+    K.lone = 1u; K.warm_lines = 0; K.async_peers = 0;
+    K.fuse_path = 2u;
+    K.h_out = r->mb->out; K.h_out_words = 240; K.h_seq = &r->mb->out_seq;
+    if (cudaMemcpy(r->d_K, &K, sizeof(K), cudaMemcpyHostToDevice) != cudaSuccess) { bibfs_resident_stop(r); return fail("resident solver: upload failed"); }
+    *out = r;
+    return 0;
+}
+
+extern "C" int bibfs_resident_launches(const bibfs_resident* r, uint64_t* launches) {
+    if (!r || !launches) return fail("NULL argument");
+    *launches = r->launches;
+    return 0;
+}
+
+extern "C" int bibfs_resident_query(bibfs_resident* r, uint32_t src, uint32_t dst, uint32_t flags,
+                                    bibfs_result* res, uint32_t* path, uint32_t path_cap) {
+    if (!r || !res) return fail("NULL argument");
+    if (flags & ~(uint32_t)BIBFS_F_NO_PATH) return fail("the resident solver takes flags 0 or BIBFS_F_NO_PATH");
+    DeviceGuard g(r->device);
+    Mailbox* mb = r->mb;
+    volatile u32* alive = &mb->alive;
+    volatile u32* out_seq = &mb->out_seq;
+    if (!r->running || !*alive) {
+        if (r->running) { BIBFS_CUDA_TRY(cudaStreamSynchronize(r->st)); r->running = false; }
+        if (resident_launch(r)) return 1;
+    }
+    // post the query: payload first, sequence number last
+    const u32 seq = ++r->seq;
+    mb->src = src; mb->dst = dst; mb->op = flags & BIBFS_F_NO_PATH;
+    std::atomic_thread_fence(std::memory_order_release);
+    *reinterpret_cast<volatile u32*>(&mb->seq) = seq;
+    const auto t0 = std::chrono::steady_clock::now();
+    const double limit_s = 2.0 * r->ctx->d.watchdog_ms * 1e-3 + 1.0;
+    for (u32 spins = 0;; ++spins) {
+        if (*out_seq == seq) break;
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();
+#endif
+        if ((spins & 1023u) == 1023u) {
+            if (!*alive) {
+                // the kernel left (idle) as the query arrived: the next one finds it in the mailbox
+                BIBFS_CUDA_TRY(cudaStreamSynchronize(r->st));
+                r->running = false;
+                if (*out_seq == seq) break;
+                if (resident_launch(r)) return 1;
+            }
+            if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > limit_s)
+                return fail("the resident kernel did not answer within %.1f s", limit_s);
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    const Result* hr = reinterpret_cast<const Result*>(mb->out);
+    if (hr->status == ST_ESCALATED) {
+        // beyond the front kernel: send it home and let the general kernel answer on the same arena
+        if (resident_send_home(r)) return 1;
+        return bibfs_ctx_query_result(r->ctx, src, dst, nullptr, flags, res, path, path_cap, r->st);
+    }
+    memset(res, 0, sizeof(*res));
+    res->length = hr->length; res->meet = hr->meet; res->depth_s = hr->depth_s; res->depth_t = hr->depth_t;
+    res->levels = hr->levels; res->levels_bottom_up = hr->levels_bu; res->status = hr->status;
+    res->edges_scanned = hr->edges_scanned; res->vertices_visited = hr->vertices_visited;
+    res->levels_grid = hr->levels_grid; res->levels_paired = hr->rounds_paired & 0x7FFFFFFFu;
+    res->search_ms = hr->search_ns * 1e-6; res->path_ms = hr->path_ns * 1e-6;
+    res->path_len = 0;
+    if (hr->status == 1) return fail("search aborted by the device watchdog");
+    if (hr->status == 2) return fail("src/dst out of range (n=%u)", r->ctx->d.n);
+    const bool want_path = !(flags & BIBFS_F_NO_PATH);
+    if (want_path && hr->status == 0 && hr->length >= 0 && path) {
+        const u32 plen = hr->path_len;
+        if (plen == 0 || plen > path_cap) res->status = 3;
+        else if (plen <= 240) { memcpy(path, mb->out + PATH_HDR_WORDS, (size_t)plen * 4); res->path_len = plen; }
+        else {
+            // long path: it sits in the arena (the kernel is idle now: the copy runs beside it on another stream)
+            BIBFS_CUDA_TRY(cudaMemcpyAsync(path, r->ctx->arena_local[0] + r->ctx->L.off_path + sizeof(Result), (size_t)plen * 4,
+                                           cudaMemcpyDeviceToHost, r->st2));
+            BIBFS_CUDA_TRY(cudaStreamSynchronize(r->st2));
+            res->path_len = plen;
+        }
+    }
     return 0;
 }
 

@@ -451,13 +451,17 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
 // query) until the list is used up, and delivers each 64-byte result into h_res[q] (pinned host memory).  A lane runs the query the way a `lone` front kernel does: pair tier, wide rounds on
 // its own cluster, no peers; a search it cannot finish is reported as ST_ESCALATED and left to the caller.  Lanes never
 // talk to one another, so the grid may be larger than what is resident at once.
+// RESIDENT mode (mb != null, one lane): the queries come one by one through a mailbox in pinned host memory and the
+// kernel stays until it is told to leave or has been idle for idle_us; [result | path] go back to the mailbox
+// (bibfs_resident_* in ctx.cu).
 // ------------------------------------------------------------------------------------------
 template <bool MULTI>
 __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* __restrict__ lane_K, unsigned long long* queries,
-                                                                Result* h_res, const u32 nq) {
+                                                                Result* h_res, const u32 nq,
+                                                                Mailbox* const mb, const u32 start_seq, const u32 idle_us) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ KParams sK;
-    __shared__ u32 s_query[3];
+    __shared__ u32 s_query[4];
     const u32 tid = threadIdx.x;
     const u32 cl_n = ptx::cluster_nctarank(), cl_rank = ptx::cluster_ctarank();
     constexpr u32 LANE_EXIT = 0xFFFFFFFFu;      // PairOut::go_wide value that sends the helpers home
@@ -498,6 +502,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
     if (MULTI) for (u32 p = 0; p < K.P; ++p) tier_ok = tier_ok && K.vrec[p] != nullptr;
     else tier_ok = K.vrec[0] != nullptr;
 
+    u32 last_seq = start_seq;        // (thread 0 of the leader CTA) sequence number of the last mailbox query taken
     auto push_out = [&]() {          // leader CTA: fs.ps.out into every helper's shared memory, then the barrier they wait at
         if (tid < 16u * (cl_n - 1u)) {
             const u32 c = 1u + tid / 16u, i = tid % 16u;
@@ -520,9 +525,29 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
             }
             continue;
         }
-        if (tid == 0) {
+        if (tid == 0 && mb) {
+            // resident mode: poll the mailbox in the host's pinned memory (one 16-byte load per PCIe round trip) until a new
+            // sequence number shows up; leave when told to, or after idle_us without a query
+            const u64 t_idle = ptx::globaltimer_ns();
+            uint4 w;
+            u32 spins = 0;
+            bool leave = false;
+            while (true) {
+                w = ptx::ld_v4_sys(reinterpret_cast<const uint4*>(mb));
+                if (w.z != last_seq) { leave = (w.w & MB_EXIT) != 0; break; }
+                if ((++spins & 15u) == 0 && ptx::globaltimer_ns() - t_idle > (u64)idle_us * 1000ull) { leave = true; break; }
+            }
+            s_query[2] = leave ? 1u : 0u;
+            if (!leave) {
+                last_seq = w.z;
+                s_query[0] = w.x; s_query[1] = w.y;
+                sK.seq = w.z;
+                sK.flags = w.w & BIBFS_F_NO_PATH;
+                sK.fuse_path = (w.w & BIBFS_F_NO_PATH) ? 1u : 2u;
+            }
+        } else if (tid == 0) {
             const u32 q = (u32)atomicAdd(queries + nq, 1ull);
-            s_query[2] = q;
+            s_query[2] = q < nq ? 0u : 1u;
             if (q < nq) {
                 const u64 w = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(queries + q));
                 s_query[0] = (u32)w; s_query[1] = (u32)(w >> 32);
@@ -530,7 +555,8 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
             }
         }
         __syncthreads();
-        if (s_query[2] >= nq) {
+        if (s_query[2]) {
+            if (mb && tid == 0) { __threadfence_system(); *reinterpret_cast<volatile u32*>(&mb->alive) = 0u; }
             if (cl_n > 1) {
                 if (tid == 0) fs.ps.out.go_wide = LANE_EXIT;
                 __syncthreads();
@@ -594,14 +620,8 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
             if (tid == 0) pair_finish<MULTI>(K, E, st, fs.acc, fs.qvalid, fs.ps.out, edges);
             __syncthreads();
         }
-        // ---- undo the marks (from the shared-memory log when the search never left the narrow rounds); result (or
-        // "not finished here") to the host
-        const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
-        if (tier && !fs.ps.out.went_wide && t0 <= PT_LOG_CAP && t1 <= PT_LOG_CAP) {
-            for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[0][i] >> 5] = 0ull;
-            for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[1][i] >> 5] = 0ull;
-        } else clear_marks(E, io, t0, t1, 0u, wide ? cl_n : 1u);
-        if (wide) ptx::cluster_sync_all();
+        // ---- result (or "not finished here") and, in resident mode, the path to the host; then undo the marks (from the
+        // shared-memory log when the search never left the narrow rounds)
         if (st.phase != PH_DONE && tid == 0) {
             Result& R = C->res;
             R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
@@ -609,7 +629,17 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
             R.edges_scanned = st.edges_total; R.vertices_visited = st.visited_total; R.search_ns = 0; R.path_ns = 0;
         }
         __syncthreads();
-        result_to_host(K);
+        const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
+        const bool in_smem = tier && !fs.ps.out.went_wide && t0 <= PT_LOG_CAP && t1 <= PT_LOG_CAP;
+        if (K.fuse_path == 2u && st.phase == PH_DONE) {
+            if (in_smem && st.status == 0 && st.length > 0) path_from_log(K, fs.ps.slog, t0, t1, &fs.ps.fv[0][0][0], fs.own);
+            else path_body_local(K, io.par[0], io.par[1]);
+        } else result_to_host(K);
+        if (in_smem) {
+            for (u32 i = tid; i < t0; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[0][i] >> 5] = 0ull;
+            for (u32 i = tid; i < t1; i += BFS_THREADS) E.vis[(u32)fs.ps.slog[1][i] >> 5] = 0ull;
+        } else clear_marks(E, io, t0, t1, 0u, wide ? cl_n : 1u);
+        if (wide) ptx::cluster_sync_all();
         __syncthreads();
     }
 }

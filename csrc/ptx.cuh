@@ -95,6 +95,11 @@ __device__ __forceinline__ uint4 ld_v4_gpu_if(bool on, const uint4* p) {
         : "memory");
     return r;
 }
+__device__ __forceinline__ uint4 ld_v4_sys(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
 __device__ __forceinline__ u32 ld_u32_gpu_if(bool on, const u32* p) {
     u32 r;
     asm volatile(

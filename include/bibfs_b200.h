@@ -308,6 +308,22 @@ int bibfs_pool_query(bibfs_pool* pool, const uint32_t* h_src, const uint32_t* h_
                      int32_t* h_len, uint32_t* h_meet, uint32_t* h_levels, uint64_t* h_edges, float* ms);
 int bibfs_pool_destroy(bibfs_pool* pool);
 
+/* Resident solver (single rank): ONE front kernel that stays on the GPU and takes its queries from a mailbox in pinned
+ * host memory — no launch per query.  bibfs_resident_query writes {src, dst} into the mailbox, the kernel (polling it
+ * over PCIe) runs the search, walks the path and writes [result | path] back, the host polls the completion word: a
+ * query costs the search plus three PCIe trips instead of a launch and a teardown.  The kernel occupies `cluster` SMs
+ * (1, 2, 4, 8 or 16; 0 -> 1) while it is resident and leaves by itself after idle_ms without a query (0 -> 50; the next
+ * query launches it again), so a device-wide synchronisation elsewhere in the process is delayed by at most that long.
+ * A search beyond the front kernel (frontier > 65536 per side) is answered by the general kernel after the resident
+ * kernel has been sent home.  flags: 0 or BIBFS_F_NO_PATH.  Needs vertex records (desc->d_vrec[0]).  One caller
+ * thread per solver.  No counterpart in the reference (one process per query). */
+typedef struct bibfs_resident bibfs_resident;
+int bibfs_resident_start(bibfs_resident** out, const bibfs_ctx_desc* desc, uint32_t cluster, uint32_t idle_ms);
+int bibfs_resident_query(bibfs_resident* r, uint32_t src, uint32_t dst, uint32_t flags,
+                         bibfs_result* res, uint32_t* path, uint32_t path_cap);
+int bibfs_resident_launches(const bibfs_resident* r, uint64_t* launches);   /* how often the kernel had to be (re)launched */
+int bibfs_resident_stop(bibfs_resident* r);                                  /* sends the kernel home and frees everything */
+
 /* ------------------------------------------------------------------------------------------
  * reference-style level-synchronous GPU baseline (one thread per vertex over all N, int flag
  * arrays, host in the loop) — OUR restatement of the v3 algorithm (v3/bibfs_cuda_only.cu:173-203)

@@ -203,3 +203,42 @@ def test_native_cli_gpu_variants(bb, tmp_path):
         p = re.search(r"Path: ([\d ]+)", out.stdout)
         nodes = [int(x) for x in p.group(1).split()]
         bb.validate_path(g_cpu, s, t, nodes, want)
+
+
+def test_resident_solver_mailbox(bb):
+    """One resident front kernel answers a stream of queries through the pinned mailbox: lengths and paths equal to the
+    serial variant, the kernel is launched once for the whole stream, idles out and comes back, and a search beyond the
+    front kernel falls back to the general kernel."""
+    import time
+    spec = bb.er_spec(20000, 2.2 / 20000, seed=3)
+    g_cpu = bb.Graph.generate(spec)
+    oracle = bb.SerialSolver(g_cpu, policy=1)
+    g = bb.Graph.generate(spec, device="cuda:0")
+    pairs = query_pairs(spec.n, 60, 4) + [(5, 5), (0, spec.n - 1)]
+    for cluster in (1, 4):
+        r = bb.ResidentSolver(g, cluster=cluster, idle_ms=30)
+        for s, t in pairs:
+            want = oracle.query(s, t, want_path=False).length
+            got = r.query(s, t)
+            assert got.length == want, (cluster, s, t, got.length, want)
+            if want is not None:
+                bb.validate_path(g_cpu, s, t, got.path, want)
+            assert r.query(s, t, want_path=False).length == want
+        assert r.launches == 1, r.launches
+        time.sleep(0.12)                      # the kernel idles out ...
+        s, t = pairs[0]
+        assert r.query(s, t).length == oracle.query(s, t, want_path=False).length      # ... and is launched again
+        assert r.launches == 2, r.launches
+        r.close()
+    # wide rounds and long rows inside the resident kernel (cluster of 4), and a grid whose frontiers outgrow one CTA
+    for spec2 in (bb.rmat_spec(14, edgefactor=16, seed=2), bb.grid_spec(400, 300)):
+        h = bb.Graph.generate(spec2)
+        o2 = bb.SerialSolver(h, policy=1)
+        r = bb.ResidentSolver(bb.Graph.generate(spec2, device="cuda:0"), cluster=4, idle_ms=30)
+        for s, t in query_pairs(spec2.n, 20, 6):
+            want = o2.query(s, t, want_path=False).length
+            got = r.query(s, t)
+            assert got.length == want, (spec2.kind, s, t, got.length, want)
+            if want is not None:
+                bb.validate_path(h, s, t, got.path, want)
+        r.close()
