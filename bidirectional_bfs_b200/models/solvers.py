@@ -385,6 +385,8 @@ def make_solver(graph: Graph, variant: str = "gpu", **kw):
         return MultiGpuSolver(graph, **kw)
     if variant == "naive-gpu":
         return NaiveGpuSolver(graph, **kw)
+    if variant == "gpu-resident":
+        return ResidentSolver(graph, **kw)
     if variant == "batch":
         return BatchSolver(graph, **kw)
-    raise ValueError(f"unknown variant {variant!r}; choose from {VARIANTS + ('batch',)}")
+    raise ValueError(f"unknown variant {variant!r}; choose from {VARIANTS + ('gpu-resident', 'batch')}")

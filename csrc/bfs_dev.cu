@@ -412,6 +412,7 @@ __device__ __noinline__ bool leader_sync(const KParams& K, const Env& E, LevelSt
             return true;
         }
     }
+    if (kind == SYNC_LEVEL && level_mode == PH_BU && lane == 0) C->hub_packed = 0;      // (the bottom-up level's own hub list)
     Slot mine;
     mine.count = A.new_count;
     mine.meet = A.meet_local;
@@ -1037,6 +1038,7 @@ __device__ __noinline__ void expand_hubs(const KParams& K, const Env& E0, const 
 // Short rows are scanned by their lane, long rows by the whole warp (ballot = early exit).
 // ------------------------------------------------------------------------------------------
 constexpr int BU_W = 8;      // adjacency entries a lane has in flight in the bottom-up scans
+constexpr u32 BU_HUB_ROW = 4096;      // bottom-up: rows at least this long are scanned by the whole grid (expand_bu_hubs)
 template <bool MULTI>
 __device__ __noinline__ void expand_bu(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps) {
     const u32 lane = threadIdx.x & 31;
@@ -1075,7 +1077,24 @@ __device__ __noinline__ void expand_bu(const KParams& K, const Env& E, const Lev
                 }
             }
         }
-        u32 big = __ballot_sync(FULL, unvis && deg >= BIG_ROW);
+        // rows of >= BU_HUB_ROW entries go to the hub list: the whole grid scans them chunk by chunk afterwards
+        // (expand_bu_hubs).  One warp walking a 300,000-entry row alone was 1.6 ms of a 2.5 ms sweep (R-MAT scale 22).
+        bool hub = unvis && deg >= BU_HUB_ROW;
+        if (hub) {
+            const u32 nch = hub_nchunks(r0, r1);
+            const unsigned long long inc = (1ull << 40) | (unsigned long long)nch;
+            const unsigned long long old = atomicAdd(&E.C->hub_packed, inc);
+            const u32 slot = (u32)(old >> 40);
+            if (slot < HUB_CAP) {
+                HubEntry h;
+                h.u = v; h.nchunks = nch; h.r0 = r0; h.r1 = r1; h.chunk_base = old & 0xFFFFFFFFFFull;
+                hub_of(K, E.me)[slot] = h;
+            } else {
+                atomicAdd(&E.C->hub_packed, 0ull - inc);      // list full: the warp walks the row
+                hub = false;
+            }
+        }
+        u32 big = __ballot_sync(FULL, unvis && deg >= BIG_ROW && !hub);
         while (big) {
             const u32 sl = __ffs(big) - 1;
             big &= big - 1;
@@ -1118,6 +1137,62 @@ __device__ __noinline__ void expand_bu(const KParams& K, const Env& E, const Lev
         cnt += __shfl_xor_sync(FULL, cnt, d);
         edges += __shfl_xor_sync(FULL, edges, d);
     }
+    if (lane == 0) {
+        if (cnt) atomicAdd(&E.A->new_count, cnt);
+        if (edges) atomicAdd(&E.A->edges, (unsigned long long)edges);
+    }
+}
+
+// second phase of a bottom-up level: the rows expand_bu deferred, one 256-entry chunk per warp and step, all warps of
+// the rank.  The first chunk that finds a parent claims the vertex (atomic on its visited word); chunks that come later
+// see the mark and skip their scan.
+template <bool MULTI>
+__device__ __noinline__ void expand_bu_hubs(const KParams& K, const Env& E, const LevelState& st, u32 warp_gid, u32 nwarps) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 side = st.side;
+    const u64 hp = ptx::ld_relaxed_gpu(reinterpret_cast<const u64*>(&E.C->hub_packed));
+    const u32 ne = min((u32)(hp >> 40), HUB_CAP), nch = (u32)(hp & 0xFFFFFFFFFFull);
+    if (!nch) return;
+    const HubEntry* H = hub_of(K, E.me);
+    const u32* fcur = fbm_of(K, E.me, side, st.fbm_cur[side]);
+    u32* fnext = fbm_of(K, E.me, side, st.fbm_cur[side] ^ 1u);
+    u32 cnt = 0;
+    u64 edges = 0;
+    static_assert(HUB_CHUNK == 32 * BU_W, "one step of the warp per chunk");
+    for (u32 c = warp_gid; c < nch; c += nwarps) {
+        const HubChunk h = hub_lookup(H, ne, E.col, c);
+        if (!h.valid) continue;
+        const u32 v = h.uu;
+        const u64 bit = 1ull << (32u * side + (v & 31u));
+        if (ptx::ld_relaxed_gpu(&E.vis[v >> 5]) & bit) continue;
+        const u32* cc = E.col + h.A;
+        u32 u[BU_W], w[BU_W];
+#pragma unroll
+        for (int k = 0; k < BU_W; ++k) { const u32 idx = h.lo + 32u * k + lane; u[k] = __ldg(cc + (idx < h.hi ? idx : h.lo)); }
+#pragma unroll
+        for (int k = 0; k < BU_W; ++k) w[k] = fcur[u[k] >> 5];
+        u32 hitpar = NO_V;
+#pragma unroll
+        for (int k = 0; k < BU_W; ++k) {
+            const bool in = h.lo + 32u * k + lane < h.hi;
+            if (in) ++edges;
+            const u32 hm = __ballot_sync(FULL, in && ((w[k] >> (u[k] & 31u)) & 1u));
+            if (hm && hitpar == NO_V) hitpar = __shfl_sync(FULL, u[k], __ffs(hm) - 1);
+        }
+        if (hitpar != NO_V && lane == 0) {
+            const u64 old = atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[v >> 5]), (unsigned long long)bit);
+            if (!(old & bit)) {
+                q_append(E, side, 1u, v);
+                E.parent[side][v - E.lo] = hitpar;
+                atomicOr(&fnext[v >> 5], 1u << (v & 31u));
+                if ((old >> (32u * (1u - side) + (v & 31u))) & 1ull) atomicMin(&E.A->meet_local, v);
+                ++cnt;
+            }
+        }
+        __syncwarp();
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) edges += __shfl_xor_sync(FULL, edges, d);
     if (lane == 0) {
         if (cnt) atomicAdd(&E.A->new_count, cnt);
         if (edges) atomicAdd(&E.A->edges, (unsigned long long)edges);
@@ -1949,6 +2024,11 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_bibfs(const __grid_constant_
                 if (!alive) break;
             }
             expand_bu<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
+            if (K.long_rows) {       // the graph may have rows for the hub list: they are scanned by all warps of the rank
+                alive = sync_grid(SYNC_LOCAL, PH_BU);
+                if (!alive) break;
+                expand_bu_hubs<MULTI>(K, E, st, E.cta * WPC + warp, E.cpr * WPC);
+            }
             if (MULTI) {
                 alive = sync_grid(SYNC_LOCAL, PH_BU);
                 if (!alive) break;
