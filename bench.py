@@ -222,6 +222,14 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
             dist.barrier()
         torch.cuda.synchronize()
 
+    def align():
+        """Several ranks, before a timed step: an NCCL barrier (coarse: the ranks leave it tens of microseconds apart, and
+        the max over ranks of a 40 us step would mostly measure that), then a trivial query (s == t) through the framework's
+        own protocol: every peer returns when rank 0's verdict reaches it, which aligns the ranks to a few microseconds.  The
+        L2 flush comes after it (the same fill on every GPU)."""
+        barrier()
+        solver.query(0, 0, want_path=False)
+
     for s, t, length, _, _ in queries[:W]:
         if flush is not None:
             flush.fill_(1)
@@ -229,16 +237,18 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
         if r.length != length:
             raise SystemExit(f"{config}: wrong length on {s}->{t}: {r.length}, the v1 schedule gives {length}")
     barrier()
-    launches0 = bb.lib().bibfs_launch_count()
+    launches = 0
     wall0 = time.perf_counter()
     ms, ms_path, own_edges, lengths = np.zeros(K), np.zeros(K), np.zeros(K), []
     for i, (s, t, length, _, _) in enumerate(queries[W:W + K]):
         if world > 1:
-            barrier()                                  # every rank starts the step together: a peer's events bracket its wait
+            align()                                    # every rank starts the step together: a peer's events bracket its wait
                                                        # kernel, which would otherwise also count rank 0's host work (path copy)
         if flush is not None:
             flush.fill_(i & 0xFF)                      # evict the graph from L2 between steps
+        l0 = bb.lib().bibfs_launch_count()
         r = solver.query(s, t, want_path=True, timing="events")      # CUDA events on the launching stream
+        launches += bb.lib().bibfs_launch_count() - l0               # kernels of the timed queries only (not the alignment queries)
         ms[i] = r.search_ms            # same coverage as the reference's timers: the search loop only
         ms_path[i] = r.path_ms
         own_edges[i] = r.edges_scanned
@@ -247,7 +257,6 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
             raise SystemExit(f"{config}: wrong length on {s}->{t}: {r.length}, the v1 schedule gives {length}")
     barrier()
     wall_dev_loop = time.perf_counter() - wall0
-    launches = bb.lib().bibfs_launch_count() - launches0
     if world > 1:
         if os.environ.get("BIBFS_BENCH_VERBOSE"):
             print(f"[rank {rank}] {config}: own event-timed search ms mean {ms.mean():.4f} min {ms.min():.4f} max {ms.max():.4f}", file=sys.stderr, flush=True)
@@ -270,7 +279,7 @@ def measure_ours(bb, comm, dist, torch, dev, rank, world, config, seed, K, W, do
             total = 0.0
             for i, (s, t, length, _, _) in enumerate(queries[W:W + K]):
                 if world > 1:
-                    dist.barrier()
+                    align()
                 if flush is not None:
                     with torch.cuda.stream(side):
                         flush.fill_(i & 0xFF)
@@ -465,7 +474,9 @@ def run_ours(args):
             "config": {"model": f"bidirectional BFS on {m['desc']}", "name": args.config, "n": m["n"], "directed_edges": m["nnz"],
                        "global_batch": 1, "seq_len": None, "queries": "0->n-1 first, then seeded random connected pairs",
                        "parallelism": f"1-D vertex partition over {world} GPU(s), one process per GPU",
-                       "l2": m["l2"], "numerator": m["numerator"], "seed": args.seed},
+                       "l2": m["l2"], "numerator": m["numerator"], "seed": args.seed,
+                       **({"step_alignment": "before every timed step: NCCL barrier + synchronize, then a trivial query (s == t) whose verdict "
+                                             "releases all ranks within a few microseconds, then the L2 flush"} if world > 1 else {})},
             "search_ms": {"mean": ms_per_step, "median": float(np.median(m["ms"])), "min": float(m["ms"].min()), "max": float(m["ms"].max())},
             "path_ms_mean": float(m["ms_path"].mean()),
             "path_length": {"min": int(min(m["lengths"])), "max": int(max(m["lengths"]))},
