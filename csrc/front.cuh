@@ -176,22 +176,25 @@ __device__ __noinline__ void path_from_log(const KParams& K, const unsigned long
     const u64 tb = ptx::globaltimer_ns();
     const u32 L = (u32)R.length, ds = R.depth_s, meet = R.meet;
     const bool ok = L + 1u <= K.max_path;
+    if (tid < 2) s_idx[tid] = 0;
+    __syncthreads();
     for (u32 i = tid; i < t0; i += BFS_THREADS) if ((u32)slog[0][i] == meet) s_idx[0] = i;
     for (u32 i = tid; i < t1; i += BFS_THREADS) if ((u32)slog[1][i] == meet) s_idx[1] = i;
     __syncthreads();
+    // (indices are masked into the log: a corrupted entry may give a wrong path, never a stray access)
     if (ok && tid == 0) {
         u32 idx = s_idx[0];
         for (u32 pos = ds;; --pos) {
-            const unsigned long long e = slog[0][idx];
+            const unsigned long long e = slog[0][min(idx, PT_LOG_CAP - 1u)];
             path[pos] = (u32)e;
             if (pos < PT_CAP_FRONT) s_path[pos] = (u32)e;
             if (pos == 0) break;
             idx = (u32)(e >> 32);
         }
     } else if (ok && tid == 32) {
-        unsigned long long e = slog[1][s_idx[1]];
+        unsigned long long e = slog[1][min(s_idx[1], PT_LOG_CAP - 1u)];
         for (u32 pos = ds; pos < L; ++pos) {
-            e = slog[1][(u32)(e >> 32)];
+            e = slog[1][min((u32)(e >> 32), PT_LOG_CAP - 1u)];
             path[pos + 1] = (u32)e;
             if (pos + 1 < PT_CAP_FRONT) s_path[pos + 1] = (u32)e;
         }
