@@ -1,13 +1,18 @@
 // front.cuh — query flow with a FRONT kernel (included by bfs_dev.cu after the search kernel).
 //
-//   k_front   one CTA on the GPU that hosts rank 0.  Starts the query, runs the pair tier (pair_tier.cuh) and, when
-//             the search ends inside the tier — every reference-sized query does — walks the path, delivers
-//             [result | path] to the caller's pinned buffer and clears the visited words it set.  Its code is a few
-//             KB, it needs no cooperative launch, no grid and no barrier other than __syncthreads: the fixed cost
-//             of a query (start-up + teardown of the general kernel: ~25 us of a 47 us query) shrinks to the launch
-//             of one small CTA.  When the tier has to stop (frontier > 512, a row >= 32 entries) it leaves the
-//             search where the general kernel k_bibfs can pick it up (KParams::resume): the level state in
-//             Ctrl::st, and with several ranks the HAND-OVER below.  The host launches k_bibfs only then.
+//   k_front   one CTA — or one thread-block cluster of up to 16 — on the GPU that hosts rank 0.  Starts the query, runs the
+//             pair tier (pair_tier.cuh: narrow rounds in the leader CTA, wide rounds on the whole cluster) and, when the
+//             search ends there — every reference-sized query does, and so do grids and power-law graphs up to frontiers
+//             of 65536 per side — walks the path (from the shared-memory log when the rounds stayed narrow), delivers
+//             [result | path] to the caller's pinned buffer and clears the visited words it set (all CTAs that took
+//             part; as a sweep once the search has covered a sizeable part of the graph).  It needs no cooperative
+//             launch and no grid barrier: the fixed cost of a query (start-up + teardown of the general kernel: ~25 us
+//             of a 47 us query) shrinks to the launch of a small kernel (~10 us).  When the tier has to stop it leaves
+//             the search where the general kernel k_bibfs can pick it up (KParams::resume): the level state in Ctrl::st,
+//             and with several ranks the HAND-OVER below.  The host launches k_bibfs only then.
+//   k_front_batch   the same query flow as a loop: every cluster of the grid is a lane with its own arena that draws
+//             queries from a counter (query pool), or ONE lane that stays resident and takes its queries from a mailbox
+//             in pinned host memory (resident solver).
 //   several ranks: rank 0's front kernel works alone on the whole graph through the peer mappings, so a small
 //             query costs the other GPUs nothing: no per-level handshake, no remote claim.  The reference pays an
 //             MPI_Allreduce over int[N] per level whatever the frontier size (v4/mpi_bas.cpp:107).

@@ -27,9 +27,11 @@
 //     thread-0 bookkeeping between them (that was 40 % of a solo level).  The counters rotate
 //     through three sets so that nobody resets a word somebody else may still read.
 //
-// The tier runs at the start of a query while both frontiers fit one CTA (<= 512 entries per side)
-// and no row of >= PT_MAXDEG entries has been discovered; then it hands the search to the general
-// machinery (solo / cluster / grid / hub / bottom-up) through the same LevelState those use.
+// Inside the general kernel the tier runs at the start of a query while both frontiers fit one CTA (<= 512 entries
+// per side) and no row of >= PT_MAXDEG entries has been discovered; then it hands the search to the general machinery
+// (solo / cluster / grid / hub / bottom-up) through the same LevelState those use.  The front kernel (front.cuh) runs
+// it with 768 entries per side, keeps the first PT_LOG_CAP log entries per side in shared memory for the path walk, and
+// continues with WIDE rounds on its whole cluster (pair_wide below) where the narrow rounds stop.
 
 // PT_MARK: points of a round where the fine-trace build takes time stamps.  The regular build keeps a NEVER-TAKEN branch
 // at each of them (query flag bit 31 is rejected by bibfs_ctx_query): measured on B200, the same round loop runs 36.3 us

@@ -292,11 +292,12 @@ int bibfs_batch_query_device(uint32_t n, const uint64_t* d_row_ptr, const uint32
                              int32_t* h_lengths, uint32_t* h_meet, void* d_ws, size_t ws_bytes,
                              float* search_ms, void* stream);
 
-/* Query pool: `lanes` single-rank contexts with small grids (ctas_per_lane, 0 -> 1) on their own
- * streams; nq queries are dealt round-robin and run concurrently.  A bidirectional search is bound
- * by the latency of its level chain, so independent queries scale with the number of SMs.  Outputs
- * may be NULL.  ms = device time from the first launch to the last completion.  Out-of-range
- * queries report length -1.  No counterpart in the reference. */
+/* Query pool: `lanes` search arenas; a batch of nq queries is ONE launch whose thread-block clusters (2 or 4 CTAs) are
+ * the lanes: each draws queries from a shared counter until the list is used up and writes its 64-byte results straight
+ * into pinned host memory.  A bidirectional search is bound by the latency of its level chain, so independent queries
+ * scale with the number of SMs.  (Without vertex records the lanes fall back to one general-kernel launch per query on
+ * their own streams, ctas_per_lane CTAs each, 0 -> 1.)  Outputs may be NULL.  ms = device time of the batch.
+ * Out-of-range queries report length -1.  No counterpart in the reference. */
 typedef struct bibfs_pool bibfs_pool;
 int bibfs_pool_create(bibfs_pool** out, const bibfs_ctx_desc* desc, uint32_t lanes, uint32_t ctas_per_lane);
 /* Pool on a PARTITIONED graph (desc->nranks > 1, created in the process that hosts rank 0): every lane is rank 0's front
