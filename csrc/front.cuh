@@ -151,6 +151,86 @@ __device__ void front_handover(const KParams& K, const Env& E, FrontSmem& fs, co
     __syncthreads();
 }
 
+// ---- pieces shared by the front kernel and its loop form (k_front_batch) ----------------------------------------------------
+
+// rank 0's view of the search: its own arena, the leader CTA's shared-memory accumulators
+__device__ __forceinline__ Env front_env(const KParams& K, FrontSmem& fs) {
+    Env E;
+    E.cta = 0; E.cpr = 1; E.me = 0; E.lo = 0;
+    E.P = K.P; E.B = K.B; E.n = K.n; E.nw = K.L.nw;
+    E.C = ctrl_of(K, 0);
+    E.A = &fs.acc; E.sA = &fs.acc;
+    E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = false; E.solo = true; E.tag = 0; E.smem_src = false;
+    E.stage = nullptr; E.stage_cnt = nullptr; E.cta_new = nullptr; E.cta_edges = nullptr; E.s_sent = nullptr; E.s_rnew = nullptr;
+    E.vis = vis_of(K, 0);
+    E.parent[0] = parent_of(K, 0, 0); E.parent[1] = parent_of(K, 0, 1);
+    E.q[0] = q_of(K, 0, 0); E.q[1] = q_of(K, 0, 1);
+    E.row_ptr = K.row_ptr[0];
+    E.col = K.col[0];
+    return E;
+}
+
+// where the tier logs what it reaches: the rank's own queues / parents (single rank), the all-vertex log / parent regions
+// of rank 0's arena (several ranks)
+template <bool MULTI>
+__device__ __forceinline__ PairIO front_io(const KParams& K, const Env& E) {
+    PairIO io;
+    if (MULTI) {
+        u32* lg = reinterpret_cast<u32*>(K.arena[0] + K.L.off_log);
+        u32* pa = reinterpret_cast<u32*>(K.arena[0] + K.L.off_pall);
+        const size_t nv = (size_t)K.B * K.P;
+        io.log[0] = lg; io.log[1] = lg + nv; io.par[0] = pa; io.par[1] = pa + nv;
+    } else {
+        io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
+    }
+    return io;
+}
+
+// thread 0 of the leader CTA: level state and seeds of a new query (or its immediate answer: bad arguments, src == dst)
+__device__ __forceinline__ void front_begin_query(const KParams& K, const Env& E, FrontSmem& fs, const PairIO& io, const u32 src, const u32 dst,
+                                                  const bool bad) {
+    Ctrl* const C = E.C;
+    LevelState& G = fs.st;
+    C->q_src = src; C->q_dst = dst;
+    C->trace_count = 0;
+    C->t_begin_ns = ptx::globaltimer_ns();
+    fs.acc.q_tail[0] = 1; fs.acc.q_tail[1] = 1; fs.acc.new_count = 0; fs.acc.meet_local = NO_V; fs.acc.edges = 0;
+    fs.fail = 0;
+    G.phase = PH_TD_SOLO; G.side = 0; G.levels = 0; G.levels_bu = 0;
+    G.depth[0] = G.depth[1] = 0; G.nf[0] = G.nf[1] = 1;
+    for (u32 s = 0; s < 2; ++s) {
+        G.q_lo[s] = 0; G.q_hi[s] = 1; G.fbm_cur[s] = 0; G.fbm_valid[s] = 0; G.rq_tag[s] = 0;
+        for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
+    }
+    G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 1; G.pad = 0; G.rounds_paired = 0; G.levels_grid = 0;
+    G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
+    G.edges_total = 0; G.visited_total = 2;
+    G.xepoch = C->xepoch;
+    if (bad) { G.status = 2; G.phase = PH_DONE; fs.acc.q_tail[0] = 0; fs.acc.q_tail[1] = 0; G.q_hi[0] = G.q_hi[1] = 0; }
+    else if (src == dst) { G.length = 0; G.meet = src; G.phase = PH_DONE; G.visited_total = 1; fs.acc.q_tail[0] = 0; fs.acc.q_tail[1] = 0; G.q_hi[0] = G.q_hi[1] = 0; }
+    else {
+        // seeds: marked in rank 0's visited words whoever owns them; the owners learn about them at a hand-over
+        atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[src >> 5]), 1ull << (src & 31));
+        atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[dst >> 5]), 1ull << ((dst & 31) + 32));
+        io.log[0][0] = src; io.par[0][src] = NO_V;
+        io.log[1][0] = dst; io.par[1][dst] = NO_V;
+    }
+    if (G.phase == PH_DONE) write_result(K, C, G);
+}
+
+// counters of the wide rounds (thread 0 of the leader CTA, before the helpers are released into them)
+__device__ __forceinline__ void wide_reset(Ctrl::Wide& W) {
+    for (u32 z = 0; z < 3; ++z) { W.cnt[z][0] = 0; W.cnt[z][1] = 0; W.flag[z] = 0; W.meet[z] = NO_V; W.tr_edges[z][0] = 0; W.tr_edges[z][1] = 0; }
+    W.meet_old[0] = NO_V; W.meet_old[1] = NO_V; W.edges = 0; W.long_packed[0] = 0; W.long_packed[1] = 0; W.long_packed[2] = 0;
+}
+
+// "not finished here": what the host (or the lane's caller) sees when the front kernel leaves a search to somebody else
+__device__ __forceinline__ void escalated_result(Result& R, const LevelState& st) {
+    R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
+    R.depth_s = st.depth[0]; R.depth_t = st.depth[1]; R.levels_bu = 0; R.levels_grid = 0;
+    R.edges_scanned = st.edges_total; R.vertices_visited = st.visited_total; R.search_ns = 0; R.path_ns = 0;
+}
+
 // Undo the marks of a finished search: share `part` of `parts` (the CTAs of the cluster after wide rounds; 0 of 1: the
 // leader CTA alone).  A search that reached a sizeable part of the graph (a grid: millions of vertices) sweeps the visited
 // words instead of looking every logged vertex up: one CTA clearing 6 M entries one by one took 5 of the 13.6 ms of a
@@ -256,30 +336,11 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
             ptx::prefetch_l2(i < K.warm_lines ? rec + 128ull * i : vw + 128ull * (i - K.warm_lines));
         return;
     }
-    Env E;
-    E.cta = 0; E.cpr = 1; E.me = 0; E.lo = 0;
-    E.P = K.P; E.B = K.B; E.n = K.n; E.nw = K.L.nw;
-    E.C = ctrl_of(K, 0);
-    E.A = &fs.acc; E.sA = &fs.acc;
-    E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = false; E.solo = true; E.tag = 0; E.smem_src = false;
-    E.stage = nullptr; E.stage_cnt = nullptr; E.cta_new = nullptr; E.cta_edges = nullptr; E.s_sent = nullptr; E.s_rnew = nullptr;
-    E.vis = vis_of(K, 0);
-    E.parent[0] = parent_of(K, 0, 0); E.parent[1] = parent_of(K, 0, 1);
-    E.q[0] = q_of(K, 0, 0); E.q[1] = q_of(K, 0, 1);
-    E.row_ptr = K.row_ptr[0];
-    E.col = K.col[0];
+    const Env E = front_env(K, fs);
     Ctrl* const C = E.C;
     const u64 deadline = ptx::globaltimer_ns() + (u64)K.watchdog_ms * 1000000ull;
     KT_STAMP(0);
-    PairIO io;
-    if (MULTI) {
-        u32* lg = reinterpret_cast<u32*>(K.arena[0] + K.L.off_log);
-        u32* pa = reinterpret_cast<u32*>(K.arena[0] + K.L.off_pall);
-        const size_t nv = (size_t)K.B * K.P;
-        io.log[0] = lg; io.log[1] = lg + nv; io.par[0] = pa; io.par[1] = pa + nv;
-    } else {
-        io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
-    }
+    const PairIO io = front_io<MULTI>(K, E);
     if (cl_rank > 0) {
         // the other CTAs of the working cluster: wait until the leader CTA has decided whether its rounds go wide (it pushes
         // its state into this CTA's shared memory before it arrives at the barrier), take part if so, and leave
@@ -297,9 +358,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
         if (!cl_pending) return;
         cl_pending = false;
         if (fs.ps.out.go_wide && tid == 0) {
-            Ctrl::Wide& W = C->wide;
-            for (u32 z = 0; z < 3; ++z) { W.cnt[z][0] = 0; W.cnt[z][1] = 0; W.flag[z] = 0; W.meet[z] = NO_V; W.tr_edges[z][0] = 0; W.tr_edges[z][1] = 0; }
-            W.meet_old[0] = NO_V; W.meet_old[1] = NO_V; W.edges = 0; W.long_packed[0] = 0; W.long_packed[1] = 0; W.long_packed[2] = 0;
+            wide_reset(C->wide);
         }
         if (tid < 16u * (cl_n - 1u)) {
             const u32 c = 1u + tid / 16u, i = tid % 16u;
@@ -326,32 +385,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
     if (MULTI) for (u32 p = 0; p < K.P; ++p) tier = tier && K.vrec[p] != nullptr;
     else tier = tier && K.vrec[0] != nullptr;
     if (tid == 0) {
-        LevelState& G = st;
-        C->q_src = src; C->q_dst = dst;
-        C->trace_count = 0;
-        C->t_begin_ns = ptx::globaltimer_ns();
-        fs.acc.q_tail[0] = 1; fs.acc.q_tail[1] = 1; fs.acc.new_count = 0; fs.acc.meet_local = NO_V; fs.acc.edges = 0;
-        fs.fail = 0;
-        G.phase = PH_TD_SOLO; G.side = 0; G.levels = 0; G.levels_bu = 0;
-        G.depth[0] = G.depth[1] = 0; G.nf[0] = G.nf[1] = 1;
-        for (u32 s = 0; s < 2; ++s) {
-            G.q_lo[s] = 0; G.q_hi[s] = 1; G.fbm_cur[s] = 0; G.fbm_valid[s] = 0; G.rq_tag[s] = 0;
-            for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
-        }
-        G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 1; G.pad = 0; G.rounds_paired = 0; G.levels_grid = 0;
-        G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
-        G.edges_total = 0; G.visited_total = 2;
-        G.xepoch = C->xepoch;
-        if (bad) { G.status = 2; G.phase = PH_DONE; }
-        else if (src == dst) { G.length = 0; G.meet = src; G.phase = PH_DONE; G.visited_total = 1; fs.acc.q_tail[0] = 0; fs.acc.q_tail[1] = 0; G.q_hi[0] = G.q_hi[1] = 0; }
-        else {
-            // seeds: marked in rank 0's visited words whoever owns them; the owners learn about them at a hand-over
-            atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[src >> 5]), 1ull << (src & 31));
-            atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[dst >> 5]), 1ull << ((dst & 31) + 32));
-            io.log[0][0] = src; io.par[0][src] = NO_V;
-            io.log[1][0] = dst; io.par[1][dst] = NO_V;
-        }
-        if (G.phase == PH_DONE) write_result(K, C, G);
+        front_begin_query(K, E, fs, io, src, dst, bad);
     }
     if (MULTI && K.async_peers && !K.lone && warp == 1) {
         // never more than one verdict ahead of a peer (the verdict slots alternate by query parity)
@@ -409,10 +443,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
         // pool lane: nobody to hand over to.  Undo the marks, report "handed over"; the caller answers the query elsewhere
         clear_marks(E, io, fs.acc.q_tail[0], fs.acc.q_tail[1], 0u, (ran_tier && fs.ps.out.went_wide) ? cl_n : 1u);
         if (tid == 0) {
-            Result& R = C->res;
-            R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
-            R.depth_s = st.depth[0]; R.depth_t = st.depth[1]; R.levels_bu = 0; R.levels_grid = 0;
-            R.edges_scanned = st.edges_total; R.vertices_visited = st.visited_total; R.search_ns = 0; R.path_ns = 0;
+            escalated_result(C->res, st);
         }
         __syncthreads();
         if (K.fuse_path) result_to_host(K);
@@ -440,10 +471,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front(const __grid_constant_
         for (u32 i = tid; i < sizeof(LevelState) / 4; i += BFS_THREADS) g[i] = s[i];
         if (tid == 0) {
             C->acc = fs.acc;
-            Result& R = C->res;
-            R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
-            R.depth_s = st.depth[0]; R.depth_t = st.depth[1]; R.levels_bu = 0; R.levels_grid = 0;
-            R.edges_scanned = st.edges_total; R.vertices_visited = st.visited_total; R.search_ns = 0; R.path_ns = 0;
+            escalated_result(C->res, st);
         }
     }
     __syncthreads();
@@ -483,28 +511,9 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
     const KParams& K = sK;
     FrontSmem& fs = *reinterpret_cast<FrontSmem*>(smem_raw);
     LevelState& st = fs.st;
-    Env E;
-    E.cta = 0; E.cpr = 1; E.me = 0; E.lo = 0;
-    E.P = K.P; E.B = K.B; E.n = K.n; E.nw = K.L.nw;
-    E.C = ctrl_of(K, 0);
-    E.A = &fs.acc; E.sA = &fs.acc;
-    E.sq = nullptr; E.sq_base = 0; E.s_hub = nullptr; E.filter = false; E.solo = true; E.tag = 0; E.smem_src = false;
-    E.stage = nullptr; E.stage_cnt = nullptr; E.cta_new = nullptr; E.cta_edges = nullptr; E.s_sent = nullptr; E.s_rnew = nullptr;
-    E.vis = vis_of(K, 0);
-    E.parent[0] = parent_of(K, 0, 0); E.parent[1] = parent_of(K, 0, 1);
-    E.q[0] = q_of(K, 0, 0); E.q[1] = q_of(K, 0, 1);
-    E.row_ptr = K.row_ptr[0];
-    E.col = K.col[0];
+    const Env E = front_env(K, fs);
     Ctrl* const C = E.C;
-    PairIO io;
-    if (MULTI) {
-        u32* lg = reinterpret_cast<u32*>(K.arena[0] + K.L.off_log);
-        u32* pa = reinterpret_cast<u32*>(K.arena[0] + K.L.off_pall);
-        const size_t nv = (size_t)K.B * K.P;
-        io.log[0] = lg; io.log[1] = lg + nv; io.par[0] = pa; io.par[1] = pa + nv;
-    } else {
-        io.log[0] = E.q[0]; io.log[1] = E.q[1]; io.par[0] = E.parent[0]; io.par[1] = E.parent[1];
-    }
+    const PairIO io = front_io<MULTI>(K, E);
     u64* const wide_stage = reinterpret_cast<u64*>(&fs.ps.fr[0][0][0][0]);
     bool tier_ok = true;
     if (MULTI) for (u32 p = 0; p < K.P; ++p) tier_ok = tier_ok && K.vrec[p] != nullptr;
@@ -576,31 +585,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
         const bool bad = src >= K.n || dst >= K.n;
         const bool tier = tier_ok && !bad && src != dst;
         if (tid == 0) {
-            LevelState& G = st;
-            C->q_src = src; C->q_dst = dst;
-            C->trace_count = 0;
-            C->t_begin_ns = ptx::globaltimer_ns();
-            fs.acc.q_tail[0] = 1; fs.acc.q_tail[1] = 1; fs.acc.new_count = 0; fs.acc.meet_local = NO_V; fs.acc.edges = 0;
-            fs.fail = 0;
-            G.phase = PH_TD_SOLO; G.side = 0; G.levels = 0; G.levels_bu = 0;
-            G.depth[0] = G.depth[1] = 0; G.nf[0] = G.nf[1] = 1;
-            for (u32 s = 0; s < 2; ++s) {
-                G.q_lo[s] = 0; G.q_hi[s] = 1; G.fbm_cur[s] = 0; G.fbm_valid[s] = 0; G.rq_tag[s] = 0;
-                for (u32 p = 0; p < MAXR; ++p) { G.rq_lo[s][p] = 0; G.rq_hi[s][p] = 0; }
-            }
-            G.length = -1; G.meet = NO_V; G.status = 0; G.wake = 0; G.local_front = 1; G.pad = 0; G.rounds_paired = 0; G.levels_grid = 0;
-            G.hub_entries = 0; G.hub_chunks = 0; G.prev_phase = PH_TD_SOLO;
-            G.edges_total = 0; G.visited_total = 2;
-            G.xepoch = C->xepoch;
-            if (bad) { G.status = 2; G.phase = PH_DONE; fs.acc.q_tail[0] = 0; fs.acc.q_tail[1] = 0; }
-            else if (src == dst) { G.length = 0; G.meet = src; G.phase = PH_DONE; G.visited_total = 1; fs.acc.q_tail[0] = 0; fs.acc.q_tail[1] = 0; }
-            else {
-                atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[src >> 5]), 1ull << (src & 31));
-                atomicOr(reinterpret_cast<unsigned long long*>(&E.vis[dst >> 5]), 1ull << ((dst & 31) + 32));
-                io.log[0][0] = src; io.par[0][src] = NO_V;
-                io.log[1][0] = dst; io.par[1][dst] = NO_V;
-            }
-            if (G.phase == PH_DONE) write_result(K, C, G);
+            front_begin_query(K, E, fs, io, src, dst, bad);
             fs.ps.out.go_wide = 0;
         }
         __syncthreads();
@@ -612,9 +597,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
         if (cl_n > 1) {
             // hand fs.ps.out to the helpers and release them
             if (wide && tid == 0) {
-                Ctrl::Wide& W = C->wide;
-                for (u32 z = 0; z < 3; ++z) { W.cnt[z][0] = 0; W.cnt[z][1] = 0; W.flag[z] = 0; W.meet[z] = NO_V; W.tr_edges[z][0] = 0; W.tr_edges[z][1] = 0; }
-                W.meet_old[0] = NO_V; W.meet_old[1] = NO_V; W.edges = 0; W.long_packed[0] = 0; W.long_packed[1] = 0; W.long_packed[2] = 0;
+                wide_reset(C->wide);
             }
             __syncthreads();
             push_out();
@@ -631,10 +614,7 @@ __global__ void __launch_bounds__(BFS_THREADS, 1) k_front_batch(const KParams* _
         // ---- result (or "not finished here") and, in resident mode, the path to the host; then undo the marks (from the
         // shared-memory log when the search never left the narrow rounds)
         if (st.phase != PH_DONE && tid == 0) {
-            Result& R = C->res;
-            R.length = -1; R.meet = NO_V; R.status = ST_ESCALATED; R.path_len = 0; R.levels = st.levels; R.rounds_paired = st.rounds_paired;
-            R.depth_s = st.depth[0]; R.depth_t = st.depth[1]; R.levels_bu = 0; R.levels_grid = 0;
-            R.edges_scanned = st.edges_total; R.vertices_visited = st.visited_total; R.search_ns = 0; R.path_ns = 0;
+            escalated_result(C->res, st);
         }
         __syncthreads();
         const u32 t0 = fs.acc.q_tail[0], t1 = fs.acc.q_tail[1];
