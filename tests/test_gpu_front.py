@@ -207,8 +207,8 @@ def test_native_cli_gpu_variants(bb, tmp_path):
 
 def test_resident_solver_mailbox(bb):
     """One resident front kernel answers a stream of queries through the pinned mailbox: lengths and paths equal to the
-    serial variant, the kernel is launched once for the whole stream, idles out and comes back, and a search beyond the
-    front kernel falls back to the general kernel."""
+    serial variant (short paths from the mailbox, long ones from the arena), the kernel is launched once for the whole
+    stream, idles out and comes back; wide rounds and long rows run inside it on a cluster of 4."""
     import time
     spec = bb.er_spec(20000, 2.2 / 20000, seed=3)
     g_cpu = bb.Graph.generate(spec)
