@@ -221,6 +221,8 @@ struct alignas(64) Mailbox {
     alignas(64) u32 out[PATH_HDR_WORDS + 240];
 };
 constexpr u32 MB_EXIT = 0x80000000u;
+static_assert(offsetof(Mailbox, seq) == 8 && offsetof(Mailbox, alive) == 64 && offsetof(Mailbox, out_seq) == 68 && offsetof(Mailbox, out) == 128,
+              "mailbox layout: the query is one 16-byte load, host-written and device-written words sit in different 64-byte lines");
 
 // implemented in bfs_dev.cu
 int bfs_max_ctas_per_device(bool multi, int* out);
